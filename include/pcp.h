@@ -1,0 +1,181 @@
+/*
+ * pcp.h -- C ABI of the B200-native nearest-neighbour + ICP library (libpcp_b200.so).
+ *
+ * This is the drop-in boundary for the one hot path of ruanyyyyyyy/point-cloud-process:
+ * exact kNN / radius search (Kdtree_Octree/lesson2) and the point-to-point ICP loop
+ * (Registration/main.py, icp_template.py).  The reference has NO FFI on this path -- it is pure
+ * Python over numpy/Open3D -- so every entry point below cites the reference Python interface it
+ * replaces (file:line relative to the reference root).  The pybind11 module `_pcp`
+ * (point_cloud_process_b200/csrc/bindings.cpp, the PCLKeypoints/src/keypoints.cpp:240-298
+ * packaging pattern) and the Python shims call ONLY these functions.
+ *
+ * Conventions
+ *   - plain pointers + sizes, no C++ / torch types; opaque handles; int status return
+ *     (0 = PCP_OK, negative = error, message via pcp_last_error(), thread-local).
+ *   - clouds are row-per-point float32 (x, y, z) with a row stride in floats (3 for packed
+ *     N x 3 -- the layout benchmark.py:19 documents -- 4 for KITTI x,y,z,intensity rows
+ *     (benchmark.py:24), 6 for the Oxford xyz+normal rows of main.py:14 / icp_template.py:16).
+ *   - `mem` says where ALL data pointers of that call live: PCP_HOST (pageable or pinned host
+ *     memory; the library stages through pinned buffers and copies inside the call) or
+ *     PCP_DEVICE (device memory of the context's GPU; nothing is copied, the call is
+ *     asynchronous on the context stream -- use pcp_ctx_synchronize()).
+ *   - thread-compatible: one context per host thread; contexts are independent.
+ *   - there is no CPU fallback: every call fails with PCP_ERR_CUDA when no sm_100 device is
+ *     usable.
+ */
+#ifndef PCP_H_
+#define PCP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PCP_API __attribute__((visibility("default")))
+#else
+#define PCP_API
+#endif
+
+#define PCP_VERSION 100 /* 0.1.0 */
+
+enum pcp_status {
+    PCP_OK = 0,
+    PCP_ERR_INVALID = -1,     /* bad argument (NULL, negative size, k out of range, dim != 3 ...) */
+    PCP_ERR_CUDA = -2,        /* CUDA runtime / launch error, or no usable device */
+    PCP_ERR_OOM = -3,         /* device or pinned-host allocation failed */
+    PCP_ERR_UNSUPPORTED = -4  /* valid request the library does not implement (k > PCP_MAX_K) */
+};
+
+enum pcp_mem { PCP_HOST = 0, PCP_DEVICE = 1 };
+
+#define PCP_MAX_K 32           /* register top-k width; the reference configs use k = 1, 8, 16 */
+#define PCP_KNN_EMPTY_DIST 1e10f /* result_set.py:19-22: unfilled KNNResultSet slots are (1e10, 0) */
+
+typedef struct pcp_ctx pcp_ctx;       /* one GPU + one stream + scratch memory */
+typedef struct pcp_index pcp_index;   /* search structure over one cloud (replaces the kd-tree / octree root) */
+
+/* ---- library ------------------------------------------------------------------------------ */
+PCP_API int pcp_version(void);
+PCP_API const char *pcp_last_error(void);
+PCP_API int pcp_device_count(int *count);
+
+/* ---- context ------------------------------------------------------------------------------- */
+PCP_API int pcp_ctx_create(int device, pcp_ctx **out);
+PCP_API int pcp_ctx_destroy(pcp_ctx *ctx);
+PCP_API int pcp_ctx_synchronize(pcp_ctx *ctx);
+/* cudaStream_t of the context as an opaque pointer (for callers that enqueue their own work). */
+PCP_API void *pcp_ctx_stream(pcp_ctx *ctx);
+/* Number of kernels this library has launched on the context since creation (bench bookkeeping). */
+PCP_API int64_t pcp_ctx_launch_count(pcp_ctx *ctx);
+
+/* Work counters -- the analogue of the reference's comparison_counter (result_set.py:24,36,70,79).
+ * When enabled, search kernels accumulate into 8 device-side 64-bit words, read back (and reset)
+ * by pcp_ctx_read_counters:
+ *   [0] distance evaluations (query, point) pairs   [1] bucket lower-bound tests (per group / query)
+ *   [2] hierarchy nodes opened                      [3] top-k drain rounds
+ *   [4] query groups (kNN) or queries (radius)      [5] buckets scanned        [6..7] reserved
+ * Counting costs a few instructions per bucket; it is OFF by default and off in timed runs. */
+PCP_API int pcp_ctx_enable_counters(pcp_ctx *ctx, int enable);
+PCP_API int pcp_ctx_read_counters(pcp_ctx *ctx, uint64_t out[8]);
+
+/* ---- index build ---------------------------------------------------------------------------
+ * Replaces kdtree_construction(db_np, leaf_size)            kdtree.py:119-137
+ *      and octree_construction(db_np, leaf_size, min_extent) octree.py:310-328.
+ * Builds the Morton-sorted 32-point bucket hierarchy on the GPU.
+ * leaf_size / min_extent of the reference have no meaning here and are not parameters.
+ * n may be 0 (every search then returns empty results). */
+PCP_API int pcp_index_build(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_floats, int mem,
+                    pcp_index **out);
+/* Re-index a new cloud into an existing handle, reusing its device buffers. */
+PCP_API int pcp_index_rebuild(pcp_index *index, const float *xyz, int64_t n, int64_t stride_floats, int mem);
+PCP_API int pcp_index_destroy(pcp_index *index);
+PCP_API int64_t pcp_index_size(const pcp_index *index);
+/* Device-resident internals for diagnostics / benches: number of buckets and hierarchy levels. */
+PCP_API int pcp_index_stats(const pcp_index *index, int64_t *n_buckets, int *n_levels);
+
+/* ---- k nearest neighbours --------------------------------------------------------------------
+ * Replaces kdtree_knn_search(root, db, result_set, query)   kdtree.py:141-172
+ *      and octree_knn_search(root, db, result_set, query)   octree.py:262-306
+ * with KNNResultSet(capacity=k) semantics                   result_set.py:16-60,
+ * batched over nq queries.  For query i:
+ *   idx [i*k .. i*k+k)  indices into the indexed cloud, ascending (distance, index);
+ *   dist[i*k .. i*k+k)  float32 EUCLIDEAN distance sqrtf((dx*dx+dy*dy)+dz*dz), bit-equal to
+ *                       np.linalg.norm(query - db[idx]) of kdtree.py:157-158;
+ *   count[i]            = min(k, n)  (KNNResultSet.count); slots >= count hold
+ *                       (PCP_KNN_EMPTY_DIST, 0) as result_set.py:19-22 leaves them.
+ * Tie rule: equal float32 distances are ordered by ascending index (the reference's order among
+ * exact ties depends on tree visit order, result_set.py:37,45).
+ * 1 <= k <= PCP_MAX_K.  count may be NULL. */
+PCP_API int pcp_knn(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats, int k, int mem,
+            int32_t *idx, float *dist, int32_t *count);
+
+/* Same search with the indexed cloud itself as the query set, in the cloud's original order
+ * (the benchmark.py:122 `query = db_np[0,:]` case generalised to every point).  Skips the query
+ * sort because the buckets already are the query groups. */
+PCP_API int pcp_knn_self(pcp_index *index, int k, int mem, int32_t *idx, float *dist, int32_t *count);
+
+/* ---- fixed-radius search -----------------------------------------------------------------------
+ * Replaces kdtree_radius_search                              kdtree.py:176-208
+ *      and octree_radius_search / octree_radius_search_fast  octree.py:166-259
+ * with RadiusNNResultSet(radius) semantics                   result_set.py:63-93:
+ * every indexed point with NOT (dist > radius), i.e. float32 dist <= radius, boundary included.
+ * Two-phase CSR sizing: pcp_radius_count writes offsets[0..nq] (exclusive prefix sum of the
+ * per-query counts, offsets[nq] = total M); the caller allocates M entries and calls
+ * pcp_radius_fill with the same queries/radius.  Within a query the order is unspecified unless
+ * sorted != 0, which orders by ascending (distance, index) (what RadiusNNResultSet.__str__,
+ * result_set.py:87, prints). */
+PCP_API int pcp_radius_count(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats,
+                     float radius, int mem, int64_t *offsets);
+PCP_API int pcp_radius_fill(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats,
+                    float radius, int mem, const int64_t *offsets, int32_t *idx, float *dist,
+                    int sorted);
+
+/* ---- point-to-point ICP, batched over independent pairs ------------------------------------------
+ * Replaces icp_point2point(source, target, transformation)   main.py:97-156
+ *      and the ICP / find_associations / procrustes_transformation contract of
+ *      icp_template.py:43-54,113-126,128-200.
+ * Every iteration (transform, 1-NN correspondence, d^2 < dist_thres gate, centroid + 3x3
+ * cross-covariance, SVD, R = U V^T, t, convergence test) runs on the device. */
+typedef struct pcp_icp_params {
+    int32_t max_iteration;      /* main.py:98   100 */
+    double R_diff_thres;        /* main.py:101  0.5  (Frobenius norm of R - R_last) */
+    double t_diff_thres;        /* main.py:102  0.5 */
+    double dist_thres;          /* main.py:103  5    (compared with the SQUARED 1-NN distance, main.py:119) */
+    int32_t first_iter_broadcast; /* 1 = reproduce main.py:150 on iteration 1, where t (3,1) minus
+                                     t_last (3,) broadcasts to 3x3 before the norm; 0 = plain ||t - t_last|| */
+} pcp_icp_params;
+
+enum pcp_icp_status_code {
+    PCP_ICP_CONVERGED = 0,       /* stopped by the R_diff / t_diff test (main.py:153-154) */
+    PCP_ICP_MAX_ITER = 1,        /* ran max_iteration iterations */
+    PCP_ICP_FEW_PAIRS = 2        /* fewer than 3 associations (main.py:125-127): T_last is the last applied transform */
+};
+
+PCP_API int pcp_icp_default_params(pcp_icp_params *p);
+
+/* src_xyz / tgt_xyz: packed rows (stride_floats each) of all pairs back to back;
+ * src_offsets / tgt_offsets: n_pairs+1 row offsets (int64, host memory always).
+ * T_init: n_pairs x 16 row-major float64 (NULL = identity).
+ * Outputs (host memory always; any may be NULL):
+ *   T_last  n_pairs x 16  the LAST INCREMENT -- what icp_point2point returns (main.py:156)
+ *   T_total n_pairs x 16  composed pose source->target incl. the last increment
+ *                         (homo_mat_total of icp_template.py:136,198)
+ *   iterations, status    per pair
+ *   diff_log n_pairs x max_iteration x 2  (R_diff, t_diff) per iteration, NaN beyond `iterations`
+ *                         (the `log` dict of icp_template.py:161,186-187) */
+PCP_API int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_pairs,
+                  const float *src_xyz, const int64_t *src_offsets,
+                  const float *tgt_xyz, const int64_t *tgt_offsets, int64_t stride_floats, int mem,
+                  const double *T_init, double *T_last, double *T_total, int32_t *iterations,
+                  int32_t *status, double *diff_log);
+
+/* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
+ * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
+PCP_API int pcp_homo2tq(const double *homo, double *tq);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCP_H_ */

@@ -1,0 +1,89 @@
+"""Batched extension of the reference interface: whole query sets / pair batches per
+call.  Thin Python over the pybind11 module, which is thin C++ over the C ABI (include/pcp.h)."""
+import threading
+
+import numpy as np
+
+from . import native
+
+_tls = threading.local()
+
+
+def default_context(device=0):
+    """One context (GPU + stream + scratch) per host thread and device."""
+    ctxs = getattr(_tls, "ctxs", None)
+    if ctxs is None:
+        ctxs = _tls.ctxs = {}
+    if device not in ctxs:
+        ctxs[device] = native.Context(device)     # raises RuntimeError when no sm_100 GPU: no CPU fallback
+    return ctxs[device]
+
+
+def _as_cloud(a, name):
+    a = np.asarray(a)
+    if a.ndim == 1 and a.shape[0] == 3:
+        a = a[None, :]
+    if a.ndim != 2 or a.shape[1] < 3:
+        raise ValueError(f"{name}: expected an (N, 3) row-per-point array, got shape {a.shape}; "
+                         "the GPU search structure is 3-D only")
+    if a.shape[1] != 3:
+        a = a[:, :3]
+    # float64 input (kdtree.py:219 demo) is down-cast: bit-parity is guaranteed for float32 only
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class SearchIndex:
+    """Replaces the kd-tree / octree root handle (kdtree.py:119-137, octree.py:310-328)."""
+
+    def __init__(self, db_np, device=0, ctx=None):
+        self.ctx = ctx or default_context(device)
+        self.db = _as_cloud(db_np, "db_np")
+        self._ix = native.Index(self.ctx, self.db)
+
+    def __len__(self):
+        return self._ix.size()
+
+    def stats(self):
+        return self._ix.stats()
+
+    def knn(self, queries, k):
+        """-> (idx (Q,k) int32, dist (Q,k) float32 Euclidean, count (Q,) int32); rows ascending by
+        (distance, index); slots >= count hold (1e10, 0) like KNNResultSet (result_set.py:19-22)."""
+        return self._ix.knn(_as_cloud(queries, "queries"), int(k))
+
+    def knn_self(self, k):
+        """kNN of every indexed point against the cloud itself, original order."""
+        return self._ix.knn_self(int(k))
+
+    def radius(self, queries, radius, sorted=False):
+        """-> CSR (offsets (Q+1,) int64, idx (M,) int32, dist (M,) float32): all points with
+        float32 dist <= radius (result_set.py:80)."""
+        return self._ix.radius(_as_cloud(queries, "queries"), float(np.float32(radius)), bool(sorted))
+
+
+def icp_batch(sources, targets, T_init=None, max_iteration=100, R_diff_thres=0.5, t_diff_thres=0.5,
+              dist_thres=5.0, first_iter_broadcast=True, device=0, ctx=None, want_log=False):
+    """Batched icp_point2point (main.py:97-156) over independent pairs.
+
+    sources / targets: lists of (N_i, 3) arrays.  Returns dict with T_last (P,4,4) -- what the
+    reference returns --, T_total (P,4,4) composed pose, iterations (P,), status (P,) and, with
+    want_log, diff_log (P, max_iteration, 2)."""
+    ctx = ctx or default_context(device)
+    src = [_as_cloud(s, "source") for s in sources]
+    tgt = [_as_cloud(t, "target") for t in targets]
+    if len(src) != len(tgt):
+        raise ValueError("sources and targets must have the same length")
+    P = len(src)
+    so = np.zeros(P + 1, np.int64)
+    to = np.zeros(P + 1, np.int64)
+    if P:
+        so[1:] = np.cumsum([len(s) for s in src])
+        to[1:] = np.cumsum([len(t) for t in tgt])
+    sp = np.concatenate(src) if P else np.zeros((0, 3), np.float32)
+    tp = np.concatenate(tgt) if P else np.zeros((0, 3), np.float32)
+    if T_init is None:
+        T0 = np.tile(np.eye(4), (P, 1, 1))
+    else:
+        T0 = np.ascontiguousarray(np.asarray(T_init, np.float64).reshape(P, 4, 4))
+    return native.icp_batch(ctx, sp, so, tp, to, T0, int(max_iteration), float(R_diff_thres),
+                            float(t_diff_thres), float(dist_thres), bool(first_iter_broadcast), bool(want_log))

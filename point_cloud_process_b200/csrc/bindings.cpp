@@ -1,0 +1,221 @@
+// pybind11 module `_pcp`: thin Python binding over the C ABI of include/pcp.h and NOTHING else
+// (the PCLKeypoints/src/keypoints.cpp:240-298 pattern: one PYBIND11_MODULE, m.def with py::arg
+// defaults, __version__ attribute, C++ failures surface as Python exceptions).
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "pcp.h"
+
+namespace py = pybind11;
+
+namespace {
+
+using f32_array = py::array_t<float, py::array::c_style | py::array::forcecast>;
+using f64_array = py::array_t<double, py::array::c_style | py::array::forcecast>;
+using i64_array = py::array_t<int64_t, py::array::c_style | py::array::forcecast>;
+
+void check(int status, const char *what) {
+    if (status == PCP_OK) return;
+    std::string msg = std::string(what) + ": " + pcp_last_error();
+    if (status == PCP_ERR_INVALID) throw py::value_error(msg);
+    if (status == PCP_ERR_OOM) throw std::bad_alloc();
+    throw std::runtime_error(msg);
+}
+
+// rows x cols float32 view; the reference's clouds are (N, 3) (benchmark.py:19); (N, >=3) rows with
+// extra columns (KITTI intensity, Oxford normals) are accepted and only x,y,z are read.
+struct Cloud {
+    f32_array arr;
+    int64_t n, stride;
+    explicit Cloud(const py::object &o, const char *name) : arr(f32_array::ensure(o)) {
+        if (!arr) throw py::value_error(std::string(name) + ": cannot convert to a float32 array");
+        if (arr.ndim() == 1 && arr.shape(0) == 3) arr = arr.reshape({(py::ssize_t)1, (py::ssize_t)3});
+        if (arr.ndim() != 2 || arr.shape(1) < 3)
+            throw py::value_error(std::string(name) + ": expected shape (N, 3) [row per point], got ndim=" +
+                                  std::to_string(arr.ndim()) +
+                                  (arr.ndim() == 2 ? " cols=" + std::to_string(arr.shape(1)) : "") +
+                                  "; the search structure is 3-D only");
+        n = arr.shape(0);
+        stride = arr.shape(1);
+    }
+    const float *data() const { return arr.data(); }
+};
+
+class Context {
+   public:
+    explicit Context(int device) { check(pcp_ctx_create(device, &ctx_), "pcp_ctx_create"); }
+    ~Context() { pcp_ctx_destroy(ctx_); }
+    Context(const Context &) = delete;
+    pcp_ctx *get() const { return ctx_; }
+    void synchronize() { check(pcp_ctx_synchronize(ctx_), "pcp_ctx_synchronize"); }
+    int64_t launch_count() const { return pcp_ctx_launch_count(ctx_); }
+    uintptr_t stream() const { return reinterpret_cast<uintptr_t>(pcp_ctx_stream(ctx_)); }
+    void enable_counters(bool on) { check(pcp_ctx_enable_counters(ctx_, on ? 1 : 0), "pcp_ctx_enable_counters"); }
+    std::vector<uint64_t> read_counters() {
+        std::vector<uint64_t> v(8);
+        check(pcp_ctx_read_counters(ctx_, v.data()), "pcp_ctx_read_counters");
+        return v;
+    }
+
+   private:
+    pcp_ctx *ctx_ = nullptr;
+};
+
+class Index {
+   public:
+    Index(std::shared_ptr<Context> ctx, const py::object &points) : ctx_(std::move(ctx)) {
+        Cloud c(points, "points");
+        check(pcp_index_build(ctx_->get(), c.data(), c.n, c.stride, PCP_HOST, &ix_), "pcp_index_build");
+    }
+    // device-resident cloud: raw device pointer (e.g. torch tensor .data_ptr()) + shape
+    Index(std::shared_ptr<Context> ctx, uintptr_t dptr, int64_t n, int64_t stride) : ctx_(std::move(ctx)) {
+        check(pcp_index_build(ctx_->get(), reinterpret_cast<const float *>(dptr), n, stride, PCP_DEVICE, &ix_),
+              "pcp_index_build");
+    }
+    ~Index() { pcp_index_destroy(ix_); }
+    Index(const Index &) = delete;
+
+    void rebuild(const py::object &points) {
+        Cloud c(points, "points");
+        check(pcp_index_rebuild(ix_, c.data(), c.n, c.stride, PCP_HOST), "pcp_index_rebuild");
+    }
+    void rebuild_device(uintptr_t dptr, int64_t n, int64_t stride) {
+        check(pcp_index_rebuild(ix_, reinterpret_cast<const float *>(dptr), n, stride, PCP_DEVICE), "pcp_index_rebuild");
+    }
+    int64_t size() const { return pcp_index_size(ix_); }
+    py::tuple stats() const {
+        int64_t nb = 0;
+        int nl = 0;
+        check(pcp_index_stats(ix_, &nb, &nl), "pcp_index_stats");
+        return py::make_tuple(nb, nl);
+    }
+
+    py::tuple knn(const py::object &queries, int k) {
+        Cloud q(queries, "queries");
+        if (k < 1) throw py::value_error("k must be >= 1");
+        py::array_t<int32_t> idx({(py::ssize_t)q.n, (py::ssize_t)k});
+        py::array_t<float> dist({(py::ssize_t)q.n, (py::ssize_t)k});
+        py::array_t<int32_t> cnt((py::ssize_t)q.n);
+        {
+            py::gil_scoped_release rel;
+            check_nogil(pcp_knn(ix_, q.data(), q.n, q.stride, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(),
+                                cnt.mutable_data()), "pcp_knn");
+        }
+        rethrow();
+        return py::make_tuple(idx, dist, cnt);
+    }
+    py::tuple knn_self(int k) {
+        if (k < 1) throw py::value_error("k must be >= 1");
+        const int64_t n = size();
+        py::array_t<int32_t> idx({(py::ssize_t)n, (py::ssize_t)k});
+        py::array_t<float> dist({(py::ssize_t)n, (py::ssize_t)k});
+        py::array_t<int32_t> cnt((py::ssize_t)n);
+        {
+            py::gil_scoped_release rel;
+            check_nogil(pcp_knn_self(ix_, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(), cnt.mutable_data()),
+                        "pcp_knn_self");
+        }
+        rethrow();
+        return py::make_tuple(idx, dist, cnt);
+    }
+    // device in / device out (raw pointers), asynchronous on the context stream
+    void knn_device(uintptr_t q, int64_t nq, int64_t stride, int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
+        check(pcp_knn(ix_, reinterpret_cast<const float *>(q), nq, stride, k, PCP_DEVICE,
+                      reinterpret_cast<int32_t *>(idx), reinterpret_cast<float *>(dist),
+                      reinterpret_cast<int32_t *>(cnt)), "pcp_knn");
+    }
+    void knn_self_device(int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
+        check(pcp_knn_self(ix_, k, PCP_DEVICE, reinterpret_cast<int32_t *>(idx), reinterpret_cast<float *>(dist),
+                           reinterpret_cast<int32_t *>(cnt)), "pcp_knn_self");
+    }
+
+    py::tuple radius(const py::object &queries, double radius, bool sorted) {
+        Cloud q(queries, "queries");
+        py::array_t<int64_t> offsets((py::ssize_t)(q.n + 1));
+        check(pcp_radius_count(ix_, q.data(), q.n, q.stride, (float)radius, PCP_HOST, offsets.mutable_data()),
+              "pcp_radius_count");
+        const int64_t m = offsets.data()[q.n];
+        py::array_t<int32_t> idx((py::ssize_t)m);
+        py::array_t<float> dist((py::ssize_t)m);
+        check(pcp_radius_fill(ix_, q.data(), q.n, q.stride, (float)radius, PCP_HOST, offsets.data(),
+                              idx.mutable_data(), dist.mutable_data(), sorted ? 1 : 0), "pcp_radius_fill");
+        return py::make_tuple(offsets, idx, dist);
+    }
+    void radius_count_device(uintptr_t q, int64_t nq, int64_t stride, double radius, uintptr_t offsets) {
+        check(pcp_radius_count(ix_, reinterpret_cast<const float *>(q), nq, stride, (float)radius, PCP_DEVICE,
+                               reinterpret_cast<int64_t *>(offsets)), "pcp_radius_count");
+    }
+    void radius_fill_device(uintptr_t q, int64_t nq, int64_t stride, double radius, uintptr_t offsets, uintptr_t idx,
+                            uintptr_t dist, bool sorted) {
+        check(pcp_radius_fill(ix_, reinterpret_cast<const float *>(q), nq, stride, (float)radius, PCP_DEVICE,
+                              reinterpret_cast<const int64_t *>(offsets), reinterpret_cast<int32_t *>(idx),
+                              reinterpret_cast<float *>(dist), sorted ? 1 : 0), "pcp_radius_fill");
+    }
+
+   private:
+    // pcp_last_error() is thread-local and we stay on the same thread, so it is safe to defer
+    void check_nogil(int status, const char *what) {
+        pending_ = status;
+        what_ = what;
+        if (status != PCP_OK) msg_ = pcp_last_error();
+    }
+    void rethrow() {
+        if (pending_ == PCP_OK) return;
+        int s = pending_;
+        pending_ = PCP_OK;
+        std::string msg = std::string(what_) + ": " + msg_;
+        if (s == PCP_ERR_INVALID) throw py::value_error(msg);
+        throw std::runtime_error(msg);
+    }
+    std::shared_ptr<Context> ctx_;
+    pcp_index *ix_ = nullptr;
+    int pending_ = PCP_OK;
+    const char *what_ = "";
+    std::string msg_;
+};
+
+}  // namespace
+
+PYBIND11_MODULE(_pcp, m) {
+    m.doc() = "B200-native exact kNN / radius search and point-to-point ICP (C ABI: include/pcp.h)";
+    m.attr("__version__") = std::to_string(pcp_version() / 100) + "." + std::to_string(pcp_version() % 100);
+    m.attr("MAX_K") = PCP_MAX_K;
+    m.attr("KNN_EMPTY_DIST") = (double)PCP_KNN_EMPTY_DIST;
+    m.def("device_count", []() {
+        int n = 0;
+        int s = pcp_device_count(&n);
+        return s == PCP_OK ? n : 0;
+    });
+    m.def("last_error", []() { return std::string(pcp_last_error()); });
+
+    py::class_<Context, std::shared_ptr<Context>>(m, "Context")
+        .def(py::init<int>(), py::arg("device") = 0)
+        .def("synchronize", &Context::synchronize)
+        .def("launch_count", &Context::launch_count)
+        .def("stream", &Context::stream)
+        .def("enable_counters", &Context::enable_counters, py::arg("on") = true)
+        .def("read_counters", &Context::read_counters);
+
+    py::class_<Index>(m, "Index")
+        .def(py::init<std::shared_ptr<Context>, const py::object &>(), py::arg("ctx"), py::arg("points"))
+        .def(py::init<std::shared_ptr<Context>, uintptr_t, int64_t, int64_t>(), py::arg("ctx"), py::arg("device_ptr"),
+             py::arg("n"), py::arg("stride_floats") = 3)
+        .def("rebuild", &Index::rebuild, py::arg("points"))
+        .def("rebuild_device", &Index::rebuild_device, py::arg("device_ptr"), py::arg("n"), py::arg("stride_floats") = 3)
+        .def("size", &Index::size)
+        .def("stats", &Index::stats)
+        .def("knn", &Index::knn, py::arg("queries"), py::arg("k"))
+        .def("knn_self", &Index::knn_self, py::arg("k"))
+        .def("knn_device", &Index::knn_device)
+        .def("knn_self_device", &Index::knn_self_device)
+        .def("radius", &Index::radius, py::arg("queries"), py::arg("radius"), py::arg("sorted") = false)
+        .def("radius_count_device", &Index::radius_count_device)
+        .def("radius_fill_device", &Index::radius_fill_device);
+
+}

@@ -1,0 +1,391 @@
+// C ABI of libpcp_b200.so (include/pcp.h): argument checking, host<->device staging, error state.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "pcp_internal.cuh"
+
+namespace pcp {
+
+static thread_local std::string g_last_error;
+
+void set_error(const std::string &msg) { g_last_error = msg; }
+
+int fail(int code, const std::string &msg) {
+    g_last_error = msg;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    g_last_error = buf;
+    cudaGetLastError();   // clear sticky-free errors
+    return e == cudaErrorMemoryAllocation ? PCP_ERR_OOM : PCP_ERR_CUDA;
+}
+
+int DevBuf::ensure(size_t bytes) {
+    if (bytes <= cap) return PCP_OK;
+    size_t want = bytes + bytes / 8 + 256;
+    void *np = nullptr;
+    cudaError_t e = cudaMalloc(&np, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(PCP_ERR_OOM, "device allocation of " + std::to_string(want) + " bytes failed: " +
+                                     cudaGetErrorString(e));
+    }
+    if (p) cudaFree(p);     // contents are scratch: never preserved across a grow
+    p = np;
+    cap = want;
+    return PCP_OK;
+}
+void DevBuf::release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+int PinBuf::ensure(size_t bytes) {
+    if (bytes <= cap) return PCP_OK;
+    size_t want = bytes + bytes / 8 + 256;
+    void *np = nullptr;
+    cudaError_t e = cudaMallocHost(&np, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(PCP_ERR_OOM, "pinned host allocation of " + std::to_string(want) + " bytes failed");
+    }
+    if (p) cudaFreeHost(p);
+    p = np;
+    cap = want;
+    return PCP_OK;
+}
+void PinBuf::release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+}
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// host -> device through a pinned bounce buffer (pageable memcpyAsync would serialise anyway;
+// pinned staging keeps the copy on the context stream at full PCIe rate)
+int upload(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes) {
+    PCP_TRY(dst.ensure(bytes));
+    if (bytes == 0) return PCP_OK;
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (pinned) {
+        PCP_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        return PCP_OK;
+    }
+    PCP_TRY(ctx->pin[pin_slot].ensure(bytes));
+    memcpy(ctx->pin[pin_slot].p, src, bytes);
+    PCP_CUDA(cudaMemcpyAsync(dst.p, ctx->pin[pin_slot].p, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return PCP_OK;
+}
+
+// device -> host, synchronous on return
+int download(pcp_ctx *ctx, void *dst, const void *src, size_t bytes) {
+    if (bytes == 0) return PCP_OK;
+    PCP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return PCP_OK;
+}
+
+bool bad_mem(int mem) { return mem != PCP_HOST && mem != PCP_DEVICE; }
+
+}  // namespace
+}  // namespace pcp
+
+using namespace pcp;
+
+extern "C" {
+
+int pcp_version(void) { return PCP_VERSION; }
+
+const char *pcp_last_error(void) { return g_last_error.c_str(); }
+
+int pcp_device_count(int *count) {
+    if (!count) return fail(PCP_ERR_INVALID, "pcp_device_count: count is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *count = 0;
+        return fail(PCP_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
+    }
+    *count = n;
+    return PCP_OK;
+}
+
+int pcp_ctx_create(int device, pcp_ctx **out) {
+    if (!out) return fail(PCP_ERR_INVALID, "pcp_ctx_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    PCP_TRY(pcp_device_count(&n));
+    if (device < 0 || device >= n)
+        return fail(PCP_ERR_CUDA, "pcp_ctx_create: device " + std::to_string(device) + " not available (" +
+                                      std::to_string(n) + " CUDA devices); this library has no CPU fallback");
+    cudaDeviceProp prop;
+    PCP_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(PCP_ERR_CUDA, std::string("pcp_ctx_create: ") + prop.name + " is sm_" + std::to_string(prop.major) +
+                                      std::to_string(prop.minor) + "; libpcp_b200 is built for sm_100a only");
+    DeviceGuard g(device);
+    pcp_ctx *ctx = new (std::nothrow) pcp_ctx();
+    if (!ctx) return fail(PCP_ERR_OOM, "pcp_ctx_create: out of host memory");
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete ctx;
+        return cuda_fail(e, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
+    }
+    *out = ctx;
+    return PCP_OK;
+}
+
+int pcp_ctx_destroy(pcp_ctx *ctx) {
+    if (!ctx) return PCP_OK;
+    DeviceGuard g(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->cub_tmp.release();
+    ctx->counters.release();
+    for (auto &b : ctx->scratch) b.release();
+    for (auto &b : ctx->pin) b.release();
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return PCP_OK;
+}
+
+int pcp_ctx_synchronize(pcp_ctx *ctx) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ctx_synchronize: ctx is NULL");
+    DeviceGuard g(ctx->device);
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+void *pcp_ctx_stream(pcp_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+int64_t pcp_ctx_launch_count(pcp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int pcp_ctx_enable_counters(pcp_ctx *ctx, int enable) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ctx_enable_counters: ctx is NULL");
+    DeviceGuard g(ctx->device);
+    if (enable) {
+        PCP_TRY(ctx->counters.ensure(8 * sizeof(unsigned long long)));
+        PCP_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    }
+    ctx->count_work = enable != 0;
+    return PCP_OK;
+}
+
+int pcp_ctx_read_counters(pcp_ctx *ctx, uint64_t out[8]) {
+    if (!ctx || !out) return fail(PCP_ERR_INVALID, "pcp_ctx_read_counters: NULL argument");
+    memset(out, 0, 8 * sizeof(uint64_t));
+    if (!ctx->counters.p) return PCP_OK;
+    DeviceGuard g(ctx->device);
+    PCP_CUDA(cudaMemcpyAsync(out, ctx->counters.p, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA(cudaMemsetAsync(ctx->counters.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- index
+
+static int check_cloud(const char *fn, const float *xyz, int64_t n, int64_t stride, int mem) {
+    if (n < 0) return fail(PCP_ERR_INVALID, std::string(fn) + ": negative point count");
+    if (n > 0 && !xyz) return fail(PCP_ERR_INVALID, std::string(fn) + ": xyz is NULL");
+    if (stride < 3)
+        return fail(PCP_ERR_INVALID, std::string(fn) + ": stride_floats must be >= 3 (rows are x,y,z[,...]); the "
+                                                       "search structure is 3-D only (dim != 3 is rejected)");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, std::string(fn) + ": mem must be PCP_HOST or PCP_DEVICE");
+    return PCP_OK;
+}
+
+int pcp_index_rebuild(pcp_index *ix, const float *xyz, int64_t n, int64_t stride, int mem) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_index_rebuild: index is NULL");
+    PCP_TRY(check_cloud("pcp_index_build", xyz, n, stride, mem));
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const float *d_xyz = xyz;
+    if (mem == PCP_HOST && n > 0) {
+        PCP_TRY(upload(ctx, 0, ix->src_copy, xyz, sizeof(float) * (size_t)n * (size_t)stride));
+        d_xyz = ix->src_copy.as<float>();
+    }
+    PCP_TRY(index_build_device(ix, d_xyz, n, stride));
+    if (mem == PCP_HOST) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+int pcp_index_build(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride, int mem, pcp_index **out) {
+    if (!ctx || !out) return fail(PCP_ERR_INVALID, "pcp_index_build: ctx/out is NULL");
+    *out = nullptr;
+    PCP_TRY(check_cloud("pcp_index_build", xyz, n, stride, mem));
+    pcp_index *ix = new (std::nothrow) pcp_index();
+    if (!ix) return fail(PCP_ERR_OOM, "pcp_index_build: out of host memory");
+    ix->ctx = ctx;
+    int s = pcp_index_rebuild(ix, xyz, n, stride, mem);
+    if (s != PCP_OK) {
+        pcp_index_destroy(ix);
+        return s;
+    }
+    *out = ix;
+    return PCP_OK;
+}
+
+int pcp_index_destroy(pcp_index *ix) {
+    if (!ix) return PCP_OK;
+    DeviceGuard g(ix->ctx->device);
+    cudaStreamSynchronize(ix->ctx->stream);
+    for (DevBuf *b : {&ix->pts, &ix->box_lo, &ix->box_hi, &ix->bbox, &ix->keys_a, &ix->keys_b, &ix->vals_a,
+                      &ix->vals_b, &ix->src_copy})
+        b->release();
+    delete ix;
+    return PCP_OK;
+}
+
+int64_t pcp_index_size(const pcp_index *ix) { return ix ? ix->n : 0; }
+
+int pcp_index_stats(const pcp_index *ix, int64_t *n_buckets, int *n_levels) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_index_stats: index is NULL");
+    if (n_buckets) *n_buckets = ix->n_leaf;
+    if (n_levels) *n_levels = ix->n_levels;
+    return PCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- kNN
+
+static int check_k(int k) {
+    if (k < 1) return fail(PCP_ERR_INVALID, "pcp_knn: k must be >= 1");
+    if (k > PCP_MAX_K) return fail(PCP_ERR_UNSUPPORTED, "pcp_knn: k > PCP_MAX_K (32) is not implemented");
+    return PCP_OK;
+}
+
+int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int k, int mem, int32_t *idx,
+            float *dist, int32_t *count) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_knn: index is NULL");
+    PCP_TRY(check_cloud("pcp_knn", queries, nq, stride, mem));
+    PCP_TRY(check_k(k));
+    if (nq > 0 && (!idx || !dist)) return fail(PCP_ERR_INVALID, "pcp_knn: idx/dist is NULL");
+    if (nq == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const float *d_q = queries;
+    int32_t *d_idx = idx, *d_cnt = count;
+    float *d_dist = dist;
+    const size_t nres = (size_t)nq * (size_t)k;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        d_q = ctx->scratch[6].as<float>();
+        // one result slab: idx | dist | count
+        PCP_TRY(ctx->scratch[7].ensure(nres * 8 + sizeof(int32_t) * (size_t)nq));
+        d_idx = ctx->scratch[7].as<int32_t>();
+        d_dist = reinterpret_cast<float *>(d_idx + nres);
+        d_cnt = reinterpret_cast<int32_t *>(d_dist + nres);
+    }
+    // one warp per query: queries are independent, no reordering pass is needed
+    const uint32_t *d_perm = nullptr;
+    PCP_TRY(knn_device(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_cnt));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
+        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
+        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_knn_self(pcp_index *ix, int k, int mem, int32_t *idx, float *dist, int32_t *count) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_knn_self: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_knn_self: mem must be PCP_HOST or PCP_DEVICE");
+    PCP_TRY(check_k(k));
+    const int64_t nq = ix->n;
+    if (nq == 0) return PCP_OK;
+    if (!idx || !dist) return fail(PCP_ERR_INVALID, "pcp_knn_self: idx/dist is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    int32_t *d_idx = idx, *d_cnt = count;
+    float *d_dist = dist;
+    const size_t nres = (size_t)nq * (size_t)k;
+    if (mem == PCP_HOST) {
+        PCP_TRY(ctx->scratch[7].ensure(nres * 8 + sizeof(int32_t) * (size_t)nq));
+        d_idx = ctx->scratch[7].as<int32_t>();
+        d_dist = reinterpret_cast<float *>(d_idx + nres);
+        d_cnt = reinterpret_cast<int32_t *>(d_dist + nres);
+    }
+    PCP_TRY(knn_self_device(ix, k, d_idx, d_dist, d_cnt));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
+        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
+        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- radius
+
+int pcp_radius_count(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, float radius, int mem,
+                     int64_t *offsets) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_radius_count: index is NULL");
+    PCP_TRY(check_cloud("pcp_radius_count", queries, nq, stride, mem));
+    if (!offsets) return fail(PCP_ERR_INVALID, "pcp_radius_count: offsets is NULL");
+    if (std::isnan(radius)) return fail(PCP_ERR_INVALID, "pcp_radius_count: radius is NaN");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const float *d_q = queries;
+    int64_t *d_off = offsets;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        d_q = ctx->scratch[6].as<float>();
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(int64_t) * (size_t)(nq + 1)));
+        d_off = ctx->scratch[7].as<int64_t>();
+    }
+    PCP_TRY(radius_count_device(ix, d_q, nq, stride, radius, d_off));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, offsets, d_off, sizeof(int64_t) * (size_t)(nq + 1)));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_radius_fill(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, float radius, int mem,
+                    const int64_t *offsets, int32_t *idx, float *dist, int sorted) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_radius_fill: index is NULL");
+    PCP_TRY(check_cloud("pcp_radius_fill", queries, nq, stride, mem));
+    if (!offsets) return fail(PCP_ERR_INVALID, "pcp_radius_fill: offsets is NULL");
+    if (std::isnan(radius)) return fail(PCP_ERR_INVALID, "pcp_radius_fill: radius is NaN");
+    if (nq == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    if (mem == PCP_DEVICE) return radius_fill_device(ix, queries, nq, stride, radius, offsets, idx, dist, sorted);
+    const int64_t m = offsets[nq];
+    if (m < 0) return fail(PCP_ERR_INVALID, "pcp_radius_fill: offsets[nq] is negative");
+    if (m > 0 && (!idx || !dist)) return fail(PCP_ERR_INVALID, "pcp_radius_fill: idx/dist is NULL");
+    PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+    PCP_TRY(upload(ctx, 2, ctx->scratch[7], offsets, sizeof(int64_t) * (size_t)(nq + 1)));
+    PCP_TRY(ctx->scratch[2].ensure((size_t)m * 8 + 16));
+    int32_t *d_idx = ctx->scratch[2].as<int32_t>();
+    float *d_dist = reinterpret_cast<float *>(d_idx + m);
+    PCP_TRY(radius_fill_device(ix, ctx->scratch[6].as<float>(), nq, stride, radius, ctx->scratch[7].as<int64_t>(),
+                               d_idx, d_dist, sorted));
+    PCP_TRY(download(ctx, idx, d_idx, (size_t)m * 4));
+    PCP_TRY(download(ctx, dist, d_dist, (size_t)m * 4));
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+}  // extern "C"

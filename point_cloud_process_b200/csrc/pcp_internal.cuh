@@ -1,0 +1,119 @@
+// Internal declarations shared by the CUDA translation units of libpcp_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "pcp.h"
+
+namespace pcp {
+
+// ------------------------------------------------------------------------------------------------
+// errors
+void set_error(const std::string &msg);
+int fail(int code, const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+#define PCP_CUDA(expr)                                                        \
+    do {                                                                      \
+        cudaError_t _e = (expr);                                              \
+        if (_e != cudaSuccess) return ::pcp::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define PCP_TRY(expr)            \
+    do {                         \
+        int _s = (expr);         \
+        if (_s != PCP_OK) return _s; \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// grow-only device / pinned-host buffers: steady-state calls never hit cudaMalloc
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes);
+    void release();
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct PinBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes);
+    void release();
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+constexpr int kLeaf = 32;          // points per bucket == warp width
+constexpr int kFan = 32;           // children per hierarchy node == warp width
+constexpr int kMaxLevels = 8;      // 32^7 buckets > 2^31 points
+
+}  // namespace pcp
+
+struct pcp_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    int64_t launches = 0;
+    pcp::DevBuf cub_tmp;           // CUB temporary storage
+    pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
+    pcp::PinBuf pin[4];            // pinned staging for host<->device copies
+    pcp::DevBuf counters;          // 8 x u64 work counters (pcp_ctx_enable_counters)
+    bool count_work = false;
+    unsigned long long *ctr() const { return count_work ? counters.as<unsigned long long>() : nullptr; }
+};
+
+// Device layout of the search structure ("bucket hierarchy"):
+//   pts      float4[n_leaf*32]  Morton-sorted points, .w = original index bits; pad lanes are NaN / -1
+//   box_lo/hi float4[total_nodes] AABB per node, level 0 (buckets) first, then level 1 ... root last
+//   level_off[l] first node of level l in box_*; level_cnt[l] nodes on level l
+struct pcp_index {
+    pcp_ctx *ctx = nullptr;
+    int64_t n = 0;
+    int64_t n_leaf = 0;
+    int n_levels = 0;                      // number of levels incl. the bucket level; root = level n_levels-1
+    int64_t level_off[pcp::kMaxLevels] = {0};
+    int64_t level_cnt[pcp::kMaxLevels] = {0};
+    pcp::DevBuf pts, box_lo, box_hi, bbox; // bbox: 8 floats (lo xyz, hi xyz, scale, pad) on device
+    pcp::DevBuf keys_a, keys_b, vals_a, vals_b, src_copy;
+};
+
+namespace pcp {
+
+struct IndexView {
+    const float4 *pts;
+    const float4 *box_lo;
+    const float4 *box_hi;
+    const float *bbox;      // lo.xyz, inv cell size
+    long long n;
+    long long n_leaf;
+    int n_levels;
+    long long level_off[kMaxLevels];
+    long long level_cnt[kMaxLevels];
+};
+IndexView make_view(const pcp_index *ix);
+
+// build (pcp_build.cu)
+int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride);
+// Morton keys of arbitrary query points in the index's frame, sorted: writes perm (nq) to d_perm
+int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm);
+
+// search (pcp_knn.cu / pcp_radius.cu); all pointers are device pointers
+int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
+               int32_t *d_idx, float *d_dist, int32_t *d_count);
+int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count);
+int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
+                        int64_t *d_offsets);
+int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
+                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted);
+
+// icp (pcp_icp.cu)
+int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, const float *d_src,
+                     const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,
+                     const double *h_T_init, double *h_T_last, double *h_T_total, int32_t *h_iters,
+                     int32_t *h_status, double *h_log);
+
+}  // namespace pcp

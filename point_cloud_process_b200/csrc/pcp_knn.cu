@@ -1,0 +1,256 @@
+// Exact kNN over the bucket hierarchy -- one warp per query.
+// Replaces kdtree_knn_search (kdtree.py:141-172), octree_knn_search (octree.py:262-306) and
+// KNNResultSet.add_point (result_set.py:35-53).
+//
+// The warp owns ONE query.  Its result list is the warp itself: lane i holds the i-th best packed
+// (distance, index) key, so the list is a 32-entry sorted register file distributed over the lanes
+// and every k <= 32 is served by the same code.  The warp walks the 32-ary AABB hierarchy
+// nearest-first: on every node lane j evaluates the exact lower bound of child j (two coalesced
+// float4 loads), a redux.min picks the nearest unvisited child, and the walk of a node stops as
+// soon as that bound exceeds the current k-th distance gate.  A bucket is scanned with one
+// coalesced 512-byte load (lane j = point j), the distance is the reference's unfused float32
+// expression, and the few candidates inside the gate are inserted with ballot + shfl_up.  The first
+// bucket is bitonic-sorted straight into the list.
+#include <cfloat>
+
+#include "pcp_device.cuh"
+#include "pcp_internal.cuh"
+
+namespace pcp {
+
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+constexpr unsigned kDone = 0xffffffffu;   // "child visited / absent" marker (> every float bit pattern in use)
+
+__device__ __forceinline__ unsigned long long shfl64(unsigned long long v, int src) {
+    return __shfl_sync(kFullMask, v, src);
+}
+
+// Ascending bitonic sort of one 64-bit key per lane across the warp.
+__device__ __forceinline__ unsigned long long warp_sort32(unsigned long long key, int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(kFullMask, key, stride);
+            const bool up = ((lane & size) == 0) || size == 32;      // final merge is ascending everywhere
+            const bool lower = (lane & stride) == 0;
+            const bool take_min = (up == lower);
+            const unsigned long long mn = key < other ? key : other;
+            const unsigned long long mx = key < other ? other : key;
+            key = take_min ? mn : mx;
+        }
+    }
+    return key;
+}
+
+// Ascending sort of a BITONIC sequence held one key per lane (5 compare-exchange stages).
+__device__ __forceinline__ unsigned long long warp_merge32(unsigned long long key, int lane) {
+#pragma unroll
+    for (int stride = 16; stride > 0; stride >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(kFullMask, key, stride);
+        const bool lower = (lane & stride) == 0;
+        const unsigned long long mn = key < other ? key : other;
+        const unsigned long long mx = key < other ? other : key;
+        key = lower ? mn : mx;
+    }
+    return key;
+}
+
+constexpr int kMergeThreshold = 10;   // survivors per bucket above which sort+merge beats serial insertion
+
+struct QueryState {
+    float qx, qy, qz;
+    float gate;                 // squared-distance gate: d2_gate of the current k-th distance (+inf until k found)
+    unsigned long long key;     // this lane's slot of the sorted 32-entry list
+    bool first;                 // no bucket scanned yet
+    unsigned n_test, n_scan, n_ins, n_open;
+};
+
+__device__ __forceinline__ void scan_bucket(QueryState &st, const IndexView &ix, long long leaf, int lane, int k) {
+    ++st.n_scan;
+    const float4 p = __ldg(ix.pts + leaf * kLeaf + lane);
+    const float d2 = ref_d2(st.qx, st.qy, st.qz, p.x, p.y, p.z);
+    if (st.first) {
+        // pad points (NaN coordinates) sort to the end as empty keys
+        const unsigned long long nk = (d2 == d2) ? pack_key(__fsqrt_rn(d2), __float_as_uint(p.w)) : kEmptyKey;
+        st.key = warp_sort32(nk, lane);
+        st.first = false;
+    } else {
+        const bool pass = d2 <= st.gate;                                 // NaN never passes
+        unsigned m = __ballot_sync(kFullMask, pass);
+        const unsigned long long mine = pack_key(__fsqrt_rn(d2), __float_as_uint(p.w));
+        if (__popc(m) > kMergeThreshold) {
+            // many survivors: sort them and bitonic-merge with the list (cost independent of the count)
+            const unsigned long long sorted_new = warp_sort32(pass ? mine : kEmptyKey, lane);
+            const unsigned long long rev = shfl64(sorted_new, 31 - lane);
+            st.key = warp_merge32(st.key < rev ? st.key : rev, lane);    // 32 smallest of the 64, bitonic -> sorted
+            st.n_ins += kMergeThreshold;
+        } else {
+            while (m) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const unsigned long long nk = shfl64(mine, j);
+                const bool gt = st.key > nk;                             // a suffix of the lanes
+                const unsigned bal = __ballot_sync(kFullMask, gt);
+                const unsigned long long up = __shfl_up_sync(kFullMask, st.key, 1);
+                const int pos = __ffs(bal) - 1;                          // -1: nk is larger than all 32 -> dropped
+                st.key = gt ? (lane == pos ? nk : up) : st.key;
+                ++st.n_ins;
+            }
+        }
+    }
+    st.gate = d2_gate(key_dist(shfl64(st.key, k - 1)));
+}
+
+template <bool SELF>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, int k,
+                int *__restrict__ out_idx, float *__restrict__ out_dist, int *__restrict__ out_cnt,
+                unsigned long long *__restrict__ ctr) {
+    // per-level traversal state: lane j keeps the pending lower bound of child j of the open node
+    __shared__ unsigned s_lb[kWarpsPerCta][kMaxLevels][32];
+    __shared__ unsigned s_cd[kWarpsPerCta][kMaxLevels][32];   // squared distance to the child's box centre
+    __shared__ unsigned s_node[kWarpsPerCta][kMaxLevels];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long wid = blockIdx.x * (long long)kWarpsPerCta + warp;
+    const long long n_work = SELF ? ix.n_leaf * kLeaf : nq;
+    if (wid >= n_work) return;
+
+    QueryState st;
+    long long qid = wid;
+    if (SELF) {
+        const float4 p = __ldg(ix.pts + wid);
+        st.qx = p.x; st.qy = p.y; st.qz = p.z;
+        qid = (long long)(int)__float_as_uint(p.w);
+        if (qid < 0) return;                       // pad slot of the last bucket (whole warp exits)
+    } else {
+        const float *q = queries + wid * stride;
+        st.qx = __ldg(q); st.qy = __ldg(q + 1); st.qz = __ldg(q + 2);
+    }
+    st.gate = __int_as_float(0x7f800000);
+    st.key = kEmptyKey;
+    st.first = true;
+    st.n_test = st.n_scan = st.n_ins = st.n_open = 0;
+
+    const int top = ix.n_levels - 1;
+    if (top == 0) {
+        scan_bucket(st, ix, 0, lane, k);
+    } else if (top > 0) {
+        unsigned(*lbs)[32] = s_lb[warp];
+        unsigned(*cds)[32] = s_cd[warp];
+        unsigned *nodes = s_node[warp];
+        // children of `node` (a level-`lv` node) live on level lv-1
+        auto open_node = [&](int lv, unsigned node) {
+            ++st.n_open;
+            if (lane == 0) nodes[lv] = node;
+            const long long c = (long long)node * kFan + lane;
+            unsigned bits = kDone, cbits = kDone;
+            if (c < ix.level_cnt[lv - 1]) {
+                const long long b = ix.level_off[lv - 1] + c;
+                const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
+                bits = __float_as_uint(box_lb2(st.qx, st.qy, st.qz, lo, hi));
+                const float cx = 0.5f * (lo.x + hi.x) - st.qx, cy = 0.5f * (lo.y + hi.y) - st.qy,
+                            cz = 0.5f * (lo.z + hi.z) - st.qz;
+                cbits = __float_as_uint(cx * cx + cy * cy + cz * cz);   // ordering hint only, never used to prune
+            }
+            lbs[lv][lane] = bits;
+            cds[lv][lane] = cbits;
+            __syncwarp();
+        };
+        int level = top;
+        open_node(top, 0u);
+        while (true) {
+            const unsigned mine = lbs[level][lane];
+            const unsigned best = __reduce_min_sync(kFullMask, mine);
+            // exact prune: every point below a child is at least `best` away (in d2 arithmetic)
+            if (best == kDone || !(__uint_as_float(best) <= st.gate)) {
+                if (level == top) break;
+                ++level;
+                continue;
+            }
+            unsigned tie = __ballot_sync(kFullMask, mine == best);
+            if (tie & (tie - 1)) {   // several children at the same bound (typically 0: the query is inside them)
+                const unsigned cd = (mine == best) ? cds[level][lane] : kDone;
+                const unsigned cbest = __reduce_min_sync(kFullMask, cd);
+                tie = __ballot_sync(kFullMask, cd == cbest);
+            }
+            const int sel = __ffs(tie) - 1;
+            if (lane == sel) lbs[level][lane] = kDone;
+            const unsigned child = nodes[level] * kFan + sel;
+            ++st.n_test;
+            if (level == 1) {
+                scan_bucket(st, ix, child, lane, k);
+            } else {
+                --level;
+                open_node(level, child);
+            }
+        }
+    }
+
+    if (ctr && lane == 0) {
+        atomicAdd(ctr + 0, (unsigned long long)st.n_scan * kLeaf);
+        atomicAdd(ctr + 1, (unsigned long long)st.n_open * kFan);
+        atomicAdd(ctr + 2, (unsigned long long)st.n_open);
+        atomicAdd(ctr + 3, (unsigned long long)st.n_ins);
+        atomicAdd(ctr + 4, 1ull);
+        atomicAdd(ctr + 5, (unsigned long long)st.n_scan);
+    }
+    // lane i < k writes slot i: one coalesced row per query
+    const unsigned id = key_index(st.key);
+    const bool filled = id != 0xffffffffu;
+    if (lane < k) {
+        // result_set.py:19-22: unfilled slots read (1e10, 0)
+        out_idx[qid * k + lane] = filled ? (int)id : 0;
+        out_dist[qid * k + lane] = filled ? key_dist(st.key) : PCP_KNN_EMPTY_DIST;
+    }
+    if (out_cnt) {
+        const int cnt = __popc(__ballot_sync(kFullMask, filled && lane < k));
+        if (lane == 0) out_cnt[qid] = cnt;
+    }
+}
+
+__global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, int *cnt) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < nq * k) { idx[i] = 0; dist[i] = PCP_KNN_EMPTY_DIST; }
+    if (cnt && i < nq) cnt[i] = 0;
+}
+
+}  // namespace
+
+int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
+               int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    (void)d_perm;
+    if (nq == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    if (ix->n == 0) {   // empty cloud: every KNNResultSet stays as constructed
+        long long tot = std::max<long long>(nq * k, nq);
+        fill_empty_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, ctx->stream>>>(nq, k, d_idx, d_dist, d_count);
+        ctx->launches += 1;
+        PCP_CUDA(cudaGetLastError());
+        return PCP_OK;
+    }
+    const IndexView v = make_view(ix);
+    const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
+    knn_warp_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist, d_count,
+                                                                        ctx->ctr());
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
+int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (ix->n == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    const IndexView v = make_view(ix);
+    const long long n_work = ix->n_leaf * kLeaf;
+    const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
+    knn_warp_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist, d_count,
+                                                                       ctx->ctr());
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
+}  // namespace pcp

@@ -1,0 +1,203 @@
+// Exact fixed-radius search over the bucket hierarchy, CSR output.
+// Replaces kdtree_radius_search (kdtree.py:176-208), octree_radius_search(_fast) (octree.py:166-259)
+// and RadiusNNResultSet.add_point (result_set.py:78-84: keep iff NOT dist > radius).
+//
+// One warp = one query.  Lane j tests child j of the current hierarchy node (coalesced AABB loads),
+// surviving internal nodes go on a small per-warp stack, surviving buckets are scanned with one
+// coalesced 512-byte load (lane j = point j).  Hits are compacted with ballot + popc, so the fill
+// pass writes each query's CSR segment with contiguous, coalesced stores -- the C1 workload emits
+// 80 M (index, distance) pairs = 642 MB and is output-bandwidth bound.
+//
+// The float32 test `sqrtf(d2) <= r` of the reference is evaluated as `d2 <= d2max` where d2max is the
+// LARGEST float whose correctly rounded square root is <= r (computed on the host, exact because
+// fl(sqrt(.)) is monotone).
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_segmented_sort.cuh>
+
+#include <cmath>
+
+#include "pcp_device.cuh"
+#include "pcp_internal.cuh"
+
+namespace pcp {
+
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kStack = kMaxLevels * kFan;
+
+// Largest float x with sqrtf(x) <= r (r >= 0, finite).  Returns -1 for r < 0 (nothing matches).
+float exact_d2_threshold(float r) {
+    if (!(r >= 0.f)) return -1.f;
+    if (std::isinf(r)) return r;
+    float x = r * r;
+    if (std::isinf(x)) x = 3.402823466e38f;
+    while (sqrtf(x) > r) x = nextafterf(x, -1.f);
+    while (true) {
+        float y = nextafterf(x, INFINITY);
+        if (std::isinf(y) || sqrtf(y) > r) break;
+        x = y;
+    }
+    return x;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+radius_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, float d2max,
+              long long *__restrict__ counts, const long long *__restrict__ offsets, int *__restrict__ out_idx,
+              float *__restrict__ out_dist, unsigned long long *__restrict__ ctr) {
+    __shared__ unsigned s_stack[kWarpsPerCta][kStack];   // entries: (level << 27) | node   (level >= 1)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long qi = blockIdx.x * (long long)kWarpsPerCta + warp;
+    if (qi >= nq) return;
+    const float *q = queries + qi * stride;
+    const float qx = __ldg(q), qy = __ldg(q + 1), qz = __ldg(q + 2);
+    unsigned *stack = s_stack[warp];
+    long long total = 0;
+    long long base = FILL ? offsets[qi] : 0;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    unsigned n_scan = 0, n_open = 0;
+
+    auto scan_bucket = [&](long long leaf) {
+        ++n_scan;
+        const float4 p = __ldg(ix.pts + leaf * kLeaf + lane);
+        const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
+        const bool hit = d2 <= d2max;                       // NaN pads never hit
+        const unsigned m = __ballot_sync(kFullMask, hit);
+        if (FILL && hit) {
+            const long long o = base + total + __popc(m & lt_mask);
+            out_idx[o] = (int)__float_as_uint(p.w);
+            out_dist[o] = __fsqrt_rn(d2);
+        }
+        total += __popc(m);
+    };
+
+    const int top = ix.n_levels - 1;
+    if (top == 0) {
+        scan_bucket(0);
+    } else if (top > 0) {
+        int sp = 0;
+        if (lane == 0) stack[0] = ((unsigned)top << 27);
+        sp = 1;
+        __syncwarp();
+        while (sp > 0) {
+            const unsigned e = stack[sp - 1];
+            --sp;
+            __syncwarp();
+            ++n_open;
+            const int lv = (int)(e >> 27);
+            const unsigned node = e & 0x07ffffffu;
+            const long long c = (long long)node * kFan + lane;
+            bool hit = false;
+            if (c < ix.level_cnt[lv - 1]) {
+                const long long b = ix.level_off[lv - 1] + c;
+                hit = box_lb2(qx, qy, qz, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)) <= d2max;
+            }
+            unsigned m = __ballot_sync(kFullMask, hit);
+            if (lv == 1) {
+                while (m) {
+                    const int j = __ffs(m) - 1;
+                    m &= m - 1;
+                    scan_bucket((long long)node * kFan + j);
+                }
+            } else {
+                if (hit) stack[sp + __popc(m & lt_mask)] = ((unsigned)(lv - 1) << 27) | (unsigned)c;
+                sp += __popc(m);
+                __syncwarp();
+            }
+        }
+    }
+    if (!FILL && lane == 0) counts[qi] = total;
+    if (ctr && lane == 0) {
+        atomicAdd(ctr + 0, (unsigned long long)n_scan * kLeaf);
+        atomicAdd(ctr + 1, (unsigned long long)n_open * kFan);
+        atomicAdd(ctr + 2, (unsigned long long)n_open);
+        atomicAdd(ctr + 4, 1ull);
+        atomicAdd(ctr + 5, (unsigned long long)n_scan);
+    }
+}
+
+// counts (nq) -> offsets (nq+1) with offsets[0] = 0
+__global__ void set_zero_kernel(long long *p) { *p = 0; }
+
+}  // namespace
+
+int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
+                        int64_t *d_offsets) {
+    pcp_ctx *ctx = ix->ctx;
+    set_zero_kernel<<<1, 1, 0, ctx->stream>>>(reinterpret_cast<long long *>(d_offsets));
+    ctx->launches += 1;
+    if (nq == 0) { PCP_CUDA(cudaGetLastError()); return PCP_OK; }
+    PCP_TRY(ctx->scratch[3].ensure(sizeof(long long) * (size_t)nq));
+    long long *counts = ctx->scratch[3].as<long long>();
+    if (ix->n == 0) {
+        PCP_CUDA(cudaMemsetAsync(d_offsets, 0, sizeof(int64_t) * (size_t)(nq + 1), ctx->stream));
+        return PCP_OK;
+    }
+    const float d2max = exact_d2_threshold(radius);
+    const IndexView v = make_view(ix);
+    const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
+    radius_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
+                                                                     nullptr, nullptr, ctx->ctr());
+    ctx->launches += 1;
+    size_t tmp = 0;
+    PCP_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp, counts, reinterpret_cast<long long *>(d_offsets) + 1, nq,
+                                           ctx->stream));
+    PCP_TRY(ctx->cub_tmp.ensure(tmp));
+    PCP_CUDA(cub::DeviceScan::InclusiveSum(ctx->cub_tmp.p, tmp, counts, reinterpret_cast<long long *>(d_offsets) + 1,
+                                           nq, ctx->stream));
+    ctx->launches += 2;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
+namespace {
+
+__global__ void __launch_bounds__(256) pack_pairs_kernel(const int *__restrict__ idx, const float *__restrict__ dist,
+                                                         long long m, unsigned long long *__restrict__ keys) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < m) keys[i] = pack_key(dist[i], (unsigned)idx[i]);
+}
+
+__global__ void __launch_bounds__(256) unpack_pairs_kernel(const unsigned long long *__restrict__ keys, long long m,
+                                                           int *__restrict__ idx, float *__restrict__ dist) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < m) { idx[i] = (int)key_index(keys[i]); dist[i] = key_dist(keys[i]); }
+}
+
+}  // namespace
+
+int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
+                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted) {
+    pcp_ctx *ctx = ix->ctx;
+    if (nq == 0 || ix->n == 0) return PCP_OK;
+    const float d2max = exact_d2_threshold(radius);
+    const IndexView v = make_view(ix);
+    const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
+    radius_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
+        v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr());
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    if (!sorted) return PCP_OK;
+    // ascending (distance, index) inside every CSR segment: what RadiusNNResultSet.__str__ prints
+    long long m = 0;
+    PCP_CUDA(cudaMemcpyAsync(&m, d_offsets + nq, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (m == 0) return PCP_OK;
+    PCP_TRY(ctx->scratch[4].ensure(sizeof(unsigned long long) * (size_t)m));
+    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned long long) * (size_t)m));
+    unsigned long long *ka = ctx->scratch[4].as<unsigned long long>(), *kb = ctx->scratch[5].as<unsigned long long>();
+    const unsigned g2 = (unsigned)((m + 255) / 256);
+    pack_pairs_kernel<<<g2, 256, 0, ctx->stream>>>(d_idx, d_dist, m, ka);
+    const long long *offs = reinterpret_cast<const long long *>(d_offsets);
+    size_t tmp = 0;
+    PCP_CUDA(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp, ka, kb, m, nq, offs, offs + 1, ctx->stream));
+    PCP_TRY(ctx->cub_tmp.ensure(tmp));
+    PCP_CUDA(cub::DeviceSegmentedSort::SortKeys(ctx->cub_tmp.p, tmp, ka, kb, m, nq, offs, offs + 1, ctx->stream));
+    unpack_pairs_kernel<<<g2, 256, 0, ctx->stream>>>(kb, m, d_idx, d_dist);
+    ctx->launches += 5;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
+}  // namespace pcp
