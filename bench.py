@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native nearest-neighbour + ICP hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference]
+
+Headline workload (BASELINE.json `metric`): kNN queries/s, k=8, on the bundled KITTI scan
+000000.bin (124 668 points, every point a query).  One STEP = one pass of the hot path over one
+scan: index build (bbox -> Morton keys -> radix sort -> bucket gather -> AABB hierarchy) followed
+by the batched exact kNN search.  `value` = queries of all ranks / device time of the K steps
+(CUDA events on the library's stream, max over ranks), inputs resident in HBM, L2 flushed
+between steps.  `e2e` = the same step through the public API (pybind11 -> C ABI, PCP_HOST mode)
+with pinned HOST buffers: H2D of the scan and the queries and D2H of indices/distances/counts
+are inside the timed region.  N > 1: one process per GPU, every rank indexes and searches its own
+scan (independent LiDAR frames; no data-path collective) -> "weak" scaling.
+
+Other workloads (parity-test configs, selectable for profiling): uniform1m_knn16 (C3),
+kitti_radius (C1 radius r=1.0), icp_pairs (C4, pairs sharded across ranks).
+
+--impl reference: the CPU arm -- oracle/knn_oracle.c (a C restatement of the reference's kd-tree,
+which itself is pure Python and cannot travel to the GPU box) on all host threads.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+KITTI = os.path.join(ROOT, "tests", "golden", "kitti_000000_xyz.f32")
+SM_COUNT_B200 = 148
+FP32_LANES_PER_SM = 128
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def scan_for_rank(rank):
+    """Rank 0: the bundled scan.  Rank r > 0: an independent frame derived from it (seeded 5 mm
+    jitter + a yaw of 7 degrees * r), so that no two ranks do identical work."""
+    pts = np.fromfile(KITTI, np.float32).reshape(-1, 3)
+    if rank == 0:
+        return pts
+    rng = np.random.default_rng(9000 + rank)
+    a = np.deg2rad(7.0 * rank)
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+    return (pts.astype(np.float64) @ R.T + rng.normal(0, 0.005, pts.shape)).astype(np.float32)
+
+
+def make_workload(name, rank):
+    if name == "kitti_knn8":
+        return dict(pts=scan_for_rank(rank), k=8, desc="KITTI 000000.bin 124668 pts, k=8, queries = all points")
+    if name == "uniform1m_knn16":
+        rng = np.random.default_rng(1234 + rank)
+        return dict(pts=(rng.random((1_000_000, 3)) * 25.4).astype(np.float32), k=16,
+                    desc="uniform 1M pts in [0,25.4)^3, k=16, queries = all points")
+    raise SystemExit(f"unknown workload {name}")
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:   # noqa: BLE001
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:   # noqa: BLE001
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:   # noqa: BLE001
+                pass
+            time.sleep(0.002)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=1.0)
+        return {"sm_mhz": (statistics.median(self.samples) if self.samples else None),
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_port_run(pts, k, threads, min_seconds, max_reps=50):
+    """oracle port: kd-tree build + kNN over ALL queries of the scan, repeated for >= min_seconds."""
+    from oracle import knn_oracle
+    reps, t_build, t_search = 0, 0.0, 0.0
+    t_start = time.perf_counter()
+    while True:
+        t0 = time.perf_counter()
+        kd = knn_oracle.KdTree(pts, 32)
+        t1 = time.perf_counter()
+        kd.knn(pts, k, threads=threads)
+        t2 = time.perf_counter()
+        t_build += t1 - t0
+        t_search += t2 - t1
+        reps += 1
+        if time.perf_counter() - t_start >= min_seconds or reps >= max_reps:
+            break
+    return reps, t_build / reps, t_search / reps
+
+
+def run_reference(args):
+    """CPU arm: the reference's algorithm (kd-tree, leaf_size 32, KNNResultSet) as restated in
+    oracle/knn_oracle.c, all host threads; each step = build + kNN over the whole scan."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = make_workload(args.workload, 0)
+    pts, k = w["pts"], w["k"]
+    threads = os.cpu_count() or 1
+    from oracle import knn_oracle
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        kd = knn_oracle.KdTree(pts, 32)
+        kd.knn(pts, k, threads=threads)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = len(pts) * len(times) / total
+    line = {
+        "impl": "reference", "metric": "kNN queries/s", "value": value, "unit": "queries/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "KITTI scan bundled with the reference (tests/golden copy)",
+        "config": {"workload": args.workload, "desc": w["desc"], "step": "kd-tree build (leaf 32) + kNN of every point"},
+        "cpu_baseline": {"value": value, "unit": "queries/s", "cores": threads, "kind": "port",
+                         "sample": f"whole scan ({len(pts)} queries) per step, {len(times)} steps; C restatement of "
+                                   "kdtree.py/result_set.py (the reference itself is pure Python: ~830 queries/s/core)"},
+        "e2e": {"value": value, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="kitti_knn8")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import point_cloud_process_b200 as pcp
+    native = pcp.native
+    peaks, peaks_kind = load_peaks()
+
+    w = make_workload(args.workload, rank)
+    pts, k = w["pts"], w["k"]
+    n = len(pts)
+    ctx = native.Context(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.stream())
+    d_pts = torch.from_numpy(pts).cuda()
+    idx = torch.empty((n, k), dtype=torch.int32, device="cuda")
+    dst = torch.empty((n, k), dtype=torch.float32, device="cuda")
+    cnt = torch.empty(n, dtype=torch.int32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # 2x the 126 MB L2
+    torch.cuda.synchronize()
+    ix = native.Index(ctx, d_pts.data_ptr(), n, 3)
+
+    def step(e0=None, e1=None, e2=None):
+        if e0 is not None:
+            with torch.cuda.stream(stream):
+                flush.zero_()                       # untimed: evicts the previous step's lines from L2
+            e0.record(stream)
+        ix.rebuild_device(d_pts.data_ptr(), n, 3)
+        if e1 is not None:
+            e1.record(stream)
+        ix.knn_device(d_pts.data_ptr(), n, 3, k, idx.data_ptr(), dst.data_ptr(), cnt.data_ptr())
+        if e2 is not None:
+            e2.record(stream)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    ctx.synchronize()
+    K = args.steps
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    sampler = ClockSampler(local_rank)
+    barrier()
+    launches0 = ctx.launch_count()
+    sampler.start()
+    t_wall0 = time.perf_counter()
+    for i in range(K):
+        step(*evs[i])
+    ctx.synchronize()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.result()
+    launches = ctx.launch_count() - launches0
+    step_ms = [e[0].elapsed_time(e[2]) for e in evs]
+    build_ms = [e[0].elapsed_time(e[1]) for e in evs]
+    knn_ms = [e[1].elapsed_time(e[2]) for e in evs]
+    total_ms = sum(step_ms)
+    if dist is not None:
+        t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    value = world * n * K / (total_ms * 1e-3)
+
+    # ---- work counters (untimed pass): distance evaluations C of the kNN kernel
+    ctx.enable_counters(True)
+    ix.knn_device(d_pts.data_ptr(), n, 3, k, idx.data_ptr(), dst.data_ptr(), cnt.data_ptr())
+    ctrs = ctx.read_counters()
+    ctx.enable_counters(False)
+    evals = int(ctrs[0])
+    knn_s = statistics.mean(knn_ms) * 1e-3
+    sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    fp32_peak = sm_count * FP32_LANES_PER_SM * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12   # T unfused FP32 op/s
+    achieved = 8.0 * evals / knn_s / 1e12
+    hbm_bytes = 16 * n + 12 * n + 8 * k * n + 4 * n
+    roofline = {
+        "bound": "fp32", "kernel": "knn", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s (unfused FP32 ops; 8 per distance evaluation)",
+        "frac": achieved / fp32_peak, "traffic": None,
+        "peak_source": f"{sm_count} SMs x 128 FP32 lanes x sm_max_mhz ({peaks_kind} MEASURED_PEAKS.json clock); no FP32 peak is measured by the driver",
+        "distance_evaluations_per_launch": evals, "evals_per_query": evals / n, "kernel_ms": knn_s * 1e3,
+        "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / knn_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
+                "frac": hbm_bytes / knn_s / 1e9 / peaks.get("hbm_gbs", 6533.8)},
+    }
+
+    # ---- end to end through the public API with pinned host buffers (H2D + D2H inside)
+    h_pts = torch.from_numpy(pts).pin_memory()
+    h_np = h_pts.numpy()
+    six = pcp.SearchIndex.__new__(pcp.SearchIndex)
+    six.ctx, six.db = ctx, h_np
+    six._ix = native.Index(ctx, h_np)
+    for _ in range(3):
+        six._ix.rebuild(h_np)
+        six.knn(h_np, k)
+    barrier()
+    Ke = max(5, min(K, 30))
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        six._ix.rebuild(h_np)                      # H2D of the scan + build
+        r_idx, r_dist, r_cnt = six.knn(h_np, k)    # H2D of the queries, search, D2H of the results
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    e2e = {"value": world * n * Ke / t_e2e, "unit": "queries/s", "h2d_bytes_per_step": 2 * n * 12,
+           "d2h_bytes_per_step": n * k * 8 + n * 4, "steps": Ke, "ms_per_step": 1e3 * t_e2e / Ke,
+           "timer": "host perf_counter around synchronous C-ABI calls (PCP_HOST mode)"}
+
+    line = {
+        "metric": "kNN queries/s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "KITTI scan bundled with the reference (tests/golden copy)" if args.workload.startswith("kitti") else "synthetic",
+        "config": {"workload": args.workload, "desc": w["desc"], "step": "index build + kNN of every point",
+                   "l2": "flushed between timed steps (256 MB write)", "multi_gpu": "one independent scan per rank, no collective"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "breakdown_ms": {"build": statistics.mean(build_ms), "knn": statistics.mean(knn_ms),
+                         "step_median": statistics.median(step_ms), "wall_region_ms_per_step": 1e3 * t_wall / K},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        reps, tb, ts = cpu_port_run(pts, k, threads, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": n / (tb + ts), "unit": "queries/s", "cores": threads, "kind": "port",
+                                "sample": f"whole scan ({n} queries), build+search, mean of {reps} repetitions "
+                                          f"(build {tb*1e3:.1f} ms, search {ts*1e3:.1f} ms)",
+                                "search_only_queries_per_s": n / ts}
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
