@@ -171,6 +171,13 @@ PCP_API int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_
                   const double *T_init, double *T_last, double *T_total, int32_t *iterations,
                   int32_t *status, double *diff_log);
 
+/* procrustes_transformation(A, B) -> (R, t, cost)               main.py:131-141, icp_template.py:43-54
+ * on GIVEN correspondences: A, B are 3 x n float64 row-major (one column per point, the reference's
+ * layout).  R: 9 row-major doubles = U V^T of the SVD of (B - mean)(A - mean)^T (no det fix, main.py:139);
+ * t: 3 doubles = mean(B - R A); cost = ||B - (R A + t 1^T)||_F (main.py:141).  Outputs are host memory. */
+PCP_API int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, int mem, double *R, double *t,
+                   double *cost);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

@@ -33,3 +33,4 @@ native = _load_native()
 __version__ = native.__version__
 
 from .api import SearchIndex, default_context, icp_batch   # noqa: E402,F401
+from . import result_set, kdtree, octree, icp   # noqa: E402,F401

@@ -5,6 +5,7 @@
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
+#include <algorithm>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -180,6 +181,92 @@ class Index {
     std::string msg_;
 };
 
+// icp_batch: packed clouds + offsets -> dict(T_last, T_total, iterations, status[, diff_log])
+py::dict icp_batch(std::shared_ptr<Context> ctx, const py::object &src, const i64_array &src_off, const py::object &tgt,
+                   const i64_array &tgt_off, const f64_array &T_init, int max_iteration, double R_diff_thres,
+                   double t_diff_thres, double dist_thres, bool first_iter_broadcast, bool want_log) {
+    Cloud s(src, "source"), t(tgt, "target");
+    if (s.stride != t.stride) throw py::value_error("source and target must have the same number of columns");
+    const int64_t P = src_off.size() - 1;
+    if (P < 0 || tgt_off.size() != src_off.size()) throw py::value_error("offset arrays must both have n_pairs+1 entries");
+    if (T_init.size() != P * 16) throw py::value_error("T_init must be (n_pairs, 4, 4)");
+    if (P > 0 && (src_off.data()[P] != s.n || tgt_off.data()[P] != t.n))
+        throw py::value_error("offsets do not match the packed clouds");
+    pcp_icp_params prm;
+    pcp_icp_default_params(&prm);
+    prm.max_iteration = max_iteration;
+    prm.R_diff_thres = R_diff_thres;
+    prm.t_diff_thres = t_diff_thres;
+    prm.dist_thres = dist_thres;
+    prm.first_iter_broadcast = first_iter_broadcast ? 1 : 0;
+    py::array_t<double> T_last({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4}), T_total({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4});
+    py::array_t<int32_t> iters((py::ssize_t)P), status((py::ssize_t)P);
+    py::array_t<double> log;
+    if (want_log) log = py::array_t<double>({(py::ssize_t)P, (py::ssize_t)std::max(max_iteration, 0), (py::ssize_t)2});
+    int rc;
+    std::string msg;
+    {
+        py::gil_scoped_release rel;
+        rc = pcp_icp_batch(ctx->get(), &prm, P, s.data(), src_off.data(), t.data(), tgt_off.data(), s.stride, PCP_HOST,
+                           T_init.data(), T_last.mutable_data(), T_total.mutable_data(), iters.mutable_data(),
+                           status.mutable_data(), want_log ? log.mutable_data() : nullptr);
+        if (rc != PCP_OK) msg = pcp_last_error();
+    }
+    if (rc == PCP_ERR_INVALID) throw py::value_error("pcp_icp_batch: " + msg);
+    if (rc != PCP_OK) throw std::runtime_error("pcp_icp_batch: " + msg);
+    py::dict out;
+    out["T_last"] = T_last;
+    out["T_total"] = T_total;
+    out["iterations"] = iters;
+    out["status"] = status;
+    if (want_log) out["diff_log"] = log;
+    return out;
+}
+
+// device-resident variant for benches: raw device pointers for the packed clouds
+py::dict icp_batch_device(std::shared_ptr<Context> ctx, uintptr_t src, const i64_array &src_off, uintptr_t tgt,
+                          const i64_array &tgt_off, int64_t stride, int max_iteration, double R_diff_thres,
+                          double t_diff_thres, double dist_thres, bool first_iter_broadcast) {
+    const int64_t P = src_off.size() - 1;
+    if (P < 0 || tgt_off.size() != src_off.size()) throw py::value_error("offset arrays must both have n_pairs+1 entries");
+    pcp_icp_params prm;
+    pcp_icp_default_params(&prm);
+    prm.max_iteration = max_iteration;
+    prm.R_diff_thres = R_diff_thres;
+    prm.t_diff_thres = t_diff_thres;
+    prm.dist_thres = dist_thres;
+    prm.first_iter_broadcast = first_iter_broadcast ? 1 : 0;
+    py::array_t<double> T_last({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4}), T_total({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4});
+    py::array_t<int32_t> iters((py::ssize_t)P), status((py::ssize_t)P);
+    check(pcp_icp_batch(ctx->get(), &prm, P, reinterpret_cast<const float *>(src), src_off.data(),
+                        reinterpret_cast<const float *>(tgt), tgt_off.data(), stride, PCP_DEVICE, nullptr,
+                        T_last.mutable_data(), T_total.mutable_data(), iters.mutable_data(), status.mutable_data(), nullptr),
+          "pcp_icp_batch");
+    py::dict out;
+    out["T_last"] = T_last;
+    out["T_total"] = T_total;
+    out["iterations"] = iters;
+    out["status"] = status;
+    return out;
+}
+
+py::tuple procrustes(std::shared_ptr<Context> ctx, const f64_array &A, const f64_array &B) {
+    if (A.ndim() != 2 || A.shape(0) != 3 || B.ndim() != 2 || B.shape(0) != 3 || A.shape(1) != B.shape(1) || A.shape(1) < 1)
+        throw py::value_error("procrustes: A and B must both be (3, N) with N >= 1");
+    py::array_t<double> R({(py::ssize_t)3, (py::ssize_t)3}), t({(py::ssize_t)3, (py::ssize_t)1});
+    double cost = 0.0;
+    check(pcp_procrustes(ctx->get(), A.data(), B.data(), A.shape(1), PCP_HOST, R.mutable_data(), t.mutable_data(), &cost),
+          "pcp_procrustes");
+    return py::make_tuple(R, t, cost);
+}
+
+py::array_t<double> homo2tq(const f64_array &homo) {
+    if (homo.size() != 16) throw py::value_error("homo2tq: expected a 4x4 matrix");
+    py::array_t<double> tq(7);
+    check(pcp_homo2tq(homo.data(), tq.mutable_data()), "pcp_homo2tq");
+    return tq;
+}
+
 }  // namespace
 
 PYBIND11_MODULE(_pcp, m) {
@@ -217,5 +304,13 @@ PYBIND11_MODULE(_pcp, m) {
         .def("radius", &Index::radius, py::arg("queries"), py::arg("radius"), py::arg("sorted") = false)
         .def("radius_count_device", &Index::radius_count_device)
         .def("radius_fill_device", &Index::radius_fill_device);
+
+    m.def("icp_batch", &icp_batch, py::arg("ctx"), py::arg("source"), py::arg("source_offsets"), py::arg("target"),
+          py::arg("target_offsets"), py::arg("T_init"), py::arg("max_iteration") = 100, py::arg("R_diff_thres") = 0.5,
+          py::arg("t_diff_thres") = 0.5, py::arg("dist_thres") = 5.0, py::arg("first_iter_broadcast") = true,
+          py::arg("want_log") = false);
+    m.def("icp_batch_device", &icp_batch_device);
+    m.def("homo2tq", &homo2tq, py::arg("homo"));
+    m.def("procrustes", &procrustes, py::arg("ctx"), py::arg("A"), py::arg("B"));
 
 }

@@ -1,15 +1,18 @@
-// Index build: Morton-sorted 32-point buckets + implicit 32-ary AABB hierarchy.
+// Index build: Morton-sorted 32-point buckets + implicit 32-ary AABB hierarchy,
+// for P independent clouds ("segments") in one pass.  P = 1 is the pcp_index case; the ICP batch
+// builds the hierarchies of all P target clouds with ONE segmented sort.
 // Replaces kdtree_recursive_build (kdtree.py:59-97, np.argsort per node) and
 // octree_recursive_build (octree.py:51-103, per-point Python loop computing the 3-bit child code).
 //
-// Kernels (all HBM-bound, one pass each):
-//   bbox_kernel        float3[N] -> 6 ordered-uint min/max words         (np.amin/np.amax, octree.py:319-320)
-//   morton_kernel      float3[N] -> (30-bit Morton key, original index)  (child-code loop, octree.py:75-85)
-//   cub::DeviceRadixSort::SortPairs                                       (np.argsort, kdtree.py:46,76)
-//   gather_leaf_kernel sorted index -> float4 bucket rows + bucket AABBs  (Node / Octant objects)
+// Kernels (all HBM-bound, one pass each; blockIdx.y = segment):
+//   bbox_kernel        float3[n] -> 6 ordered-uint min/max words per segment  (np.amin/np.amax, octree.py:319-320)
+//   key_kernel         float3[n] -> (segment | 30-bit Morton key, row)        (child-code loop, octree.py:75-85)
+//   cub::DeviceRadixSort::SortPairs                                            (np.argsort, kdtree.py:46,76)
+//   gather_leaf_kernel sorted rows -> float4 bucket rows + bucket AABBs        (Node / Octant objects)
 //   node_box_kernel    32 child AABBs -> parent AABB, once per upper level
 #include <cub/device/device_radix_sort.cuh>
 
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstring>
@@ -21,22 +24,33 @@ namespace pcp {
 
 namespace {
 
-__global__ void bbox_init_kernel(unsigned *acc) {
-    int t = threadIdx.x;
-    if (t < 3) acc[t] = 0xffffffffu;        // min slots
-    else if (t < 6) acc[t] = 0u;            // max slots
+constexpr int kMaxGridY = 65535;
+
+// per segment: 8 floats (lo.xyz, scale, hi.xyz, extent) followed by 8 ordered-uint accumulators
+constexpr int kBboxWords = 16;
+
+__global__ void bbox_init_kernel(float *bbox_all, long long P) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= P * 8) return;
+    unsigned *acc = reinterpret_cast<unsigned *>(bbox_all + (i >> 3) * kBboxWords + 8);
+    int t = (int)(i & 7);
+    acc[t] = t < 3 ? 0xffffffffu : 0u;        // min slots / max slots
 }
 
-__global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz, long long n, long long stride,
-                                                   unsigned *__restrict__ acc) {
+__global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz, long long stride,
+                                                   const IndexView *__restrict__ views) {
+    const IndexView &v = views[blockIdx.y];
+    const long long n = v.n;
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const float *p = xyz + i * stride;
+    const long long first = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (blockIdx.x * (long long)blockDim.x >= n) return;
+    for (long long i = first; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float *p = xyz + (v.src_off + i) * stride;
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-            float v = p[a];
-            lo[a] = fminf(lo[a], v);
-            hi[a] = fmaxf(hi[a], v);
+            float x = p[a];
+            lo[a] = fminf(lo[a], x);
+            hi[a] = fmaxf(hi[a], x);
         }
     }
 #pragma unroll
@@ -45,6 +59,7 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz
         hi[a] = warp_max(hi[a]);
     }
     if ((threadIdx.x & 31) == 0) {
+        unsigned *acc = reinterpret_cast<unsigned *>(const_cast<float *>(v.bbox) + 8);
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
             atomicMin(&acc[a], float_to_ordered(lo[a]));
@@ -53,8 +68,12 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz
     }
 }
 
-// bbox words -> {lo.x, lo.y, lo.z, cells-per-unit} used by morton30()
-__global__ void bbox_finish_kernel(const unsigned *acc, float *bbox) {
+// accumulator words -> {lo.x, lo.y, lo.z, cells-per-unit, hi.xyz, extent} used by morton30()
+__global__ void bbox_finish_kernel(float *bbox_all, long long P) {
+    long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (s >= P) return;
+    float *bbox = bbox_all + s * kBboxWords;
+    const unsigned *acc = reinterpret_cast<const unsigned *>(bbox + 8);
     float lo[3], hi[3];
     for (int a = 0; a < 3; ++a) {
         lo[a] = ordered_to_float(acc[a]);
@@ -66,61 +85,67 @@ __global__ void bbox_finish_kernel(const unsigned *acc, float *bbox) {
     bbox[4] = hi[0]; bbox[5] = hi[1]; bbox[6] = hi[2]; bbox[7] = ext;
 }
 
-__global__ void __launch_bounds__(256) morton_kernel(const float *__restrict__ xyz, long long n, long long stride,
-                                                     const float *__restrict__ bbox, unsigned *__restrict__ keys,
-                                                     unsigned *__restrict__ vals) {
+template <class KeyT>
+__global__ void __launch_bounds__(256) key_kernel(const float *__restrict__ xyz, long long stride,
+                                                  const IndexView *__restrict__ views, long long seg0,
+                                                  KeyT *__restrict__ keys, unsigned *__restrict__ vals) {
+    const IndexView &v = views[blockIdx.y];
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float *p = xyz + i * stride;
-    keys[i] = morton30(p[0], p[1], p[2], bbox);
-    vals[i] = static_cast<unsigned>(i);
+    if (i >= v.n) return;
+    const float *p = xyz + (v.src_off + i) * stride;
+    const KeyT seg = static_cast<KeyT>(seg0 + blockIdx.y);
+    // sizeof(KeyT) == 4 only when there is a single segment
+    keys[v.src_off + i] = (sizeof(KeyT) == 4 ? KeyT(0) : static_cast<KeyT>(seg << 30)) | morton30(p[0], p[1], p[2], v.bbox);
+    vals[v.src_off + i] = static_cast<unsigned>(v.src_off + i);
 }
 
-// One warp per bucket: lane j takes sorted position leaf*32+j, gathers its point and the warp
-// reduces the bucket AABB.  Pad lanes of the last bucket are written as NaN / index -1 so that every
-// distance against them is NaN and fails every "<=" gate.
-__global__ void __launch_bounds__(256) gather_leaf_kernel(const float *__restrict__ xyz, long long n, long long stride,
-                                                          const unsigned *__restrict__ sorted_idx,
-                                                          float4 *__restrict__ pts, float4 *__restrict__ box_lo,
-                                                          float4 *__restrict__ box_hi, long long n_leaf) {
+// One warp per bucket: lane j takes sorted position leaf*32+j of its segment, gathers the point and
+// the warp reduces the bucket AABB.  Pad lanes of a segment's last bucket are written as NaN / index
+// -1 so that every distance against them is NaN and fails every "<=" gate.
+__global__ void __launch_bounds__(256) gather_leaf_kernel(const float *__restrict__ xyz, long long stride,
+                                                          const IndexView *__restrict__ views,
+                                                          const unsigned *__restrict__ sorted_rows) {
+    const IndexView &v = views[blockIdx.y];
     long long leaf = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
-    if (leaf >= n_leaf) return;
+    if (leaf >= v.n_leaf) return;
     long long pos = leaf * kLeaf + lane;
     float x = nanf(""), y = x, z = x;
     unsigned idx = 0xffffffffu;
-    if (pos < n) {
-        idx = sorted_idx[pos];
-        const float *p = xyz + (long long)idx * stride;
+    if (pos < v.n) {
+        const unsigned row = sorted_rows[v.src_off + pos];       // sorted by (segment, morton): rows of this segment
+        const float *p = xyz + (long long)row * stride;
         x = p[0]; y = p[1]; z = p[2];
+        idx = row - static_cast<unsigned>(v.src_off);
     }
-    pts[pos] = make_float4(x, y, z, __uint_as_float(idx));
+    const_cast<float4 *>(v.pts)[pos] = make_float4(x, y, z, __uint_as_float(idx));
     // fminf/fmaxf return the non-NaN operand, so pad lanes do not disturb the box
     float lx = warp_min(x), ly = warp_min(y), lz = warp_min(z);
     float hx = warp_max(x), hy = warp_max(y), hz = warp_max(z);
     if (lane == 0) {
-        box_lo[leaf] = make_float4(lx, ly, lz, 0.f);
-        box_hi[leaf] = make_float4(hx, hy, hz, 0.f);
+        const_cast<float4 *>(v.box_lo)[leaf] = make_float4(lx, ly, lz, 0.f);
+        const_cast<float4 *>(v.box_hi)[leaf] = make_float4(hx, hy, hz, 0.f);
     }
 }
 
-__global__ void __launch_bounds__(256) node_box_kernel(float4 *__restrict__ box_lo, float4 *__restrict__ box_hi,
-                                                       long long child_off, long long child_cnt,
-                                                       long long node_off, long long node_cnt) {
+__global__ void __launch_bounds__(256) node_box_kernel(const IndexView *__restrict__ views, int level) {
+    const IndexView &v = views[blockIdx.y];
+    if (level >= v.n_levels) return;
     long long node = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
-    if (node >= node_cnt) return;
+    if (node >= v.level_cnt[level]) return;
+    float4 *box_lo = const_cast<float4 *>(v.box_lo), *box_hi = const_cast<float4 *>(v.box_hi);
     long long c = node * kFan + lane;
     float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
-    if (c < child_cnt) {
-        lo = box_lo[child_off + c];
-        hi = box_hi[child_off + c];
+    if (c < v.level_cnt[level - 1]) {
+        lo = box_lo[v.level_off[level - 1] + c];
+        hi = box_hi[v.level_off[level - 1] + c];
     }
     float lx = warp_min(lo.x), ly = warp_min(lo.y), lz = warp_min(lo.z);
     float hx = warp_max(hi.x), hy = warp_max(hi.y), hz = warp_max(hi.z);
     if (lane == 0) {
-        box_lo[node_off + node] = make_float4(lx, ly, lz, 0.f);
-        box_hi[node_off + node] = make_float4(hx, hy, hz, 0.f);
+        box_lo[v.level_off[level] + node] = make_float4(lx, ly, lz, 0.f);
+        box_hi[v.level_off[level] + node] = make_float4(hx, hy, hz, 0.f);
     }
 }
 
@@ -134,93 +159,148 @@ __global__ void __launch_bounds__(256) query_key_kernel(const float *__restrict_
     vals[i] = static_cast<unsigned>(i);
 }
 
-int radix_sort_pairs(pcp_ctx *ctx, const unsigned *k_in, unsigned *k_out, const unsigned *v_in, unsigned *v_out,
-                     long long n) {
+template <class KeyT>
+int radix_sort_pairs(pcp_ctx *ctx, const KeyT *k_in, KeyT *k_out, const unsigned *v_in, unsigned *v_out, long long n,
+                     int end_bit) {
     size_t tmp_bytes = 0;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, 30, ctx->stream));
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, end_bit, ctx->stream));
     PCP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, 30, ctx->stream));
-    ctx->launches += 5;   // onesweep: histogram + 4 digit passes (approximate, CUB internal)
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, end_bit,
+                                             ctx->stream));
+    ctx->launches += 2 + (end_bit + 7) / 8;   // onesweep: histogram + scan + one pass per 8-bit digit (CUB internal)
     return PCP_OK;
 }
 
-inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>((n + block - 1) / block); }
+inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(std::max<long long>(1, (n + block - 1) / block)); }
 
 }  // namespace
 
-IndexView make_view(const pcp_index *ix) {
-    IndexView v;
-    v.pts = ix->pts.as<float4>();
-    v.box_lo = ix->box_lo.as<float4>();
-    v.box_hi = ix->box_hi.as<float4>();
-    v.bbox = ix->bbox.as<float>();
-    v.n = ix->n;
-    v.n_leaf = ix->n_leaf;
-    v.n_levels = ix->n_levels;
-    for (int l = 0; l < kMaxLevels; ++l) {
-        v.level_off[l] = ix->level_off[l];
-        v.level_cnt[l] = ix->level_cnt[l];
-    }
-    return v;
+void BatchIndex::release() {
+    for (DevBuf *d : {&pts, &box_lo, &box_hi, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
+    h_views.clear();
+    P = 0;
 }
 
-int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride) {
-    pcp_ctx *ctx = ix->ctx;
+int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_t P, const int64_t *h_offsets) {
+    pcp_ctx *ctx = b->ctx;
     cudaStream_t st = ctx->stream;
-    ix->n = n;
-    ix->n_leaf = (n + kLeaf - 1) / kLeaf;
-    ix->n_levels = 0;
-    if (n == 0) return PCP_OK;
-    if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_index_build: more than 2^31-1 points");
+    b->P = P;
+    b->h_views.assign((size_t)P, IndexView());
+    b->total_n = P ? h_offsets[P] - h_offsets[0] : 0;
+    b->total_leaf = b->total_nodes = b->max_n = b->max_leaf = 0;
+    b->max_levels = 0;
+    for (int l = 0; l < kMaxLevels; ++l) b->level_max_cnt[l] = 0;
+    if (P == 0) return PCP_OK;
+    if (h_offsets[0] != 0) return fail(PCP_ERR_INVALID, "index build: offsets[0] must be 0");
+    if (b->total_n > 0xfffffffeLL) return fail(PCP_ERR_UNSUPPORTED, "index build: more than 2^32-2 points in one batch");
 
-    // hierarchy shape
-    long long cnt = ix->n_leaf, off = 0;
-    int levels = 0;
-    while (true) {
-        if (levels >= kMaxLevels) return fail(PCP_ERR_UNSUPPORTED, "pcp_index_build: hierarchy too deep");
-        ix->level_off[levels] = off;
-        ix->level_cnt[levels] = cnt;
-        ++levels;
-        off += cnt;
-        if (cnt == 1) break;
-        cnt = (cnt + kFan - 1) / kFan;
+    // hierarchy shapes (host): per segment, levels of ceil(cnt/32) nodes down to a single root
+    for (int64_t p = 0; p < P; ++p) {
+        IndexView &v = b->h_views[(size_t)p];
+        const int64_t n = h_offsets[p + 1] - h_offsets[p];
+        if (n < 0) return fail(PCP_ERR_INVALID, "index build: offsets must be non-decreasing");
+        if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "index build: more than 2^31-1 points in one cloud");
+        v.src_off = h_offsets[p];
+        v.n = n;
+        v.n_leaf = (n + kLeaf - 1) / kLeaf;
+        v.n_levels = 0;
+        long long cnt = v.n_leaf, off = 0;
+        while (cnt > 0) {
+            if (v.n_levels >= kMaxLevels) return fail(PCP_ERR_UNSUPPORTED, "index build: hierarchy too deep");
+            v.level_off[v.n_levels] = off;
+            v.level_cnt[v.n_levels] = cnt;
+            b->level_max_cnt[v.n_levels] = std::max<int64_t>(b->level_max_cnt[v.n_levels], cnt);
+            ++v.n_levels;
+            off += cnt;
+            if (cnt == 1) break;
+            cnt = (cnt + kFan - 1) / kFan;
+        }
+        // pointers are patched below once the arrays are sized: keep element offsets for now
+        v.pts = reinterpret_cast<const float4 *>((uintptr_t)(b->total_leaf * kLeaf));
+        v.box_lo = reinterpret_cast<const float4 *>((uintptr_t)b->total_nodes);
+        b->total_leaf += v.n_leaf;
+        b->total_nodes += off;
+        b->max_n = std::max<int64_t>(b->max_n, n);
+        b->max_leaf = std::max<int64_t>(b->max_leaf, v.n_leaf);
+        b->max_levels = std::max(b->max_levels, v.n_levels);
     }
-    ix->n_levels = levels;
-    long long total_nodes = off;
 
-    PCP_TRY(ix->pts.ensure(sizeof(float4) * (size_t)ix->n_leaf * kLeaf));
-    PCP_TRY(ix->box_lo.ensure(sizeof(float4) * (size_t)total_nodes));
-    PCP_TRY(ix->box_hi.ensure(sizeof(float4) * (size_t)total_nodes));
-    PCP_TRY(ix->bbox.ensure(sizeof(float) * 8 + sizeof(unsigned) * 8));
-    PCP_TRY(ix->keys_a.ensure(sizeof(unsigned) * (size_t)n));
-    PCP_TRY(ix->keys_b.ensure(sizeof(unsigned) * (size_t)n));
-    PCP_TRY(ix->vals_a.ensure(sizeof(unsigned) * (size_t)n));
-    PCP_TRY(ix->vals_b.ensure(sizeof(unsigned) * (size_t)n));
+    PCP_TRY(b->pts.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_leaf) * kLeaf));
+    PCP_TRY(b->box_lo.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
+    PCP_TRY(b->box_hi.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
+    PCP_TRY(b->bbox.ensure(sizeof(float) * kBboxWords * (size_t)P));
+    PCP_TRY(b->views.ensure(sizeof(IndexView) * (size_t)P));
+    for (int64_t p = 0; p < P; ++p) {
+        IndexView &v = b->h_views[(size_t)p];
+        const uintptr_t pt_off = reinterpret_cast<uintptr_t>(v.pts), node_off = reinterpret_cast<uintptr_t>(v.box_lo);
+        v.pts = b->pts.as<float4>() + pt_off;
+        v.box_lo = b->box_lo.as<float4>() + node_off;
+        v.box_hi = b->box_hi.as<float4>() + node_off;
+        v.bbox = b->bbox.as<float>() + p * kBboxWords;
+    }
+    // views are small (184 B per segment): pageable copy, staged by the driver before it returns
+    PCP_CUDA(cudaMemcpyAsync(b->views.p, b->h_views.data(), sizeof(IndexView) * (size_t)P, cudaMemcpyHostToDevice, st));
+    if (b->total_n == 0) return PCP_OK;
 
-    float *bbox = ix->bbox.as<float>();
-    unsigned *acc = reinterpret_cast<unsigned *>(bbox + 8);
+    const bool wide = P > 1;
+    const size_t key_bytes = wide ? 8 : 4;
+    PCP_TRY(b->keys_a.ensure(key_bytes * (size_t)b->total_n));
+    PCP_TRY(b->keys_b.ensure(key_bytes * (size_t)b->total_n));
+    PCP_TRY(b->vals_a.ensure(sizeof(unsigned) * (size_t)b->total_n));
+    PCP_TRY(b->vals_b.ensure(sizeof(unsigned) * (size_t)b->total_n));
+    const IndexView *dv = b->d_views();
 
-    bbox_init_kernel<<<1, 32, 0, st>>>(acc);
-    int bgrid = (int)std::min<long long>(grid_for(n, 256), (long long)ctx->sm_count * 8);
-    bbox_kernel<<<bgrid, 256, 0, st>>>(d_xyz, n, stride, acc);
-    bbox_finish_kernel<<<1, 1, 0, st>>>(acc, bbox);
-    morton_kernel<<<grid_for(n, 256), 256, 0, st>>>(d_xyz, n, stride, bbox, ix->keys_a.as<unsigned>(),
-                                                    ix->vals_a.as<unsigned>());
-    ctx->launches += 4;
-    PCP_TRY(radix_sort_pairs(ctx, ix->keys_a.as<unsigned>(), ix->keys_b.as<unsigned>(), ix->vals_a.as<unsigned>(),
-                             ix->vals_b.as<unsigned>(), n));
-    gather_leaf_kernel<<<grid_for(ix->n_leaf * 32, 256), 256, 0, st>>>(
-        d_xyz, n, stride, ix->vals_b.as<unsigned>(), ix->pts.as<float4>(), ix->box_lo.as<float4>(),
-        ix->box_hi.as<float4>(), ix->n_leaf);
+    bbox_init_kernel<<<grid_for(P * 8, 256), 256, 0, st>>>(b->bbox.as<float>(), P);
     ctx->launches += 1;
-    for (int l = 1; l < levels; ++l) {
-        node_box_kernel<<<grid_for(ix->level_cnt[l] * 32, 256), 256, 0, st>>>(
-            ix->box_lo.as<float4>(), ix->box_hi.as<float4>(), ix->level_off[l - 1], ix->level_cnt[l - 1],
-            ix->level_off[l], ix->level_cnt[l]);
+    const unsigned bx = (unsigned)std::min<long long>(grid_for(b->max_n, 256),
+                                                      P == 1 ? (long long)ctx->sm_count * 8 : 16);
+    for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+        const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+        bbox_kernel<<<dim3(bx, gy), 256, 0, st>>>(d_xyz, stride, dv + p0);
         ctx->launches += 1;
+    }
+    bbox_finish_kernel<<<grid_for(P, 128), 128, 0, st>>>(b->bbox.as<float>(), P);
+    ctx->launches += 1;
+    for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+        const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+        if (wide)
+            key_kernel<unsigned long long><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
+                d_xyz, stride, dv + p0, p0, b->keys_a.as<unsigned long long>(), b->vals_a.as<unsigned>());
+        else
+            key_kernel<unsigned><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
+                d_xyz, stride, dv + p0, p0, b->keys_a.as<unsigned>(), b->vals_a.as<unsigned>());
+        ctx->launches += 1;
+    }
+    if (wide) {
+        int seg_bits = 1;
+        while ((1LL << seg_bits) < P) ++seg_bits;
+        PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
+                                                     b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
+                                                     b->vals_b.as<unsigned>(), b->total_n, 30 + seg_bits));
+    } else {
+        PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
+                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n, 30));
+    }
+    for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+        const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+        gather_leaf_kernel<<<dim3(grid_for(b->max_leaf * 32, 256), gy), 256, 0, st>>>(d_xyz, stride, dv + p0,
+                                                                                    b->vals_b.as<unsigned>());
+        ctx->launches += 1;
+        for (int l = 1; l < b->max_levels; ++l) {
+            node_box_kernel<<<dim3(grid_for(b->level_max_cnt[l] * 32, 256), gy), 256, 0, st>>>(dv + p0, l);
+            ctx->launches += 1;
+        }
     }
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
+}
+
+int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride) {
+    if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_index_build: more than 2^31-1 points");
+    ix->n = n;
+    ix->b.ctx = ix->ctx;
+    const int64_t offs[2] = {0, n};
+    return batch_build_device(&ix->b, d_xyz, stride, 1, offs);
 }
 
 int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm) {
@@ -231,9 +311,9 @@ int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, ui
     PCP_TRY(ctx->scratch[2].ensure(sizeof(unsigned) * (size_t)nq));
     unsigned *ka = ctx->scratch[0].as<unsigned>(), *kb = ctx->scratch[1].as<unsigned>();
     unsigned *va = ctx->scratch[2].as<unsigned>();
-    query_key_kernel<<<grid_for(nq, 256), 256, 0, ctx->stream>>>(d_q, nq, stride, ix->bbox.as<float>(), ka, va);
+    query_key_kernel<<<grid_for(nq, 256), 256, 0, ctx->stream>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
     ctx->launches += 1;
-    PCP_TRY(radix_sort_pairs(ctx, ka, kb, va, d_perm, nq));
+    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, 30));
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
 }

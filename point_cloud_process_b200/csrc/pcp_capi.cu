@@ -163,6 +163,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     ctx->cub_tmp.release();
     ctx->counters.release();
+    ctx->icp_targets.release();
     for (auto &b : ctx->scratch) b.release();
     for (auto &b : ctx->pin) b.release();
     cudaStreamDestroy(ctx->stream);
@@ -250,9 +251,8 @@ int pcp_index_destroy(pcp_index *ix) {
     if (!ix) return PCP_OK;
     DeviceGuard g(ix->ctx->device);
     cudaStreamSynchronize(ix->ctx->stream);
-    for (DevBuf *b : {&ix->pts, &ix->box_lo, &ix->box_hi, &ix->bbox, &ix->keys_a, &ix->keys_b, &ix->vals_a,
-                      &ix->vals_b, &ix->src_copy})
-        b->release();
+    ix->b.release();
+    ix->src_copy.release();
     delete ix;
     return PCP_OK;
 }
@@ -261,8 +261,8 @@ int64_t pcp_index_size(const pcp_index *ix) { return ix ? ix->n : 0; }
 
 int pcp_index_stats(const pcp_index *ix, int64_t *n_buckets, int *n_levels) {
     if (!ix) return fail(PCP_ERR_INVALID, "pcp_index_stats: index is NULL");
-    if (n_buckets) *n_buckets = ix->n_leaf;
-    if (n_levels) *n_levels = ix->n_levels;
+    if (n_buckets) *n_buckets = ix->b.h_views.empty() ? 0 : ix->b.h_views[0].n_leaf;
+    if (n_levels) *n_levels = ix->b.h_views.empty() ? 0 : ix->b.h_views[0].n_levels;
     return PCP_OK;
 }
 
@@ -385,6 +385,82 @@ int pcp_radius_fill(pcp_index *ix, const float *queries, int64_t nq, int64_t str
     PCP_TRY(download(ctx, idx, d_idx, (size_t)m * 4));
     PCP_TRY(download(ctx, dist, d_dist, (size_t)m * 4));
     PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- ICP
+
+int pcp_icp_default_params(pcp_icp_params *p) {
+    if (!p) return fail(PCP_ERR_INVALID, "pcp_icp_default_params: p is NULL");
+    p->max_iteration = 100;        // main.py:98
+    p->R_diff_thres = 0.5;         // main.py:101
+    p->t_diff_thres = 0.5;         // main.py:102
+    p->dist_thres = 5.0;           // main.py:103
+    p->first_iter_broadcast = 1;   // main.py:150 as built
+    return PCP_OK;
+}
+
+int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_pairs, const float *src_xyz,
+                  const int64_t *src_offsets, const float *tgt_xyz, const int64_t *tgt_offsets, int64_t stride, int mem,
+                  const double *T_init, double *T_last, double *T_total, int32_t *iterations, int32_t *status,
+                  double *diff_log) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_icp_batch: ctx is NULL");
+    if (n_pairs < 0) return fail(PCP_ERR_INVALID, "pcp_icp_batch: negative pair count");
+    if (n_pairs == 0) return PCP_OK;
+    if (!src_offsets || !tgt_offsets) return fail(PCP_ERR_INVALID, "pcp_icp_batch: offsets are NULL");
+    if (src_offsets[0] != 0 || tgt_offsets[0] != 0) return fail(PCP_ERR_INVALID, "pcp_icp_batch: offsets[0] must be 0");
+    const int64_t ns = src_offsets[n_pairs], nt = tgt_offsets[n_pairs];
+    PCP_TRY(check_cloud("pcp_icp_batch", src_xyz, ns, stride, mem));
+    PCP_TRY(check_cloud("pcp_icp_batch", tgt_xyz, nt, stride, mem));
+    pcp_icp_params prm;
+    pcp_icp_default_params(&prm);
+    if (params) prm = *params;
+    if (prm.max_iteration < 0) return fail(PCP_ERR_INVALID, "pcp_icp_batch: max_iteration < 0");
+    if (std::isnan(prm.dist_thres) || std::isnan(prm.R_diff_thres) || std::isnan(prm.t_diff_thres))
+        return fail(PCP_ERR_INVALID, "pcp_icp_batch: NaN threshold");
+    DeviceGuard g(ctx->device);
+    const float *d_src = src_xyz, *d_tgt = tgt_xyz;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 0, ctx->scratch[5], src_xyz, sizeof(float) * (size_t)ns * (size_t)stride));
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], tgt_xyz, sizeof(float) * (size_t)nt * (size_t)stride));
+        d_src = ctx->scratch[5].as<float>();
+        d_tgt = ctx->scratch[6].as<float>();
+    }
+    return icp_batch_device(ctx, prm, n_pairs, d_src, src_offsets, d_tgt, tgt_offsets, stride, T_init, T_last, T_total,
+                            iterations, status, diff_log);
+}
+
+int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, int mem, double *R, double *t, double *cost) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_procrustes: ctx is NULL");
+    if (n < 1 || !A || !B) return fail(PCP_ERR_INVALID, "pcp_procrustes: need n >= 1 correspondences and non-NULL A, B");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_procrustes: mem must be PCP_HOST or PCP_DEVICE");
+    DeviceGuard g(ctx->device);
+    const double *d_A = A, *d_B = B;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 0, ctx->scratch[5], A, sizeof(double) * 3 * (size_t)n));
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], B, sizeof(double) * 3 * (size_t)n));
+        d_A = ctx->scratch[5].as<double>();
+        d_B = ctx->scratch[6].as<double>();
+    }
+    return procrustes_device(ctx, d_A, d_B, n, R, t, cost);
+}
+
+// rotmat2quaternion / copysign / homo2tq of main.py:158-180 (host arithmetic, float64)
+int pcp_homo2tq(const double *m, double *tq) {
+    if (!m || !tq) return fail(PCP_ERR_INVALID, "pcp_homo2tq: NULL argument");
+    auto at = [&](int r, int c) { return m[r * 4 + c]; };
+    auto half_sqrt = [](double v) { return std::sqrt(v > 0.0 ? v : 0.0) / 2.0; };     // np.sqrt(max(0, v)) / 2
+    auto copysign_ref = [](double v, double s) { return v * s < 0 ? -v : v; };       // main.py:176-180
+    const double trace = at(0, 0) + at(1, 1) + at(2, 2);
+    double qw = half_sqrt(trace + 1);
+    double qx = half_sqrt(1 + at(0, 0) - at(1, 1) - at(2, 2));
+    double qy = half_sqrt(1 - at(0, 0) + at(1, 1) - at(2, 2));
+    double qz = half_sqrt(1 - at(0, 0) - at(1, 1) + at(2, 2));
+    qx = copysign_ref(qx, at(2, 1) - at(1, 2));
+    qy = copysign_ref(qy, at(0, 2) - at(2, 0));
+    qz = copysign_ref(qz, at(1, 0) - at(0, 1));
+    tq[0] = at(0, 3); tq[1] = at(1, 3); tq[2] = at(2, 3);
+    tq[3] = qw; tq[4] = qx; tq[5] = qy; tq[6] = qz;
     return PCP_OK;
 }
 

@@ -1,0 +1,572 @@
+// Point-to-point ICP, batched over independent registration pairs, every iteration on the device.
+// Replaces icp_point2point (Registration/main.py:97-156) and the ICP / find_associations /
+// procrustes_transformation contract of icp_template.py:43-54,113-126,128-200.
+//
+// Per iteration two kernels run over ALL still-active pairs (no host round trip on the data path;
+// the host only reads one "pairs still active" word at geometrically spaced iterations to stop
+// enqueueing launches):
+//
+//   icp_assoc_kernel   grid (chunks, pairs).  Fuses, in one pass over a chunk of source points:
+//       main.py:110      source.transform(T)        -> p = applied * p0 in float64 (applied = composed pose)
+//       main.py:116-117  1-NN in the target          -> warp-per-query walk of the target's bucket hierarchy,
+//                                                       float32 box/point filter with a proven error margin,
+//                                                       float64 distance on the survivors (Open3D computes in doubles)
+//       main.py:119      keep iff d^2 < dist_thres
+//       main.py:131-137  centroids + cross-covariance -> 16 float64 sums (M, sum a, sum b, sum b a^T), warp
+//                                                       shuffle-free lane-0 accumulation + block reduction,
+//                                                       one partial record per CTA (deterministic, no atomics)
+//   icp_solve_kernel   one warp per pair:
+//       main.py:125-127  fewer than 3 associations -> stop
+//       main.py:134-140  H = sum (b - bm)(a - am)^T;  U S V^T = H by one-sided Jacobi (float64);  R = U V^T (no det fix);
+//                        t = bm - R am
+//       main.py:149-154  R_diff = ||R - R_last||_F, t_diff = ||t - t_last|| with the first-iteration (3,1)-(3,)
+//                        broadcast of main.py:150; stop when both <= thresholds
+//       main.py:156      T_last = last increment;   icp_template.py:198 homo_mat_total = composed pose
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "pcp_device.cuh"
+#include "pcp_internal.cuh"
+
+namespace pcp {
+
+namespace {
+
+constexpr int kAssocWarps = 8;
+constexpr int kChunk = 512;               // source points per CTA
+constexpr int kSums = 16;                 // M, a(3), b(3), b a^T (9)
+constexpr unsigned kDone = 0xffffffffu;
+
+struct IcpState {
+    double applied[12];     // 3x4 row-major: pose applied to the ORIGINAL source in the current iteration
+    double cur[12];         // last increment (main.py:143-146); the initial transformation before iteration 1
+    double total[12];       // composed pose incl. the last increment (icp_template.py:198)
+    double R_last[9];
+    double t_last[3];
+    int active;
+    int iters;
+    int status;
+    int pad;
+};
+
+__device__ __forceinline__ unsigned long long shfl_xor64(unsigned long long v, int m) {
+    return __shfl_xor_sync(kFullMask, v, m);
+}
+
+// Exact 1-NN of the float64 point q in one segment, restricted to d^2 < limit.  Warp-cooperative:
+// every lane returns the same (d2, idx); idx == kDone when no point qualifies.
+// Float32 filter: q is rounded to float (|e_i| <= 2^-24 |q_i|) and distances / box bounds are
+// evaluated in the library's float32 arithmetic; |d2_f - d2| <= 2 d E + E^2 + 4 eps d2 with
+// E = sqrt(3) 2^-24 max|q_i|, so every candidate that can beat the current float64 best passes
+// "d2_f <= gate" with gate = best (1 + 2^-20) + 2 sqrt(best) E + E^2 (rounded up).
+struct Nn1 {
+    double d2;
+    unsigned idx;
+    float bx, by, bz;       // coordinates of the winner (exact float32 target point)
+};
+
+__device__ __forceinline__ float nn1_gate(double best, double E) {
+    if (!(best < 1e300)) return __int_as_float(0x7f800000);
+    return __double2float_ru(best * (1.0 + 9.6e-7) + 2.0 * sqrt(best) * E + E * E);
+}
+
+__device__ Nn1 nn1_search(const IndexView &ix, double qxd, double qyd, double qzd, double limit, unsigned (*lbs)[32],
+                          unsigned *nodes, int lane) {
+    Nn1 r;
+    r.d2 = limit;
+    r.idx = kDone;
+    r.bx = r.by = r.bz = 0.f;
+    if (ix.n_levels == 0) return r;
+    const float qx = (float)qxd, qy = (float)qyd, qz = (float)qzd;
+    const double E = 1.04e-7 * (fabs(qxd) + fabs(qyd) + fabs(qzd));
+    float gate = nn1_gate(r.d2, E);
+
+    auto scan_bucket = [&](long long leaf) {
+        const float4 p = __ldg(ix.pts + leaf * kLeaf + lane);
+        const float d2f = ref_d2(qx, qy, qz, p.x, p.y, p.z);
+        const bool pass = d2f <= gate;                 // NaN pads never pass
+        if (__ballot_sync(kFullMask, pass) == 0) return;
+        double d2 = 1e308;
+        unsigned id = kDone;
+        if (pass) {
+            const double dx = qxd - (double)p.x, dy = qyd - (double)p.y, dz = qzd - (double)p.z;
+            d2 = dx * dx + dy * dy + dz * dz;
+            id = __float_as_uint(p.w);
+        }
+        // warp arg-min over (d2, index): non-negative doubles order like their bit patterns
+        unsigned long long key = __double_as_longlong(d2);
+        unsigned wid = id;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long ok = shfl_xor64(key, o);
+            const unsigned oi = __shfl_xor_sync(kFullMask, wid, o);
+            if (ok < key || (ok == key && oi < wid)) { key = ok; wid = oi; }
+        }
+        const double best = __longlong_as_double(key);
+        if (best < r.d2 || (best == r.d2 && wid < r.idx)) {      // warp-uniform branch
+            const int src = __ffs(__ballot_sync(kFullMask, pass && id == wid)) - 1;
+            r.d2 = best;
+            r.idx = wid;
+            r.bx = __shfl_sync(kFullMask, p.x, src);
+            r.by = __shfl_sync(kFullMask, p.y, src);
+            r.bz = __shfl_sync(kFullMask, p.z, src);
+            gate = nn1_gate(r.d2, E);
+        }
+    };
+
+    const int top = ix.n_levels - 1;
+    if (top == 0) {
+        scan_bucket(0);
+        return r;
+    }
+    auto open_node = [&](int lv, unsigned node) {
+        if (lane == 0) nodes[lv] = node;
+        const long long c = (long long)node * kFan + lane;
+        unsigned bits = kDone;
+        if (c < ix.level_cnt[lv - 1]) {
+            const long long b = ix.level_off[lv - 1] + c;
+            bits = __float_as_uint(box_lb2(qx, qy, qz, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)));
+        }
+        lbs[lv][lane] = bits;
+        __syncwarp();
+    };
+    int level = top;
+    open_node(top, 0u);
+    while (true) {
+        const unsigned mine = lbs[level][lane];
+        const unsigned best = __reduce_min_sync(kFullMask, mine);
+        if (best == kDone || !(__uint_as_float(best) <= gate)) {
+            if (level == top) break;
+            ++level;
+            continue;
+        }
+        const int sel = __ffs(__ballot_sync(kFullMask, mine == best)) - 1;
+        if (lane == sel) lbs[level][lane] = kDone;
+        const unsigned child = nodes[level] * kFan + sel;
+        __syncwarp();
+        if (level == 1) {
+            scan_bucket(child);
+        } else {
+            --level;
+            open_node(level, child);
+        }
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(kAssocWarps * 32)
+icp_assoc_kernel(const IndexView *__restrict__ views, const float *__restrict__ src, const long long *__restrict__ src_off,
+                 long long stride, const IcpState *__restrict__ states, double *__restrict__ partials,
+                 int chunks_per_pair, double dist_thres) {
+    __shared__ unsigned s_lb[kAssocWarps][kMaxLevels][32];
+    __shared__ unsigned s_node[kAssocWarps][kMaxLevels];
+    __shared__ double s_sum[kAssocWarps][kSums];
+    const int pair = blockIdx.y, chunk = blockIdx.x;
+    const IcpState &st = states[pair];
+    if (!st.active) return;
+    const long long s0 = src_off[pair], ns = src_off[pair + 1] - s0;
+    const long long first = (long long)chunk * kChunk;
+    if (first >= ns) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const IndexView &ix = views[pair];
+    double T[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) T[i] = st.applied[i];
+    double acc[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) acc[i] = 0.0;
+    const long long last = min(first + (long long)kChunk, ns);
+    for (long long i = first + warp; i < last; i += kAssocWarps) {
+        const float *p = src + (s0 + i) * stride;
+        const double x = (double)__ldg(p), y = (double)__ldg(p + 1), z = (double)__ldg(p + 2);
+        // main.py:110 -- the reference transforms its float64 copy cumulatively; composing the pose and
+        // transforming the original differs by O(1e-16) relative
+        const double ax = T[0] * x + T[1] * y + T[2] * z + T[3];
+        const double ay = T[4] * x + T[5] * y + T[6] * z + T[7];
+        const double az = T[8] * x + T[9] * y + T[10] * z + T[11];
+        const Nn1 nn = nn1_search(ix, ax, ay, az, dist_thres, s_lb[warp], s_node[warp], lane);
+        if (nn.idx != kDone && nn.d2 < dist_thres) {       // main.py:119 (squared distance vs dist_thres)
+            const double bx = (double)nn.bx, by = (double)nn.by, bz = (double)nn.bz;
+            acc[0] += 1.0;
+            acc[1] += ax; acc[2] += ay; acc[3] += az;
+            acc[4] += bx; acc[5] += by; acc[6] += bz;
+            acc[7] += bx * ax; acc[8] += bx * ay; acc[9] += bx * az;
+            acc[10] += by * ax; acc[11] += by * ay; acc[12] += by * az;
+            acc[13] += bz * ax; acc[14] += bz * ay; acc[15] += bz * az;
+        }
+    }
+    // every lane of a warp holds identical sums; fixed-order block reduction -> one record per CTA
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < kSums; ++i) s_sum[warp][i] = acc[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < kSums) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kAssocWarps; ++w) s += s_sum[w][threadIdx.x];
+        partials[((long long)pair * chunks_per_pair + chunk) * kSums + threadIdx.x] = s;
+    }
+}
+
+// One-sided (Hestenes) Jacobi SVD of a 3x3 float64 matrix: A V = U S.  Returns R = U V^T, the
+// orthogonal polar factor u @ vt of main.py:138-139 (independent of the SVD's sign conventions
+// whenever the smallest singular value is > 0).
+__device__ void polar_uvt(const double H[9], double R[9]) {
+    double A[9], V[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+#pragma unroll
+    for (int i = 0; i < 9; ++i) A[i] = H[i];
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        double off = 0.0;
+#pragma unroll
+        for (int pq = 0; pq < 3; ++pq) {
+            const int p = pq == 2 ? 1 : 0, q = pq == 0 ? 1 : 2;
+            double alpha = 0, beta = 0, gamma = 0;
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                alpha += A[r * 3 + p] * A[r * 3 + p];
+                beta += A[r * 3 + q] * A[r * 3 + q];
+                gamma += A[r * 3 + p] * A[r * 3 + q];
+            }
+            const double lim = 1e-15 * sqrt(alpha * beta);
+            if (fabs(gamma) <= lim || gamma == 0.0) continue;
+            off = fmax(off, fabs(gamma) / fmax(sqrt(alpha * beta), 1e-300));
+            const double zeta = (beta - alpha) / (2.0 * gamma);
+            const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+            const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const double ap = A[r * 3 + p], aq = A[r * 3 + q];
+                A[r * 3 + p] = c * ap - s * aq;
+                A[r * 3 + q] = s * ap + c * aq;
+                const double vp = V[r * 3 + p], vq = V[r * 3 + q];
+                V[r * 3 + p] = c * vp - s * vq;
+                V[r * 3 + q] = s * vp + c * vq;
+            }
+        }
+        if (off < 1e-15) break;
+    }
+    // U columns = normalised A columns; a vanishing column (rank-deficient H: collinear / planar
+    // correspondences) is completed by the cross product of the other two, as any SVD would pick
+    // some unit vector orthogonal to them.
+    double U[9], nrm[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) nrm[j] = sqrt(A[j] * A[j] + A[3 + j] * A[3 + j] + A[6 + j] * A[6 + j]);
+    const double big = fmax(nrm[0], fmax(nrm[1], nrm[2]));
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const double inv = nrm[j] > 1e-14 * big && nrm[j] > 0.0 ? 1.0 / nrm[j] : 0.0;
+        U[j] = A[j] * inv; U[3 + j] = A[3 + j] * inv; U[6 + j] = A[6 + j] * inv;
+    }
+    for (int j = 0; j < 3; ++j) {
+        if (nrm[j] > 1e-14 * big && nrm[j] > 0.0) continue;
+        const int a = (j + 1) % 3, b = (j + 2) % 3;
+        U[j] = U[3 + a] * U[6 + b] - U[6 + a] * U[3 + b];
+        U[3 + j] = U[6 + a] * U[b] - U[a] * U[6 + b];
+        U[6 + j] = U[a] * U[3 + b] - U[3 + a] * U[b];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            R[i * 3 + j] = U[i * 3 + 0] * V[j * 3 + 0] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
+}
+
+// out = inc o prev for 3x4 row-major rigid transforms
+__device__ __forceinline__ void compose(const double inc[12], const double prev[12], double out[12]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            double s = inc[i * 4 + 0] * prev[0 * 4 + j] + inc[i * 4 + 1] * prev[1 * 4 + j] + inc[i * 4 + 2] * prev[2 * 4 + j];
+            if (j == 3) s += inc[i * 4 + 3];
+            out[i * 4 + j] = s;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+icp_solve_kernel(IcpState *__restrict__ states, const double *__restrict__ partials, const long long *__restrict__ src_off,
+                 long long n_pairs, int chunks_per_pair, int iteration, int max_iteration, double R_thr, double t_thr,
+                 int first_iter_broadcast, double *__restrict__ diff_log, int *__restrict__ n_active) {
+    const long long pair = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (pair >= n_pairs) return;
+    IcpState &st = states[pair];
+    if (!st.active) return;
+    const long long ns = src_off[pair + 1] - src_off[pair];
+    const int chunks = (int)((ns + kChunk - 1) / kChunk);
+    // lane l < 16 sums component l over the pair's chunk records in chunk order (deterministic)
+    double s = 0.0;
+    if (lane < kSums)
+        for (int c = 0; c < chunks; ++c) s += partials[((long long)pair * chunks_per_pair + c) * kSums + lane];
+    double S[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) S[i] = __shfl_sync(kFullMask, s, i);
+    if (lane != 0) return;
+
+    st.iters = iteration + 1;
+    const double M = S[0];
+    if (M < 3.0) {                                  // main.py:125-127 "ICP failed, cannot find enough associations!"
+        st.status = PCP_ICP_FEW_PAIRS;
+        st.active = 0;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) st.total[i] = st.applied[i];
+        atomicSub(n_active, 1);
+        return;
+    }
+    const double inv = 1.0 / M;
+    const double am[3] = {S[1] * inv, S[2] * inv, S[3] * inv}, bm[3] = {S[4] * inv, S[5] * inv, S[6] * inv};
+    double H[9], R[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) H[i * 3 + j] = S[7 + i * 3 + j] - M * bm[i] * am[j];   // Bp @ Ap.T, main.py:137
+    polar_uvt(H, R);                                // main.py:138-139
+    double t[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) t[i] = bm[i] - (R[i * 3] * am[0] + R[i * 3 + 1] * am[1] + R[i * 3 + 2] * am[2]);   // main.py:140
+    double rd = 0.0, td = 0.0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) rd += (R[i] - st.R_last[i]) * (R[i] - st.R_last[i]);
+    if (iteration == 0 && first_iter_broadcast) {
+        // main.py:150 on the first pass: t is (3,1), t_last is (3,) -> the difference broadcasts to 3x3
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) td += (t[i] - st.t_last[j]) * (t[i] - st.t_last[j]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) td += (t[i] - st.t_last[i]) * (t[i] - st.t_last[i]);
+    }
+    rd = sqrt(rd);
+    td = sqrt(td);
+    if (diff_log) {
+        diff_log[((long long)pair * max_iteration + iteration) * 2 + 0] = rd;
+        diff_log[((long long)pair * max_iteration + iteration) * 2 + 1] = td;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        st.cur[i * 4 + 0] = R[i * 3 + 0]; st.cur[i * 4 + 1] = R[i * 3 + 1]; st.cur[i * 4 + 2] = R[i * 3 + 2];
+        st.cur[i * 4 + 3] = t[i];
+        st.t_last[i] = t[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) st.R_last[i] = R[i];
+    double next[12];
+    compose(st.cur, st.applied, next);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) st.total[i] = next[i];
+    const bool converged = rd <= R_thr && td <= t_thr;        // main.py:153-154
+    if (converged || iteration + 1 >= max_iteration) {
+        st.status = converged ? PCP_ICP_CONVERGED : PCP_ICP_MAX_ITER;
+        st.active = 0;
+        atomicSub(n_active, 1);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) st.applied[i] = next[i];     // main.py:110 of the next pass
+    }
+}
+
+// ---- procrustes_transformation(A, B) of main.py:131-141 / icp_template.py:43-54 on given correspondences.
+// A, B: 3 x n float64, row-major (one COLUMN per point, the reference's layout).
+constexpr int kProcThreads = 256;
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(kProcThreads)
+procrustes_sum_kernel(const double *__restrict__ A, const double *__restrict__ B, long long n, double *__restrict__ partials) {
+    __shared__ double s_sum[kProcThreads / 32][kSums];
+    double acc[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) acc[i] = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double ax = A[i], ay = A[n + i], az = A[2 * n + i];
+        const double bx = B[i], by = B[n + i], bz = B[2 * n + i];
+        acc[0] += 1.0;
+        acc[1] += ax; acc[2] += ay; acc[3] += az;
+        acc[4] += bx; acc[5] += by; acc[6] += bz;
+        acc[7] += bx * ax; acc[8] += bx * ay; acc[9] += bx * az;
+        acc[10] += by * ax; acc[11] += by * ay; acc[12] += by * az;
+        acc[13] += bz * ax; acc[14] += bz * ay; acc[15] += bz * az;
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) {
+        const double v = warp_sum(acc[i]);
+        if (lane == 0) s_sum[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < kSums) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < kProcThreads / 32; ++w) v += s_sum[w][threadIdx.x];
+        partials[(long long)blockIdx.x * kSums + threadIdx.x] = v;
+    }
+}
+
+// out: R (9), t (3)
+__global__ void procrustes_solve_kernel(const double *__restrict__ partials, int n_blocks, double *__restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    double s = 0.0;
+    if (lane < kSums)
+        for (int b = 0; b < n_blocks; ++b) s += partials[(long long)b * kSums + lane];
+    double S[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) S[i] = __shfl_sync(kFullMask, s, i);
+    if (lane != 0) return;
+    const double M = S[0], inv = M > 0.0 ? 1.0 / M : 0.0;
+    const double am[3] = {S[1] * inv, S[2] * inv, S[3] * inv}, bm[3] = {S[4] * inv, S[5] * inv, S[6] * inv};
+    double H[9], R[9];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) H[i * 3 + j] = S[7 + i * 3 + j] - M * bm[i] * am[j];
+    polar_uvt(H, R);
+    for (int i = 0; i < 9; ++i) out[i] = R[i];
+    for (int i = 0; i < 3; ++i) out[9 + i] = bm[i] - (R[i * 3] * am[0] + R[i * 3 + 1] * am[1] + R[i * 3 + 2] * am[2]);
+}
+
+// sum over points of |b - (R a + t)|^2 -> partials[block]
+__global__ void __launch_bounds__(kProcThreads)
+procrustes_cost_kernel(const double *__restrict__ A, const double *__restrict__ B, long long n, const double *__restrict__ Rt,
+                       double *__restrict__ partials) {
+    __shared__ double s_sum[kProcThreads / 32];
+    double R[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) R[i] = Rt[i];
+    double acc = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double ax = A[i], ay = A[n + i], az = A[2 * n + i];
+        const double rx = B[i] - (R[0] * ax + R[1] * ay + R[2] * az + R[9]);
+        const double ry = B[n + i] - (R[3] * ax + R[4] * ay + R[5] * az + R[10]);
+        const double rz = B[2 * n + i] - (R[6] * ax + R[7] * ay + R[8] * az + R[11]);
+        acc += rx * rx + ry * ry + rz * rz;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double v = 0.0;
+        for (int w = 0; w < kProcThreads / 32; ++w) v += s_sum[w];
+        partials[blockIdx.x] = v;
+    }
+}
+
+}  // namespace
+
+int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t, double *h_cost) {
+    cudaStream_t st = ctx->stream;
+    const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((n + kProcThreads - 1) / kProcThreads, ctx->sm_count * 4));
+    DevBuf &b_part = ctx->scratch[0], &b_out = ctx->scratch[1];
+    PCP_TRY(b_part.ensure(sizeof(double) * kSums * (size_t)blocks));
+    PCP_TRY(b_out.ensure(sizeof(double) * 12));
+    procrustes_sum_kernel<<<blocks, kProcThreads, 0, st>>>(d_A, d_B, n, b_part.as<double>());
+    procrustes_solve_kernel<<<1, 32, 0, st>>>(b_part.as<double>(), blocks, b_out.as<double>());
+    procrustes_cost_kernel<<<blocks, kProcThreads, 0, st>>>(d_A, d_B, n, b_out.as<double>(), b_part.as<double>());
+    ctx->launches += 3;
+    PCP_CUDA(cudaGetLastError());
+    std::vector<double> h_part((size_t)blocks), h_out(12);
+    PCP_CUDA(cudaMemcpyAsync(h_out.data(), b_out.p, sizeof(double) * 12, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaMemcpyAsync(h_part.data(), b_part.p, sizeof(double) * (size_t)blocks, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaStreamSynchronize(st));
+    if (h_R) memcpy(h_R, h_out.data(), sizeof(double) * 9);
+    if (h_t) memcpy(h_t, h_out.data() + 9, sizeof(double) * 3);
+    if (h_cost) {
+        double c = 0.0;
+        for (double v : h_part) c += v;
+        *h_cost = std::sqrt(c);                       // np.linalg.norm(B - (R A + t 1^T)), main.py:141
+    }
+    return PCP_OK;
+}
+
+int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const float *d_src, const int64_t *h_src_off,
+                     const float *d_tgt, const int64_t *h_tgt_off, int64_t stride, const double *h_T_init,
+                     double *h_T_last, double *h_T_total, int32_t *h_iters, int32_t *h_status, double *h_log) {
+    if (P == 0) return PCP_OK;
+    if (P > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_icp_batch: too many pairs");
+    cudaStream_t st = ctx->stream;
+    const int max_it = prm.max_iteration;
+
+    // target hierarchies of all pairs in one segmented build (kept in the context between calls)
+    BatchIndex &tb = ctx->icp_targets;
+    tb.ctx = ctx;
+    PCP_TRY(batch_build_device(&tb, d_tgt, stride, P, h_tgt_off));
+
+    int64_t max_ns = 0;
+    for (int64_t p = 0; p < P; ++p) {
+        if (h_src_off[p + 1] < h_src_off[p]) return fail(PCP_ERR_INVALID, "pcp_icp_batch: src_offsets must be non-decreasing");
+        max_ns = std::max<int64_t>(max_ns, h_src_off[p + 1] - h_src_off[p]);
+    }
+    const int chunks = (int)std::max<int64_t>(1, (max_ns + kChunk - 1) / kChunk);
+
+    std::vector<IcpState> h_states((size_t)P);
+    for (int64_t p = 0; p < P; ++p) {
+        IcpState &s = h_states[(size_t)p];
+        memset(&s, 0, sizeof s);
+        double T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        if (h_T_init) memcpy(T, h_T_init + p * 16, sizeof T);
+        for (int i = 0; i < 12; ++i) s.applied[i] = s.cur[i] = s.total[i] = T[i];
+        for (int i = 0; i < 3; ++i) {                 // main.py:99-100
+            for (int j = 0; j < 3; ++j) s.R_last[i * 3 + j] = T[i * 4 + j];
+            s.t_last[i] = T[i * 4 + 3];
+        }
+        s.active = max_it > 0 ? 1 : 0;
+        s.status = PCP_ICP_MAX_ITER;
+    }
+    DevBuf &b_states = ctx->scratch[0], &b_part = ctx->scratch[1], &b_off = ctx->scratch[2], &b_log = ctx->scratch[3],
+           &b_act = ctx->scratch[4];
+    PCP_TRY(b_states.ensure(sizeof(IcpState) * (size_t)P));
+    PCP_TRY(b_part.ensure(sizeof(double) * kSums * (size_t)P * (size_t)chunks));
+    PCP_TRY(b_off.ensure(sizeof(long long) * (size_t)(P + 1)));
+    PCP_TRY(b_act.ensure(sizeof(int)));
+    double *d_log = nullptr;
+    if (h_log && max_it > 0) {
+        PCP_TRY(b_log.ensure(sizeof(double) * 2 * (size_t)P * (size_t)max_it));
+        d_log = b_log.as<double>();
+        PCP_CUDA(cudaMemsetAsync(d_log, 0xff, sizeof(double) * 2 * (size_t)P * (size_t)max_it, st));   // NaN fill
+    }
+    PCP_CUDA(cudaMemcpyAsync(b_states.p, h_states.data(), sizeof(IcpState) * (size_t)P, cudaMemcpyHostToDevice, st));
+    PCP_CUDA(cudaMemcpyAsync(b_off.p, h_src_off, sizeof(long long) * (size_t)(P + 1), cudaMemcpyHostToDevice, st));
+    int h_active = max_it > 0 ? (int)P : 0;
+    PCP_CUDA(cudaMemcpyAsync(b_act.p, &h_active, sizeof(int), cudaMemcpyHostToDevice, st));
+
+    int next_check = 1;
+    for (int it = 0; it < max_it && h_active > 0; ++it) {
+        for (int64_t p0 = 0; p0 < P; p0 += 65535) {
+            const unsigned gy = (unsigned)std::min<int64_t>(65535, P - p0);
+            icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
+                tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
+                b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+            ctx->launches += 1;
+        }
+        icp_solve_kernel<<<(unsigned)((P * 32 + 127) / 128), 128, 0, st>>>(
+            b_states.as<IcpState>(), b_part.as<double>(), b_off.as<long long>(), P, chunks, it, max_it, prm.R_diff_thres,
+            prm.t_diff_thres, prm.first_iter_broadcast, d_log, b_act.as<int>());
+        ctx->launches += 1;
+        if (it + 1 == next_check && it + 1 < max_it) {
+            // not on the data path: one word tells the host whether any pair still iterates
+            PCP_CUDA(cudaMemcpyAsync(&h_active, b_act.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+            PCP_CUDA(cudaStreamSynchronize(st));
+            next_check = next_check < 4 ? next_check + 1 : next_check + (next_check + 1) / 2;
+        }
+    }
+    PCP_CUDA(cudaGetLastError());
+    PCP_CUDA(cudaMemcpyAsync(h_states.data(), b_states.p, sizeof(IcpState) * (size_t)P, cudaMemcpyDeviceToHost, st));
+    if (d_log) PCP_CUDA(cudaMemcpyAsync(h_log, d_log, sizeof(double) * 2 * (size_t)P * (size_t)max_it, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaStreamSynchronize(st));
+    for (int64_t p = 0; p < P; ++p) {
+        const IcpState &s = h_states[(size_t)p];
+        const double bottom[4] = {0, 0, 0, 1};
+        if (h_T_last) { memcpy(h_T_last + p * 16, s.cur, sizeof s.cur); memcpy(h_T_last + p * 16 + 12, bottom, sizeof bottom); }
+        if (h_T_total) { memcpy(h_T_total + p * 16, s.total, sizeof s.total); memcpy(h_T_total + p * 16 + 12, bottom, sizeof bottom); }
+        if (h_iters) h_iters[p] = s.iters;
+        if (h_status) h_status[p] = s.status;
+    }
+    return PCP_OK;
+}
+
+}  // namespace pcp

@@ -53,6 +53,47 @@ constexpr int kMaxLevels = 8;      // 32^7 buckets > 2^31 points
 
 }  // namespace pcp
 
+
+namespace pcp {
+
+// One indexed cloud ("segment") as the kernels see it.  All pointers are already offset to the
+// segment's own sub-arrays, so the same device code serves a single index and one pair of a batch.
+//   pts       float4[n_leaf*32]  Morton-sorted points, .w = index bits (row within the segment); pad lanes NaN / -1
+//   box_lo/hi float4[nodes]      AABB per node, level 0 (buckets) first, then level 1 ... root last
+//   level_off[l] first node of level l in box_*; level_cnt[l] nodes on level l
+struct IndexView {
+    const float4 *pts;
+    const float4 *box_lo;
+    const float4 *box_hi;
+    const float *bbox;      // lo.xyz, cells per unit, hi.xyz, extent
+    long long src_off;      // first row of this segment in the source array handed to the build
+    long long n;
+    long long n_leaf;
+    int n_levels;           // number of levels incl. the bucket level; root = level n_levels-1
+    long long level_off[kMaxLevels];
+    long long level_cnt[kMaxLevels];
+};
+
+// Search structure over P independent clouds built in ONE pass (segmented Morton sort): P = 1 for
+// pcp_index, P = number of registration pairs for the ICP targets.  DESIGN.md section 3.
+struct BatchIndex {
+    pcp_ctx *ctx = nullptr;
+    int64_t P = 0;
+    int64_t total_n = 0, total_leaf = 0, total_nodes = 0;
+    int64_t max_n = 0, max_leaf = 0;
+    int max_levels = 0;
+    int64_t level_max_cnt[kMaxLevels] = {0};
+    std::vector<IndexView> h_views;
+    DevBuf pts, box_lo, box_hi, bbox, views, keys_a, keys_b, vals_a, vals_b;
+    const IndexView *d_views() const { return views.as<IndexView>(); }
+    void release();
+};
+
+// Build over rows [offsets[p], offsets[p+1]) of d_xyz for p < P (offsets: P+1 host values).
+int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_t P, const int64_t *h_offsets);
+
+}  // namespace pcp
+
 struct pcp_ctx {
     int device = 0;
     int sm_count = 0;
@@ -62,39 +103,21 @@ struct pcp_ctx {
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
     pcp::PinBuf pin[4];            // pinned staging for host<->device copies
     pcp::DevBuf counters;          // 8 x u64 work counters (pcp_ctx_enable_counters)
+    pcp::BatchIndex icp_targets;   // hierarchies of the ICP target clouds (pcp_icp_batch), reused across calls
     bool count_work = false;
     unsigned long long *ctr() const { return count_work ? counters.as<unsigned long long>() : nullptr; }
 };
 
-// Device layout of the search structure ("bucket hierarchy"):
-//   pts      float4[n_leaf*32]  Morton-sorted points, .w = original index bits; pad lanes are NaN / -1
-//   box_lo/hi float4[total_nodes] AABB per node, level 0 (buckets) first, then level 1 ... root last
-//   level_off[l] first node of level l in box_*; level_cnt[l] nodes on level l
 struct pcp_index {
     pcp_ctx *ctx = nullptr;
     int64_t n = 0;
-    int64_t n_leaf = 0;
-    int n_levels = 0;                      // number of levels incl. the bucket level; root = level n_levels-1
-    int64_t level_off[pcp::kMaxLevels] = {0};
-    int64_t level_cnt[pcp::kMaxLevels] = {0};
-    pcp::DevBuf pts, box_lo, box_hi, bbox; // bbox: 8 floats (lo xyz, hi xyz, scale, pad) on device
-    pcp::DevBuf keys_a, keys_b, vals_a, vals_b, src_copy;
+    pcp::BatchIndex b;       // P == 1
+    pcp::DevBuf src_copy;
 };
 
 namespace pcp {
 
-struct IndexView {
-    const float4 *pts;
-    const float4 *box_lo;
-    const float4 *box_hi;
-    const float *bbox;      // lo.xyz, inv cell size
-    long long n;
-    long long n_leaf;
-    int n_levels;
-    long long level_off[kMaxLevels];
-    long long level_cnt[kMaxLevels];
-};
-IndexView make_view(const pcp_index *ix);
+inline const IndexView &make_view(const pcp_index *ix) { return ix->b.h_views[0]; }
 
 // build (pcp_build.cu)
 int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride);
@@ -115,5 +138,8 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, c
                      const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,
                      const double *h_T_init, double *h_T_last, double *h_T_total, int32_t *h_iters,
                      int32_t *h_status, double *h_log);
+
+int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,
+                      double *h_cost);
 
 }  // namespace pcp

@@ -244,7 +244,7 @@ int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t
     if (ix->n == 0) return PCP_OK;
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
-    const long long n_work = ix->n_leaf * kLeaf;
+    const long long n_work = v.n_leaf * kLeaf;
     const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
     knn_warp_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist, d_count,
                                                                        ctx->ctr());

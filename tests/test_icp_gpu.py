@@ -1,0 +1,135 @@
+"""GPU parity: batched CUDA ICP (pybind11 -> C ABI -> pcp_icp.cu) vs the reference-generated golden
+vectors (Registration/main.py:icp_point2point run under an Open3D stand-in) and the float64 oracle.
+
+Tolerances (BASELINE.json north_star): rotation within 1e-4 rad, translation within 1e-4 m, identical
+iteration counts / status, for BOTH the last increment (what main.py:156 returns) and the composed pose
+(icp_template.py:198)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROT_TOL = 1e-4      # rad
+TRANS_TOL = 1e-4    # m
+
+
+@pytest.fixture(scope="module")
+def pcp():
+    import point_cloud_process_b200 as m
+    return m
+
+
+def pose_err(Ta, Tb):
+    dR = Ta[:3, :3] @ Tb[:3, :3].T
+    ang = float(np.arccos(np.clip((np.trace(dR) - 1.0) / 2.0, -1.0, 1.0)))
+    return ang, float(np.linalg.norm(Ta[:3, 3] - Tb[:3, 3]))
+
+
+def assert_pose(Ta, Tb, what=""):
+    ang, dt = pose_err(np.asarray(Ta), np.asarray(Tb))
+    assert ang <= ROT_TOL and dt <= TRANS_TOL, f"{what}: rotation {ang:.3e} rad, translation {dt:.3e} m"
+
+
+MODES = {"A": {}, "B": dict(max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6)}
+
+
+@pytest.mark.parametrize("name", ["a0", "a1", "a2", "a3", "a4", "a5"])
+@pytest.mark.parametrize("mode", ["A", "B"])
+def test_icp_golden(pcp, icp_golden, name, mode):
+    """Against the reference's own icp_point2point: last increment + final in-place source points."""
+    g = icp_golden
+    src, tgt, T0 = g[name + "/source"], g[name + "/target"], g[name + "/T_init"]
+    out = pcp.icp_batch([src], [tgt], T_init=T0[None], **MODES[mode])
+    assert_pose(out["T_last"][0], g[f"{name}/{mode}_T_last"], "last increment")
+    # the reference leaves `source` transformed by every pose it applied (main.py:110): T_total minus the last increment
+    applied = np.linalg.inv(out["T_last"][0]) @ out["T_total"][0] if out["status"][0] != 2 else out["T_total"][0]
+    moved = src.astype(np.float64) @ applied[:3, :3].T + applied[:3, 3]
+    assert np.abs(moved - g[f"{name}/{mode}_source_final"]).max() <= 2e-4
+
+
+def test_icp_failure_case(pcp, icp_golden):
+    g = icp_golden
+    out = pcp.icp_batch([g["fail/source"]], [g["fail/target"]], T_init=g["fail/T_init"][None])
+    assert out["status"][0] == 2 and out["iterations"][0] == 1      # PCP_ICP_FEW_PAIRS after one pass (main.py:125-127)
+    assert np.array_equal(out["T_last"][0], g["fail/A_T_last"])
+    assert np.array_equal(out["T_total"][0], g["fail/T_init"])
+
+
+@pytest.mark.parametrize("mode", ["A", "B"])
+def test_icp_batch_vs_oracle(pcp, mode):
+    """A ragged batch (different sizes, one perturbed init, one hopeless pair) in ONE call vs the float64
+    oracle pair by pair: iterations, status, both poses and the R_diff / t_diff log."""
+    from oracle import icp_oracle
+    specs = [(1000, 4000), (1001, 2500), (1002, 6000), (1003, 777), (1004, 3000), (1005, 5000)]
+    srcs, tgts, inits = [], [], []
+    for i, (seed, n) in enumerate(specs):
+        tgt, src, T_gt = icp_oracle.make_pair(seed, n=n, box=(30.0, 30.0, 5.0))
+        T0 = np.eye(4)
+        if i == 4:
+            T0 = T_gt.copy()
+            T0[:3, 3] += 0.05
+        srcs.append(src), tgts.append(tgt), inits.append(T0)
+    tgt, src, _ = icp_oracle.make_pair(1100, n=300, box=(5.0, 5.0, 2.0))
+    srcs.append(src + np.float32(100.0)), tgts.append(tgt), inits.append(np.eye(4))
+    kw = MODES[mode]
+    out = pcp.icp_batch(srcs, tgts, T_init=np.asarray(inits), want_log=True, **kw)
+    for p in range(len(srcs)):
+        T, info = icp_oracle.icp_point2point(srcs[p], tgts[p], inits[p], return_info=True, **kw)
+        assert out["iterations"][p] == info["iterations"], f"pair {p}"
+        want_status = 2 if info["status"] == 1 else (1 if (info["iterations"] == kw.get("max_iteration", 100) and not (
+            info["log"]["R_diff"][-1] <= kw.get("R_diff_thres", 0.5) and info["log"]["t_diff"][-1] <= kw.get("t_diff_thres", 0.5))) else 0)
+        assert out["status"][p] == want_status, f"pair {p}"
+        assert_pose(out["T_last"][p], T, f"pair {p} last increment")
+        assert_pose(out["T_total"][p], info["total"], f"pair {p} composed pose")
+        nlog = len(info["log"]["R_diff"])
+        log = out["diff_log"][p]
+        assert np.allclose(log[:nlog, 0], info["log"]["R_diff"], rtol=0, atol=2e-4)
+        assert np.allclose(log[:nlog, 1], info["log"]["t_diff"], rtol=0, atol=2e-4)
+        assert np.isnan(log[nlog:]).all()
+
+
+def test_icp_first_iteration_broadcast_switch(pcp):
+    """main.py:150: on iteration 1 t (3,1) - t_last (3,) broadcasts to 3x3; the flag reproduces / removes it."""
+    from oracle import icp_oracle
+    tgt, src, _ = icp_oracle.make_pair(1010, n=3000, box=(25.0, 25.0, 5.0))
+    a = pcp.icp_batch([src], [tgt], want_log=True)
+    b = pcp.icp_batch([src], [tgt], want_log=True, first_iter_broadcast=False)
+    T, info = icp_oracle.icp_point2point(src, tgt, np.eye(4), return_info=True)
+    assert abs(a["diff_log"][0][0, 1] - info["log"]["t_diff"][0]) < 1e-6
+    t = a["T_last"][0][:3, 3] if a["iterations"][0] == 1 else None
+    # without the quirk the first t_diff is the plain norm, which is sqrt(3) times smaller for t_last = 0
+    assert abs(b["diff_log"][0][0, 1] * np.sqrt(3.0) - a["diff_log"][0][0, 1]) < 1e-9
+    assert t is None or abs(np.linalg.norm(t) - b["diff_log"][0][0, 1]) < 1e-9
+
+
+def test_icp_pose_accuracy_mode_b(pcp):
+    """SURVEY 8(d) C4 Mode B at the full 20 000-point size: converges to the ground truth."""
+    from oracle import icp_oracle
+    tgt, src, T_gt = icp_oracle.make_pair(1000, n=20000)
+    out = pcp.icp_batch([src], [tgt], max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6)
+    ang, dt = pose_err(out["T_total"][0], T_gt)
+    assert ang < 2e-4 and dt < 2e-3, (ang, dt)
+    T, info = icp_oracle.icp_point2point(src, tgt, np.eye(4), max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6,
+                                         return_info=True)
+    assert out["iterations"][0] == info["iterations"]
+    assert_pose(out["T_total"][0], info["total"], "composed pose")
+
+
+def test_icp_edge_cases(pcp):
+    e = np.zeros((0, 3), np.float32)
+    out = pcp.icp_batch([], [])
+    assert out["T_last"].shape == (0, 4, 4)
+    rng = np.random.default_rng(0)
+    pts = rng.random((100, 3)).astype(np.float32)
+    out = pcp.icp_batch([e, pts], [pts, e])          # empty source / empty target -> too few associations
+    assert out["status"].tolist() == [2, 2] and out["iterations"].tolist() == [1, 1]
+    out = pcp.icp_batch([pts], [pts])                # identical clouds -> identity in one pass
+    assert out["status"][0] == 0 and np.allclose(out["T_last"][0], np.eye(4), atol=1e-12)
+    with pytest.raises(ValueError):
+        pcp.icp_batch([pts], [pts, pts])
+
+
+def test_homo2tq_golden(pcp, icp_golden):
+    g = icp_golden
+    got = np.asarray([pcp.native.homo2tq(M) for M in g["quat/homo"]])
+    assert np.array_equal(got, g["quat/tq"])
