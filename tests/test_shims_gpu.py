@@ -1,0 +1,156 @@
+"""GPU: the drop-in Python modules (same names / call shapes as Kdtree_Octree/lesson2/*.py and
+Registration/main.py, icp_template.py) against the reference-generated golden vectors."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pcp():
+    import point_cloud_process_b200 as m
+    return m
+
+
+def test_lesson2_call_sequence_known_answer(pcp, kitti):
+    """The benchmark.py:119-131 call sequence on the N x 3 scan; SURVEY Appendix A.1 known answer."""
+    from point_cloud_process_b200 import kdtree, octree
+    from point_cloud_process_b200.result_set import KNNResultSet, RadiusNNResultSet
+    db_np = kitti
+    query = db_np[0, :]
+    for build, knn, rad in ((lambda: kdtree.kdtree_construction(db_np, 32), kdtree.kdtree_knn_search, kdtree.kdtree_radius_search),
+                            (lambda: octree.octree_construction(db_np, 32, 0.0001), octree.octree_knn_search, octree.octree_radius_search),
+                            (lambda: octree.octree_construction(db_np, 32, 0.0001), octree.octree_knn_search, octree.octree_radius_search_fast)):
+        root = build()
+        rs = KNNResultSet(capacity=8)
+        ret = knn(root, db_np, rs, query)
+        assert ret is False or isinstance(ret, bool)
+        assert [d.index for d in rs.dist_index_list] == [0, 3943, 5884, 3944, 5885, 1, 5883, 1966]
+        assert np.array_equal(np.float32([d.distance for d in rs.dist_index_list]),
+                              np.float32([0, .37504396, .62682277, .78833336, .8193119, .86983556, .8800213, .9055708]))
+        assert rs.full() and rs.size() == 8 and rs.worstDist() == np.float32(.9055708)
+        assert str(rs).splitlines()[0] == "0 - 0.00"
+        rr = RadiusNNResultSet(radius=1)
+        rad(root, db_np, rr, query)
+        assert rr.size() == 10 and len(rr.dist_index_list) == 10
+        assert "In total 10 neighbors within 1.000000." in str(rr)
+    assert kdtree.kdtree_knn_search(kdtree.kdtree_construction(db_np, 32), db_np, KNNResultSet(3), query) is False
+
+
+@pytest.mark.parametrize("name", ["kitti", "uniform", "fewer_than_k", "single_point"])
+def test_shim_per_query_vs_golden(pcp, knn_golden, kitti, name):
+    from point_cloud_process_b200 import kdtree, octree
+    from point_cloud_process_b200.result_set import KNNResultSet, RadiusNNResultSet
+    g = knn_golden
+    db = kitti if name.startswith("kitti") else g[name + "/db"]
+    q, k, r = g[name + "/queries"], int(g[name + "/k"]), float(g[name + "/r"])
+    kd = kdtree.kdtree_construction(db, int(g[name + "/leaf_size"]))
+    oc = octree.octree_construction(db, int(g[name + "/leaf_size"]), 0.0001)
+    go = g[name + "/kd_rad_off"]
+    for i in range(min(len(q), 40)):
+        for root, fn in ((kd, kdtree.kdtree_knn_search), (oc, octree.octree_knn_search)):
+            rs = KNNResultSet(k)
+            fn(root, db, rs, q[i])
+            assert rs.count == g[name + "/kd_knn_cnt"][i]
+            assert np.array_equal(np.float32([d.distance for d in rs.dist_index_list]), g[name + "/kd_knn_dist"][i])
+            d = g[name + "/kd_knn_dist"][i]
+            if len(set(d[:rs.count].tolist())) == rs.count and rs.count < k:
+                assert [x.index for x in rs.dist_index_list] == g[name + "/kd_knn_idx"][i].tolist()
+        rr = RadiusNNResultSet(r)
+        kdtree.kdtree_radius_search(kd, db, rr, q[i])
+        assert sorted(d.index for d in rr.dist_index_list) == sorted(g[name + "/kd_rad_idx"][go[i]:go[i + 1]].tolist())
+
+
+def test_unchanged_driver_style_script_via_pythonpath(pcp, tmp_path):
+    """A driver written like benchmark.py (top-level `import kdtree, octree`, `from result_set import ...`)
+    picks up the GPU modules when the shims directory is on PYTHONPATH (SURVEY 8b launch recipe)."""
+    script = tmp_path / "driver.py"
+    script.write_text(
+        "import numpy as np, sys\n"
+        "import octree as octree\nimport kdtree as kdtree\n"
+        "from result_set import KNNResultSet, RadiusNNResultSet\n"
+        f"db_np = np.fromfile(r'{os.path.join(ROOT, 'tests', 'golden', 'kitti_000000_xyz.f32')}', np.float32).reshape(-1, 3)\n"
+        "root = octree.octree_construction(db_np, 32, 0.0001)\n"
+        "rs = KNNResultSet(capacity=8); octree.octree_knn_search(root, db_np, rs, db_np[0, :])\n"
+        "root = kdtree.kdtree_construction(db_np, 32)\n"
+        "rs2 = KNNResultSet(capacity=8); kdtree.kdtree_knn_search(root, db_np, rs2, db_np[0, :])\n"
+        "rr = RadiusNNResultSet(radius=1); kdtree.kdtree_radius_search(root, db_np, rr, db_np[0, :])\n"
+        "print([d.index for d in rs.dist_index_list], [d.index for d in rs2.dist_index_list], rr.size(), kdtree.__name__)\n")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([os.path.join(ROOT, "point_cloud_process_b200", "shims"), ROOT]))
+    out = subprocess.run([sys.executable, "-P", str(script)], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout.strip() == ("[0, 3943, 5884, 3944, 5885, 1, 5883, 1966] [0, 3943, 5884, 3944, 5885, 1, 5883, 1966] 10 kdtree")
+
+
+class FakeCloud:
+    """Open3D-like PointCloud: .points float64 (N,3), .transform(T) in place (main.py:110)."""
+
+    def __init__(self, pts):
+        self.points = np.array(pts, dtype=np.float64)
+
+    def transform(self, T):
+        self.points[:] = self.points @ T[:3, :3].T + T[:3, 3]
+        return self
+
+
+@pytest.mark.parametrize("name", ["a0", "a4"])
+@pytest.mark.parametrize("mode", ["A", "B"])
+def test_icp_point2point_drop_in(pcp, icp_golden, name, mode):
+    from point_cloud_process_b200 import icp
+    g = icp_golden
+    kw = {} if mode == "A" else dict(max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6)
+    source, target = FakeCloud(g[name + "/source"]), FakeCloud(g[name + "/target"])
+    T = icp.icp_point2point(source, target, g[name + "/T_init"], **kw)
+    assert T.shape == (4, 4) and np.array_equal(T[3], [0, 0, 0, 1])
+    assert np.abs(T - g[f"{name}/{mode}_T_last"]).max() < 1e-4
+    assert np.abs(source.points - g[f"{name}/{mode}_source_final"]).max() < 2e-4      # in-place side effect of main.py:110
+    tq = icp.homo2tq(T)
+    assert len(tq) == 7 and abs(np.linalg.norm(tq[3:]) - 1) < 1e-9
+
+
+def test_icp_template_contract(pcp):
+    from oracle import icp_oracle
+    from point_cloud_process_b200 import icp
+    tgt, src, T_gt = icp_oracle.make_pair(1003, n=3000, box=(25.0, 25.0, 5.0))
+    kw = dict(max_iteration=40, R_diff_thres=1e-5, t_diff_thres=1e-5)
+    total, log = icp.ICP(src.T, tgt.T, **kw)                      # 3 x N arrays (read_oxford_bin layout)
+    assert set(log) == {"R_diff", "t_diff"} and len(log["R_diff"]) == len(log["t_diff"]) >= 2
+    dR = total[:3, :3] @ T_gt[:3, :3].T
+    assert np.arccos(np.clip((np.trace(dR) - 1) / 2, -1, 1)) < 1e-3 and np.linalg.norm(total[:3, 3] - T_gt[:3, 3]) < 5e-3
+    # find_associations / procrustes_transformation vs the oracle restatement
+    from scipy.spatial import cKDTree
+    a = icp.find_associations(src.T.astype(np.float64), pcp.SearchIndex(tgt))
+    b = icp_oracle.find_associations(src.T.astype(np.float64), cKDTree(tgt.astype(np.float64)))
+    assert a.shape == b.shape and (a == b).mean() > 0.999
+    A, B = src[a[:, 0]].T.astype(np.float64), tgt[a[:, 1]].T.astype(np.float64)
+    R, t, cost = icp.procrustes_transformation(A, B)
+    Ro, to, co = icp_oracle.procrustes_transformation(A, B)
+    assert R.shape == (3, 3) and t.shape == (3, 1)
+    assert np.abs(R - Ro).max() < 1e-10 and np.abs(t - to).max() < 1e-8 and abs(cost - co) < 1e-6 * co
+
+
+def test_register_pairs_writes_reg_result(pcp, tmp_path):
+    """C2 flow: pair list -> batched ICP -> reg_result.txt rows identical to the oracle's after %f formatting."""
+    from oracle import icp_oracle
+    from point_cloud_process_b200 import icp
+    pair_ids = [(643, 456), (0, 456), (645, 189), (12, 7)]
+    srcs, tgts, rows_o = [], [], []
+    for j, (trg, src_id) in enumerate(pair_ids):
+        tgt, src, _ = icp_oracle.make_pair(7000 + j, n=2500, box=(25.0, 25.0, 5.0))
+        srcs.append(src), tgts.append(tgt)
+        T = icp_oracle.icp_point2point(src, tgt, np.eye(4))
+        rows_o.append([trg, src_id, *icp_oracle.homo2tq(T)])
+    path = tmp_path / "reg_result.txt"
+    rows, out = icp.register_pairs(srcs, tgts, np.tile(np.eye(4), (4, 1, 1)), pair_ids, out_path=path)
+    assert np.abs(rows - np.asarray(rows_o)).max() < 1e-5
+    got, want = path.read_text().splitlines(), icp_oracle.format_reg_result(rows_o).splitlines()
+    assert got[0] == want[0] and len(got) == len(want) == 5
+    for a, b in zip(got[1:], want[1:]):
+        fa, fb = np.float64(a.split(",")), np.float64(b.split(","))
+        assert np.abs(fa - fb).max() <= 1.01e-6            # equal after %f formatting up to one rounding step
