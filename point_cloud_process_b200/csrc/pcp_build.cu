@@ -204,6 +204,8 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         v.n = n;
         v.n_leaf = (n + kLeaf - 1) / kLeaf;
         v.n_levels = 0;
+        // a non-empty segment always has a root ABOVE the bucket level (n_levels >= 2), so the
+        // search kernels have a single traversal loop and a single bucket-scan site
         long long cnt = v.n_leaf, off = 0;
         while (cnt > 0) {
             if (v.n_levels >= kMaxLevels) return fail(PCP_ERR_UNSUPPORTED, "index build: hierarchy too deep");
@@ -212,7 +214,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
             b->level_max_cnt[v.n_levels] = std::max<int64_t>(b->level_max_cnt[v.n_levels], cnt);
             ++v.n_levels;
             off += cnt;
-            if (cnt == 1) break;
+            if (cnt == 1 && v.n_levels >= 2) break;
             cnt = (cnt + kFan - 1) / kFan;
         }
         // pointers are patched below once the arrays are sized: keep element offsets for now

@@ -12,6 +12,8 @@
 // expression, and the few candidates inside the gate are inserted with ballot + shfl_up.  The first
 // bucket is bitonic-sorted straight into the list.
 #include <cfloat>
+#include <cstdlib>
+#include <cstring>
 
 #include "pcp_device.cuh"
 #include "pcp_internal.cuh"
@@ -219,11 +221,30 @@ __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, in
 
 }  // namespace
 
+int knn_kernel_choice() {
+    static const int choice = [] {
+        const char *e = getenv("PCP_KNN_KERNEL");
+        if (!e) return 0;
+        return strcmp(e, "warp") == 0 ? 1 : strcmp(e, "tile") == 0 ? 2 : 0;
+    }();
+    return choice;
+}
+
+// Below this many queries the warp-per-query kernel wins: it needs no query sort and exposes 32x more warps.
+constexpr int64_t kTileMinQueries = 8192;
+
 int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
                int32_t *d_idx, float *d_dist, int32_t *d_count) {
     (void)d_perm;
     if (nq == 0) return PCP_OK;
     pcp_ctx *ctx = ix->ctx;
+    const int choice = knn_kernel_choice();
+    if (ix->n > 0 && (choice == 2 || (choice == 0 && nq >= kTileMinQueries))) {
+        // group queries by Morton order in the index's frame, 32 per warp
+        PCP_TRY(ctx->scratch[3].ensure(sizeof(uint32_t) * (size_t)nq));
+        PCP_TRY(sort_queries(ix, d_q, nq, stride, ctx->scratch[3].as<uint32_t>()));
+        return knn_tile_device(ix, d_q, nq, stride, ctx->scratch[3].as<uint32_t>(), k, d_idx, d_dist, d_count);
+    }
     if (ix->n == 0) {   // empty cloud: every KNNResultSet stays as constructed
         long long tot = std::max<long long>(nq * k, nq);
         fill_empty_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, ctx->stream>>>(nq, k, d_idx, d_dist, d_count);
@@ -243,6 +264,8 @@ int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, cons
 int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
     if (ix->n == 0) return PCP_OK;
     pcp_ctx *ctx = ix->ctx;
+    const int choice = knn_kernel_choice();
+    if (choice == 2 || (choice == 0 && ix->n >= kTileMinQueries)) return knn_tile_self_device(ix, k, d_idx, d_dist, d_count);
     const IndexView v = make_view(ix);
     const long long n_work = v.n_leaf * kLeaf;
     const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
