@@ -68,6 +68,83 @@ def make_workload(name, rank):
     raise SystemExit(f"unknown workload {name}")
 
 
+def make_pair(seed, n=20000, box=(60.0, 60.0, 5.0), max_rot_deg=(2.0, 2.0, 5.0), max_t=0.5, noise=0.01):
+    """SURVEY 8(d) C4 recipe (same stream as the test-suite generator): seeded synthetic registration pair."""
+    rng = np.random.default_rng(seed)
+    target = (rng.random((n, 3)) * np.asarray(box)).astype(np.float32)
+    c = target.astype(np.float64).mean(0)
+    ang = np.deg2rad(rng.uniform(-1, 1, 3) * np.asarray(max_rot_deg))
+    cx, cy, cz = np.cos(ang)
+    sx, sy, sz = np.sin(ang)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    R = Rz @ Ry @ Rx
+    t = rng.uniform(-max_t, max_t, 3)
+    source = (target.astype(np.float64) - c - t) @ R + c + rng.normal(0, noise, (n, 3))
+    source = source[rng.permutation(n)].astype(np.float32)
+    return target, source
+
+
+ICP_MODES = {"A": dict(max_iteration=100, R_diff_thres=0.5, t_diff_thres=0.5),          # main.py:98-102 as shipped
+             "B": dict(max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6)}        # converging variant
+
+
+def measure_icp(torch, native, ctx, stream, first_pair, n_pairs, n_pts, mode, steps, warmup, e2e=True):
+    """Batched ICP over `n_pairs` synthetic pairs (ids first_pair ...): device-resident pairs/s and, through the
+    host-buffer API, end-to-end pairs/s."""
+    tg, sr = [], []
+    for i in range(n_pairs):
+        t, s = make_pair(1000 + first_pair + i, n=n_pts)
+        tg.append(t), sr.append(s)
+    off = np.arange(n_pairs + 1, dtype=np.int64) * n_pts
+    h_src, h_tgt = np.concatenate(sr), np.concatenate(tg)
+    d_src, d_tgt = torch.from_numpy(h_src).cuda(), torch.from_numpy(h_tgt).cuda()
+    prm = ICP_MODES[mode]
+    args = (prm["max_iteration"], prm["R_diff_thres"], prm["t_diff_thres"], 5.0, True)
+
+    def run():
+        return native.icp_batch_device(ctx, d_src.data_ptr(), off, d_tgt.data_ptr(), off, 3, *args)
+    for _ in range(warmup):
+        out = run()
+    ctx.synchronize()
+    l0 = ctx.launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in evs:
+        a.record(stream)
+        out = run()
+        b.record(stream)
+    ctx.synchronize()
+    ms = [a.elapsed_time(b) for a, b in evs]
+    res = {"pairs": n_pairs, "points_per_cloud": n_pts, "mode": mode, "device_ms_per_batch": float(np.mean(ms)),
+           "device_total_ms": float(np.sum(ms)), "steps": steps, "launches_per_batch": (ctx.launch_count() - l0) / steps,
+           "iterations_hist": np.bincount(out["iterations"]).tolist(), "status_hist": np.bincount(out["status"], minlength=3).tolist()}
+    if e2e:
+        T0 = np.tile(np.eye(4), (n_pairs, 1, 1))
+        p_src, p_tgt = torch.from_numpy(h_src).pin_memory().numpy(), torch.from_numpy(h_tgt).pin_memory().numpy()
+        native.icp_batch(ctx, p_src, off, p_tgt, off, T0, *args, False)
+        t0 = time.perf_counter()
+        reps = max(1, min(steps, 3))
+        for _ in range(reps):
+            native.icp_batch(ctx, p_src, off, p_tgt, off, T0, *args, False)
+        res["e2e_ms_per_batch"] = 1e3 * (time.perf_counter() - t0) / reps
+        res["e2e_h2d_bytes"] = int(h_src.nbytes + h_tgt.nbytes)
+    return res
+
+
+def cpu_icp_port(n_pairs, n_pts, mode, first_pair=0):
+    """oracle port of icp_point2point (float64 numpy + cKDTree), one core."""
+    from oracle import icp_oracle
+    t_total, its = 0.0, []
+    for i in range(n_pairs):
+        t, s = make_pair(1000 + first_pair + i, n=n_pts)
+        t0 = time.perf_counter()
+        _, info = icp_oracle.icp_point2point(s, t, np.eye(4), return_info=True, **ICP_MODES[mode])
+        t_total += time.perf_counter() - t0
+        its.append(info["iterations"])
+    return n_pairs / t_total, its
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -176,6 +253,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti_knn8")
+    ap.add_argument("--icp-pairs", type=int, default=256, help="pairs per rank of the secondary ICP measurement (0 = skip)")
+    ap.add_argument("--icp-points", type=int, default=20000)
+    ap.add_argument("--icp-mode", default="A", choices=["A", "B"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     args = ap.parse_args()
@@ -300,13 +380,32 @@ def main():
            "d2h_bytes_per_step": n * k * 8 + n * 4, "steps": Ke, "ms_per_step": 1e3 * t_e2e / Ke,
            "timer": "host perf_counter around synchronous C-ABI calls (PCP_HOST mode)"}
 
+    # ---- second half of the metric: batched ICP pairs/s (SURVEY C4 recipe; pairs sharded across ranks, no collective)
+    also = {}
+    if args.icp_pairs > 0:
+        r = measure_icp(torch, native, ctx, stream, rank * args.icp_pairs, args.icp_pairs, args.icp_points, args.icp_mode,
+                        steps=3, warmup=1)
+        t_dev, t_e2e = r["device_total_ms"], r["e2e_ms_per_batch"]
+        if dist is not None:
+            t = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_dev, t_e2e = float(t[0].item()), float(t[1].item())
+        also = {"metric": "ICP pairs/s", "value": world * args.icp_pairs * r["steps"] / (t_dev * 1e-3), "unit": "pairs/s",
+                "e2e_value": world * args.icp_pairs / (t_e2e * 1e-3), "scaling": "weak",
+                "config": {"workload": f"{args.icp_pairs} synthetic pairs per rank x {args.icp_points} pts (SURVEY C4 recipe), "
+                                       f"mode {args.icp_mode} ({ICP_MODES[args.icp_mode]})"}, "rank0": r}
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            v, its = cpu_icp_port(2, args.icp_points, args.icp_mode)
+            also["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": 1, "kind": "port",
+                                    "sample": f"2 pairs, float64 numpy + cKDTree restatement of main.py:97-156, iterations {its}"}
+
     line = {
         "metric": "kNN queries/s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "KITTI scan bundled with the reference (tests/golden copy)" if args.workload.startswith("kitti") else "synthetic",
         "config": {"workload": args.workload, "desc": w["desc"], "step": "index build + kNN of every point",
                    "l2": "flushed between timed steps (256 MB write)", "multi_gpu": "one independent scan per rank, no collective"},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "also": also,
         "breakdown_ms": {"build": statistics.mean(build_ms), "knn": statistics.mean(knn_ms),
                          "step_median": statistics.median(step_ms), "wall_region_ms_per_step": 1e3 * t_wall / K},
     }

@@ -106,29 +106,38 @@ __device__ __forceinline__ void scan_bucket(QueryState &st, const IndexView &ix,
     st.gate = d2_gate(key_dist(shfl64(st.key, k - 1)));
 }
 
-template <bool SELF>
+// LIST = false: warp w of the grid takes query w (SELF: sorted slot w).
+// LIST = true:  persistent warps drain the overflow list of the tiled kernel (pcp_knn_tile.cu): list[0] = number
+//               of groups, list[1..] = group ids; warp item w -> query lane (w % 32) of group list[1 + w / 32].
+template <bool SELF, bool LIST>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, int k,
                 int *__restrict__ out_idx, float *__restrict__ out_dist, int *__restrict__ out_cnt,
-                unsigned long long *__restrict__ ctr) {
+                unsigned long long *__restrict__ ctr, const unsigned *__restrict__ list,
+                const unsigned *__restrict__ perm) {
     // per-level traversal state: lane j keeps the pending lower bound of child j of the open node
     __shared__ unsigned s_lb[kWarpsPerCta][kMaxLevels][32];
     __shared__ unsigned s_cd[kWarpsPerCta][kMaxLevels][32];   // squared distance to the child's box centre
     __shared__ unsigned s_node[kWarpsPerCta][kMaxLevels];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long wid = blockIdx.x * (long long)kWarpsPerCta + warp;
-    const long long n_work = SELF ? ix.n_leaf * kLeaf : nq;
-    if (wid >= n_work) return;
-
+    const long long n_work = LIST ? (long long)list[0] * 32 : (SELF ? ix.n_leaf * kLeaf : nq);
+    for (long long item = blockIdx.x * (long long)kWarpsPerCta + warp; item < n_work;
+         item += LIST ? gridDim.x * (long long)kWarpsPerCta : n_work) {
+    long long wid = item;
+    if (LIST) wid = (long long)list[1 + (item >> 5)] * 32 + (item & 31);    // slot (SELF) / sorted position
     QueryState st;
     long long qid = wid;
     if (SELF) {
         const float4 p = __ldg(ix.pts + wid);
         st.qx = p.x; st.qy = p.y; st.qz = p.z;
         qid = (long long)(int)__float_as_uint(p.w);
-        if (qid < 0) return;                       // pad slot of the last bucket (whole warp exits)
+        if (qid < 0) continue;                     // pad slot of the last bucket (whole warp skips)
     } else {
-        const float *q = queries + wid * stride;
+        if (LIST) {
+            if (wid >= nq) continue;
+            qid = perm ? (long long)perm[wid] : wid;
+        }
+        const float *q = queries + qid * stride;
         st.qx = __ldg(q); st.qy = __ldg(q + 1); st.qz = __ldg(q + 2);
     }
     st.gate = __int_as_float(0x7f800000);
@@ -211,6 +220,8 @@ knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long
         const int cnt = __popc(__ballot_sync(kFullMask, filled && lane < k));
         if (lane == 0) out_cnt[qid] = cnt;
     }
+    __syncwarp();
+    }
 }
 
 __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, int *cnt) {
@@ -220,6 +231,23 @@ __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, in
 }
 
 }  // namespace
+
+// Overflow groups of the tiled kernel, one warp per query, persistent grid.
+int knn_warp_list_device(pcp_index *ix, bool self, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
+                         const uint32_t *d_list, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    pcp_ctx *ctx = ix->ctx;
+    const IndexView v = make_view(ix);
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    if (self)
+        knn_warp_kernel<true, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
+                                                                                d_count, ctx->ctr(), d_list, nullptr);
+    else
+        knn_warp_kernel<false, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
+                                                                                 d_count, ctx->ctr(), d_list, d_perm);
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
 
 int knn_kernel_choice() {
     static const int choice = [] {
@@ -254,8 +282,8 @@ int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, cons
     }
     const IndexView v = make_view(ix);
     const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-    knn_warp_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist, d_count,
-                                                                        ctx->ctr());
+    knn_warp_kernel<false, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
+                                                                               d_count, ctx->ctr(), nullptr, nullptr);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
@@ -269,8 +297,8 @@ int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t
     const IndexView v = make_view(ix);
     const long long n_work = v.n_leaf * kLeaf;
     const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
-    knn_warp_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist, d_count,
-                                                                       ctx->ctr());
+    knn_warp_kernel<true, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
+                                                                              d_count, ctx->ctr(), nullptr, nullptr);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;

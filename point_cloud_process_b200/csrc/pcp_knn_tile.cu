@@ -13,6 +13,7 @@
 //
 // Query groups: for pcp_knn_self the buckets themselves (Morton-sorted cloud); for arbitrary query
 // sets the queries are first sorted by their Morton code in the index's frame (sort_queries).
+#include <algorithm>
 #include <cfloat>
 #include <cstdio>
 #include <cstdlib>
@@ -28,6 +29,12 @@ namespace {
 constexpr int kTileWarps = 4;
 constexpr unsigned kDone = 0xffffffffu;
 constexpr unsigned kInfBits = 0x7f800000u;
+// Work budget of one group, per result slot K, before it is handed to the warp-per-query kernel.  It only
+// applies when the whole grid fits in about two waves of resident warps (e.g. the 124 668-point KITTI scan =
+// 3 896 groups): there the kernel lasts as long as its slowest group, and the sparse outlier groups (a box far
+// larger than its queries' neighbourhoods) are 8x the mean.  Larger inputs run unbounded.
+constexpr unsigned kScansPerSlot = 4;
+constexpr unsigned kTestsPerSlot = 12;
 
 template <int K>
 struct TopK {
@@ -51,12 +58,19 @@ struct TopK {
     }
 };
 
+// group-box lower bound of bucket c of the open level-1 node, from the boxes kept in shared memory
+__device__ __forceinline__ unsigned lbs_bound(const float4 *boxes, const float3 &glo, const float3 &ghi, int c) {
+    return __float_as_uint(boxbox_lb2(glo, ghi, boxes[2 * c], boxes[2 * c + 1]));
+}
+
 template <int K, bool SELF>
 __global__ void __launch_bounds__(kTileWarps * 32)
 knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm, long long nq,
                 long long stride, int k, int *__restrict__ out_idx, float *__restrict__ out_dist,
-                int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg) {
+                int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg,
+                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests) {
     __shared__ float4 s_tile[kTileWarps][32];
+    __shared__ float4 s_box[kTileWarps][64];
     __shared__ unsigned s_lb[kTileWarps][kMaxLevels][32];
     __shared__ unsigned s_cd[kTileWarps][kMaxLevels][32];
     __shared__ unsigned s_node[kTileWarps][kMaxLevels];
@@ -92,17 +106,21 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     float gate = active ? __uint_as_float(kInfBits) : -1.f;     // squared-distance gate of this lane (inactive: nothing passes)
     unsigned group_gate = kInfBits;                             // bits of the loosest gate in the group
     unsigned n_scan = 0, n_open = 0, n_test = 0, n_round = 0;
+    bool aborted = false;
     const unsigned n_active = __popc(__ballot_sync(kFullMask, active));
 
     float4 *tile = s_tile[warp];
-    auto scan_bucket = [&](long long leaf) {
+    float4 *boxes = s_box[warp];            // boxes of the 32 buckets below the open level-1 node: [2*c] = lo, [2*c+1] = hi
+    // Exact per-lane lower bound against bucket c's box (shared-memory broadcast): can ANY lane still use it?
+    auto bucket_needed = [&](int c) -> bool {
         ++n_test;
-        // per-lane exact lower bound against the bucket box: skip the bucket when no lane can use it
-        const float4 blo = __ldg(ix.box_lo + leaf), bhi = __ldg(ix.box_hi + leaf);
-        if (__ballot_sync(kFullMask, box_lb2(qx, qy, qz, blo, bhi) <= gate) == 0) return;
+        return __ballot_sync(kFullMask, box_lb2(qx, qy, qz, boxes[2 * c], boxes[2 * c + 1]) <= gate) != 0;
+    };
+    // Scan one bucket whose points `pv` (lane j = point j) are already in registers.
+    auto scan_bucket = [&](const float4 pv) {
         ++n_scan;
         __syncwarp();
-        tile[lane] = __ldg(ix.pts + leaf * kLeaf + lane);
+        tile[lane] = pv;
         __syncwarp();
         unsigned mask = 0;
 #pragma unroll
@@ -146,39 +164,74 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                 bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
                 const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
                 cbits = __float_as_uint(cx * cx + cy * cy + cz * cz);   // ordering hint only, never used to prune
+                if (lv == 1) { boxes[2 * lane] = lo; boxes[2 * lane + 1] = hi; }
             }
             lbs[lv][lane] = bits;
             cds[lv][lane] = cbits;
             __syncwarp();
         };
-        int level = top_level;
-        open_node(top_level, 0u);
-        while (true) {
-            const unsigned mine = lbs[level][lane];
+        // nearest unvisited child of the open node on `lv` that can still matter: -1 if none.  Marks it visited.
+        auto pick = [&](int lv) -> int {
+            const unsigned mine = lbs[lv][lane];
             const unsigned best = __reduce_min_sync(kFullMask, mine);
             // exact prune: every point below a child is at least `best` away from every query of the group
-            if (best == kDone || best > group_gate) {
-                if (level == top_level) break;
-                ++level;
-                continue;
-            }
+            if (best == kDone || best > group_gate) return -1;
             unsigned tie = __ballot_sync(kFullMask, mine == best);
             if (tie & (tie - 1)) {   // several children at the same bound (typically 0: they overlap the group box)
-                const unsigned cd = (mine == best) ? cds[level][lane] : kDone;
+                const unsigned cd = (mine == best) ? cds[lv][lane] : kDone;
                 const unsigned cbest = __reduce_min_sync(kFullMask, cd);
                 tie = __ballot_sync(kFullMask, cd == cbest);
             }
             const int sel = __ffs(tie) - 1;
-            if (lane == sel) lbs[level][lane] = kDone;
-            const unsigned child = nodes[level] * kFan + sel;
+            if (lane == sel) lbs[lv][lane] = kDone;
             __syncwarp();
-            if (level == 1) {
-                scan_bucket(child);
-            } else {
+            return sel;
+        };
+        int level = top_level;
+        open_node(top_level, 0u);
+        while (true) {
+            int sel = pick(level);
+            if (sel < 0) {
+                if (level == top_level) break;
+                ++level;
+                continue;
+            }
+            if (level > 1) {
+                const unsigned child = nodes[level] * kFan + sel;
                 --level;
                 open_node(level, child);
+                continue;
             }
+            // level 1: buckets.  Software pipeline: the points of the NEXT needed bucket in visiting order are
+            // loaded while the current one is scanned (the order depends only on the box bounds; the gates only
+            // shrink, so a bucket rejected now stays rejected).
+            const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
+            while (sel >= 0 && !bucket_needed(sel)) sel = pick(1);
+            if (sel < 0) continue;
+            float4 cur = __ldg(base + sel * kLeaf);
+            while (true) {
+                int nxt = pick(1);
+                while (nxt >= 0 && !bucket_needed(nxt)) nxt = pick(1);
+                float4 pf = cur;
+                if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
+                scan_bucket(cur);
+                if (nxt < 0) break;
+                sel = nxt;
+                cur = pf;
+                if (n_scan > max_scans || n_test > max_tests) break;
+            }
+            if (n_scan > max_scans || n_test > max_tests) { aborted = true; break; }
         }
+    }
+    if (aborted) {
+        // work budget exceeded (a sparse group whose box is much larger than its neighbourhoods): hand the
+        // group's queries to the warp-per-query kernel, which re-does them in parallel
+        if (lane == 0) overflow[1 + atomicAdd(overflow, 1u)] = (unsigned)group;
+        if (ctr && lane == 0) {
+            atomicAdd(ctr + 0, (unsigned long long)n_scan * kLeaf * n_active);
+            atomicAdd(ctr + 6, 1ull);
+        }
+        return;
     }
 
     if (ctr && lane == 0) {
@@ -207,12 +260,23 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
 }
 
 template <bool SELF>
-int launch_tile(pcp_ctx *ctx, const IndexView &v, const float *d_q, const unsigned *d_perm, long long nq, long long stride,
+int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long long nq, long long stride,
                 int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    pcp_ctx *ctx = ix->ctx;
+    const IndexView v = make_view(ix);
     const long long n_groups = SELF ? v.n_leaf : (nq + 31) / 32;
     const unsigned grid = (unsigned)((n_groups + kTileWarps - 1) / kTileWarps);
     const unsigned block = kTileWarps * 32;
     unsigned long long *ctr = ctx->ctr();
+    // overflow list: [0] = count, [1..] = group ids
+    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 1)));
+    unsigned *overflow = ctx->scratch[5].as<unsigned>();
+    PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned), ctx->stream));
+    const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
+    const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
+    static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS");   // developer overrides
+    const unsigned max_scans = e_scans ? (unsigned)atoi(e_scans) : small_grid ? kScansPerSlot * std::max(K, 4) : 0xffffffffu;
+    const unsigned max_tests = e_tests ? (unsigned)atoi(e_tests) : small_grid ? kTestsPerSlot * std::max(K, 4) : 0xffffffffu;
     unsigned *dbg = nullptr;
     const char *dump = ctr ? getenv("PCP_DUMP_GROUPS") : nullptr;     // developer aid: per-group work counters
     if (dump) {
@@ -220,7 +284,8 @@ int launch_tile(pcp_ctx *ctx, const IndexView &v, const float *d_q, const unsign
         dbg = ctx->scratch[4].as<unsigned>();
     }
 #define PCP_TILE(KK)                                                                                              \
-    knn_tile_kernel<KK, SELF><<<grid, block, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count, ctr, dbg)
+    knn_tile_kernel<KK, SELF><<<grid, block, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count, ctr, dbg, \
+                                                               overflow, max_scans, max_tests)
     if (k == 1) PCP_TILE(1);
     else if (k == 2) PCP_TILE(2);
     else if (k <= 4) PCP_TILE(4);
@@ -236,18 +301,19 @@ int launch_tile(pcp_ctx *ctx, const IndexView &v, const float *d_q, const unsign
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
         if (FILE *f = fopen(dump, "wb")) { fwrite(h.data(), sizeof(unsigned), h.size(), f); fclose(f); }
     }
-    return PCP_OK;
+    // groups that ran out of budget: one warp per query, persistent grid sized by the device-side count
+    return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, k, d_idx, d_dist, d_count);
 }
 
 }  // namespace
 
 int knn_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
                     int32_t *d_idx, float *d_dist, int32_t *d_count) {
-    return launch_tile<false>(ix->ctx, make_view(ix), d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count);
+    return launch_tile<false>(ix, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count);
 }
 
 int knn_tile_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
-    return launch_tile<true>(ix->ctx, make_view(ix), nullptr, nullptr, ix->n, 3, k, d_idx, d_dist, d_count);
+    return launch_tile<true>(ix, nullptr, nullptr, ix->n, 3, k, d_idx, d_dist, d_count);
 }
 
 }  // namespace pcp
