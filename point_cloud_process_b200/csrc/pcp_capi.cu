@@ -164,6 +164,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     ctx->cub_tmp.release();
     ctx->counters.release();
     ctx->icp_targets.release();
+    ctx->icp_sources.release();
     for (auto &b : ctx->scratch) b.release();
     for (auto &b : ctx->pin) b.release();
     cudaStreamDestroy(ctx->stream);

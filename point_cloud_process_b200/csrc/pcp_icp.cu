@@ -23,6 +23,7 @@
 //                        broadcast of main.py:150; stop when both <= thresholds
 //       main.py:156      T_last = last increment;   icp_template.py:198 homo_mat_total = composed pose
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -210,6 +211,192 @@ icp_assoc_kernel(const IndexView *__restrict__ views, const float *__restrict__ 
     }
 }
 
+// ---- tiled association: one warp = one bucket of 32 Morton-adjacent SOURCE points, one point per lane --------
+// Same structure as knn_tile_kernel (pcp_knn_tile.cu) with K = 1: the group walks the pair's TARGET hierarchy once,
+// buckets are staged in shared memory and every lane evaluates its own (transformed) point against the 32 staged
+// points in float32; survivors of the proven-margin filter are re-evaluated in float64 (nn1 semantics above).
+constexpr int kTileAssocWarps = 8;
+
+__device__ __forceinline__ float nn1_gate_fast(double best, float E) {
+    // upper bound of best (1 + 2^-20) + 2 sqrt(best) E + E^2 in float, every step rounded up
+    if (!(best < 1e30)) return __int_as_float(0x7f800000);
+    const float b = __double2float_ru(best * (1.0 + 9.6e-7));
+    const float r = __fsqrt_ru(b);
+    return __fadd_ru(__fadd_ru(b, __fmul_ru(__fmul_ru(2.f, r), E)), __fmul_ru(E, E));
+}
+
+__global__ void __launch_bounds__(kTileAssocWarps * 32)
+icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *__restrict__ src_views,
+                      const IcpState *__restrict__ states, double *__restrict__ partials, int chunks_per_pair,
+                      double dist_thres) {
+    __shared__ float4 s_tile[kTileAssocWarps][32];
+    __shared__ float4 s_box[kTileAssocWarps][64];
+    __shared__ unsigned s_lb[kTileAssocWarps][kMaxLevels][32];
+    __shared__ unsigned s_cd[kTileAssocWarps][kMaxLevels][32];
+    __shared__ unsigned s_node[kTileAssocWarps][kMaxLevels];
+    __shared__ double s_sum[kTileAssocWarps][kSums];
+    const int pair = blockIdx.y, chunk = blockIdx.x;
+    const IcpState &st = states[pair];
+    if (!st.active) return;
+    const IndexView &sx = src_views[pair];
+    if ((long long)chunk * kTileAssocWarps >= sx.n_leaf) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long group = (long long)chunk * kTileAssocWarps + warp;
+    const IndexView &ix = tgt_views[pair];
+    double acc[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) acc[i] = 0.0;
+
+    if (group < sx.n_leaf) {                                   // warp-uniform
+        const float4 sp = __ldg(sx.pts + group * kLeaf + lane);
+        const bool active = (int)__float_as_uint(sp.w) >= 0;   // pad lanes carry index -1
+        // main.py:110 in float64: composed pose applied to the original point
+        const double x = (double)sp.x, y = (double)sp.y, z = (double)sp.z;
+        const double ax = st.applied[0] * x + st.applied[1] * y + st.applied[2] * z + st.applied[3];
+        const double ay = st.applied[4] * x + st.applied[5] * y + st.applied[6] * z + st.applied[7];
+        const double az = st.applied[8] * x + st.applied[9] * y + st.applied[10] * z + st.applied[11];
+        const float qx = (float)ax, qy = (float)ay, qz = (float)az;
+        const float E = __double2float_ru(1.04e-7 * (fabs(ax) + fabs(ay) + fabs(az)));
+        float3 glo, ghi;
+        glo.x = warp_min(active ? qx : 3.0e38f); glo.y = warp_min(active ? qy : 3.0e38f); glo.z = warp_min(active ? qz : 3.0e38f);
+        ghi.x = warp_max(active ? qx : -3.0e38f); ghi.y = warp_max(active ? qy : -3.0e38f); ghi.z = warp_max(active ? qz : -3.0e38f);
+        const float gcx = 0.5f * (glo.x + ghi.x), gcy = 0.5f * (glo.y + ghi.y), gcz = 0.5f * (glo.z + ghi.z);
+
+        double best = dist_thres;                              // only d^2 < dist_thres matters (main.py:119)
+        unsigned best_id = kDone;
+        float bx = 0.f, by = 0.f, bz = 0.f;
+        float gate = active ? nn1_gate_fast(best, E) : -1.f;
+        unsigned group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
+
+        float4 *tile = s_tile[warp];
+        float4 *boxes = s_box[warp];
+        auto bucket_needed = [&](int c) -> bool {
+            return __ballot_sync(kFullMask, box_lb2(qx, qy, qz, boxes[2 * c], boxes[2 * c + 1]) <= gate) != 0;
+        };
+        auto scan_bucket = [&](const float4 pv) {
+            __syncwarp();
+            tile[lane] = pv;
+            __syncwarp();
+            unsigned mask = 0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float4 p = tile[j];
+                const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
+                if (d2 <= gate) mask |= 1u << j;               // NaN pads never pass
+            }
+            bool changed = false;
+            while (__any_sync(kFullMask, mask != 0)) {
+                if (mask) {
+                    const int j = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const float4 p = tile[j];
+                    const double dx = ax - (double)p.x, dy = ay - (double)p.y, dz = az - (double)p.z;
+                    const double d2 = dx * dx + dy * dy + dz * dz;
+                    const unsigned id = __float_as_uint(p.w);
+                    if (d2 < best || (d2 == best && id < best_id)) {
+                        best = d2; best_id = id; bx = p.x; by = p.y; bz = p.z;
+                        changed = true;
+                    }
+                }
+            }
+            if (changed) gate = nn1_gate_fast(best, E);
+            group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
+        };
+
+        const int top_level = ix.n_levels - 1;
+        if (top_level > 0) {
+            unsigned(*lbs)[32] = s_lb[warp];
+            unsigned(*cds)[32] = s_cd[warp];
+            unsigned *nodes = s_node[warp];
+            auto open_node = [&](int lv, unsigned node) {
+                if (lane == 0) nodes[lv] = node;
+                const long long c = (long long)node * kFan + lane;
+                unsigned bits = kDone, cbits = kDone;
+                if (c < ix.level_cnt[lv - 1]) {
+                    const long long b = ix.level_off[lv - 1] + c;
+                    const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
+                    bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+                    const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
+                    cbits = __float_as_uint(cx * cx + cy * cy + cz * cz);
+                    if (lv == 1) { boxes[2 * lane] = lo; boxes[2 * lane + 1] = hi; }
+                }
+                lbs[lv][lane] = bits;
+                cds[lv][lane] = cbits;
+                __syncwarp();
+            };
+            auto pick = [&](int lv) -> int {
+                const unsigned mine = lbs[lv][lane];
+                const unsigned bestb = __reduce_min_sync(kFullMask, mine);
+                if (bestb == kDone || bestb > group_gate) return -1;
+                unsigned tie = __ballot_sync(kFullMask, mine == bestb);
+                if (tie & (tie - 1)) {
+                    const unsigned cd = (mine == bestb) ? cds[lv][lane] : kDone;
+                    const unsigned cbest = __reduce_min_sync(kFullMask, cd);
+                    tie = __ballot_sync(kFullMask, cd == cbest);
+                }
+                const int sel = __ffs(tie) - 1;
+                if (lane == sel) lbs[lv][lane] = kDone;
+                __syncwarp();
+                return sel;
+            };
+            int level = top_level;
+            open_node(top_level, 0u);
+            while (true) {
+                int sel = pick(level);
+                if (sel < 0) {
+                    if (level == top_level) break;
+                    ++level;
+                    continue;
+                }
+                if (level > 1) {
+                    const unsigned child = nodes[level] * kFan + sel;
+                    --level;
+                    open_node(level, child);
+                    continue;
+                }
+                const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
+                while (sel >= 0 && !bucket_needed(sel)) sel = pick(1);
+                if (sel < 0) continue;
+                float4 cur = __ldg(base + sel * kLeaf);
+                while (true) {
+                    int nxt = pick(1);
+                    while (nxt >= 0 && !bucket_needed(nxt)) nxt = pick(1);
+                    float4 pf = cur;
+                    if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
+                    scan_bucket(cur);
+                    if (nxt < 0) break;
+                    sel = nxt;
+                    cur = pf;
+                }
+            }
+        }
+        if (active && best_id != kDone && best < dist_thres) {   // main.py:119
+            const double tx = (double)bx, ty = (double)by, tz = (double)bz;
+            acc[0] = 1.0;
+            acc[1] = ax; acc[2] = ay; acc[3] = az;
+            acc[4] = tx; acc[5] = ty; acc[6] = tz;
+            acc[7] = tx * ax; acc[8] = tx * ay; acc[9] = tx * az;
+            acc[10] = ty * ax; acc[11] = ty * ay; acc[12] = ty * az;
+            acc[13] = tz * ax; acc[14] = tz * ay; acc[15] = tz * az;
+        }
+    }
+    // fixed-shape reductions: xor-shuffle tree inside the warp, warps in order inside the CTA -> deterministic
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+        if (lane == 0) s_sum[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < kSums) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kTileAssocWarps; ++w) s += s_sum[w][threadIdx.x];
+        partials[((long long)pair * chunks_per_pair + chunk) * kSums + threadIdx.x] = s;
+    }
+}
+
 // One-sided (Hestenes) Jacobi SVD of a 3x3 float64 matrix: A V = U S.  Returns R = U V^T, the
 // orthogonal polar factor u @ vt of main.py:138-139 (independent of the SVD's sign conventions
 // whenever the smallest singular value is > 0).
@@ -289,14 +476,17 @@ __device__ __forceinline__ void compose(const double inc[12], const double prev[
 __global__ void __launch_bounds__(128)
 icp_solve_kernel(IcpState *__restrict__ states, const double *__restrict__ partials, const long long *__restrict__ src_off,
                  long long n_pairs, int chunks_per_pair, int iteration, int max_iteration, double R_thr, double t_thr,
-                 int first_iter_broadcast, double *__restrict__ diff_log, int *__restrict__ n_active) {
+                 int first_iter_broadcast, double *__restrict__ diff_log, int *__restrict__ n_active,
+                 const IndexView *__restrict__ src_views) {
     const long long pair = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (pair >= n_pairs) return;
     IcpState &st = states[pair];
     if (!st.active) return;
     const long long ns = src_off[pair + 1] - src_off[pair];
-    const int chunks = (int)((ns + kChunk - 1) / kChunk);
+    // chunk records written for this pair: tiled association -> one per 8 source buckets, else one per 512 points
+    const int chunks = src_views ? (int)((src_views[pair].n_leaf + kTileAssocWarps - 1) / kTileAssocWarps)
+                                 : (int)((ns + kChunk - 1) / kChunk);
     // lane l < 16 sums component l over the pair's chunk records in chunk order (deterministic)
     double s = 0.0;
     if (lane < kSums)
@@ -501,7 +691,16 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
         if (h_src_off[p + 1] < h_src_off[p]) return fail(PCP_ERR_INVALID, "pcp_icp_batch: src_offsets must be non-decreasing");
         max_ns = std::max<int64_t>(max_ns, h_src_off[p + 1] - h_src_off[p]);
     }
-    const int chunks = (int)std::max<int64_t>(1, (max_ns + kChunk - 1) / kChunk);
+    // Tiled association (default): the sources are Morton-bucketed once per call with the same segmented build,
+    // so that a warp's 32 source points are spatial neighbours.  PCP_ICP_KERNEL=warp keeps the warp-per-point walk.
+    static const bool use_tile = !(getenv("PCP_ICP_KERNEL") && strcmp(getenv("PCP_ICP_KERNEL"), "warp") == 0);
+    BatchIndex &sb = ctx->icp_sources;
+    if (use_tile) {
+        sb.ctx = ctx;
+        PCP_TRY(batch_build_device(&sb, d_src, stride, P, h_src_off));
+    }
+    const int chunks = use_tile ? (int)std::max<int64_t>(1, (sb.max_leaf + kTileAssocWarps - 1) / kTileAssocWarps)
+                                : (int)std::max<int64_t>(1, (max_ns + kChunk - 1) / kChunk);
 
     std::vector<IcpState> h_states((size_t)P);
     for (int64_t p = 0; p < P; ++p) {
@@ -538,14 +737,19 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
     for (int it = 0; it < max_it && h_active > 0; ++it) {
         for (int64_t p0 = 0; p0 < P; p0 += 65535) {
             const unsigned gy = (unsigned)std::min<int64_t>(65535, P - p0);
-            icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
-                tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
-                b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+            if (use_tile)
+                icp_assoc_tile_kernel<<<dim3((unsigned)chunks, gy), kTileAssocWarps * 32, 0, st>>>(
+                    tb.d_views() + p0, sb.d_views() + p0, b_states.as<IcpState>() + p0,
+                    b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+            else
+                icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
+                    tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
+                    b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
             ctx->launches += 1;
         }
         icp_solve_kernel<<<(unsigned)((P * 32 + 127) / 128), 128, 0, st>>>(
             b_states.as<IcpState>(), b_part.as<double>(), b_off.as<long long>(), P, chunks, it, max_it, prm.R_diff_thres,
-            prm.t_diff_thres, prm.first_iter_broadcast, d_log, b_act.as<int>());
+            prm.t_diff_thres, prm.first_iter_broadcast, d_log, b_act.as<int>(), use_tile ? sb.d_views() : nullptr);
         ctx->launches += 1;
         if (it + 1 == next_check && it + 1 < max_it) {
             // not on the data path: one word tells the host whether any pair still iterates

@@ -103,6 +103,7 @@ struct pcp_ctx {
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
     pcp::PinBuf pin[4];            // pinned staging for host<->device copies
     pcp::DevBuf counters;          // 8 x u64 work counters (pcp_ctx_enable_counters)
+    pcp::BatchIndex icp_sources;   // Morton buckets of the ICP source clouds (query groups of the tiled association)
     pcp::BatchIndex icp_targets;   // hierarchies of the ICP target clouds (pcp_icp_batch), reused across calls
     bool count_work = false;
     unsigned long long *ctr() const { return count_work ? counters.as<unsigned long long>() : nullptr; }
