@@ -3,13 +3,19 @@
 // KNNResultSet.add_point (result_set.py:35-53) for batched query sets.
 //
 // The group walks the 32-ary AABB hierarchy ONCE for all its queries, nearest-first, pruning with
-// the exact box-to-box lower bound against the loosest k-th distance in the group.  Every surviving
-// bucket (32 points, 512 B) is staged in shared memory with one coalesced float4 load per lane and
-// then read back as 32 broadcast LDS.128: each lane evaluates its own query against all 32 points
-// (8 unfused FP32 ops per pair, the reference's operation order) and only records a 32-bit pass
-// mask against its own k-th-distance gate.  The few survivors are then inserted into the lane's
-// sorted register list of K packed (distance, index) keys.  The inner loop is 11 instructions per
-// distance evaluation, 8 of them FP32 pipe work -- this is the kernel the FP32 roofline is quoted on.
+// the exact box-to-box lower bound against the loosest k-th distance gate in the group.  Every
+// surviving bucket (32 points, 512 B) is staged in shared memory with one coalesced float4 load per
+// lane and read back as 32 broadcast LDS.128: each lane evaluates its own query against all 32
+// points (8 unfused FP32 ops per pair, the reference's operation order).  A candidate inside the
+// lane's gate is APPENDED to the lane's column of a shared-memory candidate buffer with one
+// predicated store -- no sorted insertion, no divergence in the scan loop (12 instructions per
+// distance evaluation, 8 of them FP32 pipe work: the kernel the FP32 roofline is quoted on).
+// When a column could overflow on the next scan the whole warp COMPACTS: each lane selects the
+// k-th smallest squared distance of its column with a register min/max network (2 FMNMX per slot),
+// tightens its gate to it and drops the candidates beyond it.  The first scan (gate = +inf) fills the
+// columns with 32 candidates and so bootstraps the gates.  After the walk one last compaction leaves
+// k (+ distance ties) candidates per lane, which are ranked by the packed (float32 sqrt, index) key
+// -- KNNResultSet order made canonical (distance, then index).
 //
 // Query groups: for pcp_knn_self the buckets themselves (Morton-sorted cloud); for arbitrary query
 // sets the queries are first sorted by their Morton code in the index's frame (sort_queries).
@@ -26,7 +32,6 @@ namespace pcp {
 
 namespace {
 
-constexpr int kTileWarps = 4;
 constexpr unsigned kDone = 0xffffffffu;
 constexpr unsigned kInfBits = 0x7f800000u;
 // Work budget of one group, per result slot K, before it is handed to the warp-per-query kernel.  It only
@@ -36,6 +41,16 @@ constexpr unsigned kInfBits = 0x7f800000u;
 constexpr unsigned kScansPerSlot = 4;
 constexpr unsigned kTestsPerSlot = 12;
 
+// Candidate-buffer geometry per result capacity K: CAP entries per lane (a chunk of 8 evaluations appends at
+// most 8, a compaction leaves k + ties), WARPS groups per CTA.  Shared memory per CTA = WARPS * CAP * 256 B.
+constexpr int kChunk = 8;
+template <int K> struct TileCfg { static constexpr int kCap = 32, kWarps = 4; };
+template <> struct TileCfg<16> { static constexpr int kCap = 40, kWarps = 4; };
+template <> struct TileCfg<32> { static constexpr int kCap = 72, kWarps = 2; };
+// Children whose box overlaps the group box (lower bound 0) are visited in the order of their centre distance:
+// the slot then holds the distance's float bits >> 9, i.e. a value below kMinNormalBits that never prunes.
+constexpr unsigned kMinNormalBits = 0x00800000u;
+
 template <int K>
 struct TopK {
     unsigned long long key[K];
@@ -44,10 +59,8 @@ struct TopK {
 #pragma unroll
         for (int i = 0; i < K; ++i) key[i] = kEmptyKey;
     }
-    // The gate is always taken from slot K-1: for a runtime k < K (k not a power of two) the list simply
-    // keeps a few more candidates than needed; the first k are still the exact k nearest.
     __device__ __forceinline__ unsigned long long worst() const { return key[K - 1]; }
-    // sorted insertion of nk (caller guarantees nk < key[K-1] or accepts a no-op otherwise)
+    // sorted insertion of nk (a no-op when nk >= key[K-1])
     __device__ __forceinline__ void insert(unsigned long long nk) {
         bool g[K];
 #pragma unroll
@@ -58,21 +71,18 @@ struct TopK {
     }
 };
 
-// group-box lower bound of bucket c of the open level-1 node, from the boxes kept in shared memory
-__device__ __forceinline__ unsigned lbs_bound(const float4 *boxes, const float3 &glo, const float3 &ghi, int c) {
-    return __float_as_uint(boxbox_lb2(glo, ghi, boxes[2 * c], boxes[2 * c + 1]));
-}
-
 template <int K, bool SELF>
-__global__ void __launch_bounds__(kTileWarps * 32)
+__global__ void __launch_bounds__(TileCfg<K>::kWarps * 32)
 knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm, long long nq,
                 long long stride, int k, int *__restrict__ out_idx, float *__restrict__ out_dist,
                 int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg,
-                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests) {
+                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests, int trigger) {
+    constexpr int kTileWarps = TileCfg<K>::kWarps;
+    constexpr int kCap = TileCfg<K>::kCap;
+    extern __shared__ uint2 s_cand[];                       // [kTileWarps][kCap][32]: (d2 bits, index) per lane column
     __shared__ float4 s_tile[kTileWarps][32];
     __shared__ float4 s_box[kTileWarps][64];
     __shared__ unsigned s_lb[kTileWarps][kMaxLevels][32];
-    __shared__ unsigned s_cd[kTileWarps][kMaxLevels][32];
     __shared__ unsigned s_node[kTileWarps][kMaxLevels];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long group = blockIdx.x * (long long)kTileWarps + warp;
@@ -101,9 +111,8 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     ghi.x = warp_max(active ? qx : -FLT_MAX); ghi.y = warp_max(active ? qy : -FLT_MAX); ghi.z = warp_max(active ? qz : -FLT_MAX);
     const float gcx = 0.5f * (glo.x + ghi.x), gcy = 0.5f * (glo.y + ghi.y), gcz = 0.5f * (glo.z + ghi.z);
 
-    TopK<K> top;
-    top.init();
-    float gate = active ? __uint_as_float(kInfBits) : -1.f;     // squared-distance gate of this lane (inactive: nothing passes)
+    const float inf = __uint_as_float(kInfBits);
+    float gate = active ? inf : -1.f;                           // squared-distance gate of this lane (inactive: nothing passes)
     unsigned group_gate = kInfBits;                             // bits of the loosest gate in the group
     unsigned n_scan = 0, n_open = 0, n_test = 0, n_round = 0;
     bool aborted = false;
@@ -111,6 +120,48 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
 
     float4 *tile = s_tile[warp];
     float4 *boxes = s_box[warp];            // boxes of the 32 buckets below the open level-1 node: [2*c] = lo, [2*c+1] = hi
+    uint2 *col = s_cand + warp * (kCap * 32) + lane;            // this lane's column: entry e at col[e * 32]
+    const unsigned col_addr = (unsigned)__cvta_generic_to_shared(col);
+    unsigned waddr = col_addr;                                  // append position (shared-memory byte address; 256 B per entry)
+
+    // Running k smallest squared distances of this lane's column, ascending (k < K: the first K - k slots hold
+    // a sentinel below every distance, so that l[K-1] is always the k-th smallest).
+    float l[K];
+#pragma unroll
+    for (int i = 0; i < K; ++i) l[i] = i < K - k ? -1.f : inf;
+    int n_old = 0;                                              // entries of the column already merged into l[]
+
+    // Merge the candidates appended since the last compaction into l[] (register min/max network), tighten the
+    // gates to the k-th smallest squared distance and drop the candidates beyond it.  Warp-uniform loops.
+    auto compact = [&]() {
+        const int cnt = (int)((waddr - col_addr) >> 8);
+        const int n_new = __reduce_max_sync(kFullMask, cnt - n_old);
+        const int nmax = __reduce_max_sync(kFullMask, cnt);
+        n_round += n_new;
+        const uint2 *src_new = col + n_old * 32;
+#pragma unroll 2
+        for (int e = 0; e < n_new; ++e) {
+            float v = n_old + e < cnt ? __uint_as_float(src_new[e * 32].x) : inf;
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                const float lo = fminf(v, l[i]);
+                v = fmaxf(v, l[i]);
+                l[i] = lo;
+            }
+        }
+        // candidates whose float32 sqrt can still tie the k-th distance stay (canonical (distance, index) order)
+        if (l[K - 1] < inf) gate = fminf(gate, d2_gate(__fsqrt_rn(l[K - 1])));
+        unsigned w = 0;
+#pragma unroll 2
+        for (int e = 0; e < nmax; ++e) {
+            const uint2 ent = col[e * 32];
+            if (e < cnt && __uint_as_float(ent.x) <= gate) { col[w] = ent; w += 32; }
+        }
+        waddr = col_addr + w * 8;
+        n_old = (int)(w >> 5);
+        group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
+    };
+
     // Exact per-lane lower bound against bucket c's box (shared-memory broadcast): can ANY lane still use it?
     auto bucket_needed = [&](int c) -> bool {
         ++n_test;
@@ -122,52 +173,49 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         __syncwarp();
         tile[lane] = pv;
         __syncwarp();
-        unsigned mask = 0;
+        // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores
+#pragma unroll 1
+        for (int j0 = 0; j0 < 32; j0 += kChunk) {
+            float4 p[kChunk];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const float4 p = tile[j];
-            const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
-            if (d2 <= gate) mask |= 1u << j;                     // NaN pads never pass
-        }
-        while (__any_sync(kFullMask, mask != 0)) {
-            ++n_round;
-            if (mask) {
-                const int j = __ffs(mask) - 1;
-                mask &= mask - 1;
-                const float4 p = tile[j];
-                const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
-                if (d2 <= gate) {                                // the gate may have tightened since the mask was taken
-                    const unsigned long long nk = pack_key(__fsqrt_rn(d2), __float_as_uint(p.w));
-                    if (nk < top.worst()) {
-                        top.insert(nk);
-                        gate = d2_gate(key_dist(top.worst()));
-                    }
+            for (int j = 0; j < kChunk; ++j) p[j] = tile[j0 + j];
+#pragma unroll
+            for (int j = 0; j < kChunk; ++j) {
+                const float d2 = ref_d2(qx, qy, qz, p[j].x, p[j].y, p[j].z);
+                if (d2 <= gate) {                                // NaN pads never pass
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(d2), "f"(p[j].w) : "memory");
+                    waddr += 256;
                 }
             }
+            // a column that could overflow during the next chunk: compact all columns of the warp
+            if (__any_sync(kFullMask, waddr > col_addr + (unsigned)trigger * 256)) {
+                compact();
+                // still too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
+                if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kChunk) * 256)) { aborted = true; break; }
+            }
         }
-        group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
     };
 
     const int top_level = ix.n_levels - 1;      // >= 1 for every non-empty index (pcp_build.cu)
     if (top_level > 0) {
         unsigned(*lbs)[32] = s_lb[warp];
-        unsigned(*cds)[32] = s_cd[warp];
         unsigned *nodes = s_node[warp];
         auto open_node = [&](int lv, unsigned node) {
             ++n_open;
             if (lane == 0) nodes[lv] = node;
             const long long c = (long long)node * kFan + lane;
-            unsigned bits = kDone, cbits = kDone;
+            unsigned bits = kDone;
             if (c < ix.level_cnt[lv - 1]) {
                 const long long b = ix.level_off[lv - 1] + c;
                 const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
                 bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
-                const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
-                cbits = __float_as_uint(cx * cx + cy * cy + cz * cz);   // ordering hint only, never used to prune
+                if (bits == 0u) {   // overlaps the group box: order by centre distance (a hint, never used to prune)
+                    const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
+                    bits = __float_as_uint(cx * cx + cy * cy + cz * cz) >> 9;
+                }
                 if (lv == 1) { boxes[2 * lane] = lo; boxes[2 * lane + 1] = hi; }
             }
             lbs[lv][lane] = bits;
-            cds[lv][lane] = cbits;
             __syncwarp();
         };
         // nearest unvisited child of the open node on `lv` that can still matter: -1 if none.  Marks it visited.
@@ -175,14 +223,9 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
             const unsigned mine = lbs[lv][lane];
             const unsigned best = __reduce_min_sync(kFullMask, mine);
             // exact prune: every point below a child is at least `best` away from every query of the group
-            if (best == kDone || best > group_gate) return -1;
-            unsigned tie = __ballot_sync(kFullMask, mine == best);
-            if (tie & (tie - 1)) {   // several children at the same bound (typically 0: they overlap the group box)
-                const unsigned cd = (mine == best) ? cds[lv][lane] : kDone;
-                const unsigned cbest = __reduce_min_sync(kFullMask, cd);
-                tie = __ballot_sync(kFullMask, cd == cbest);
-            }
-            const int sel = __ffs(tie) - 1;
+            // (slots below kMinNormalBits are ordering hints of overlapping children or denormal bounds: kept)
+            if (best == kDone || (best > group_gate && best >= kMinNormalBits)) return -1;
+            const int sel = __ffs(__ballot_sync(kFullMask, mine == best)) - 1;
             if (lane == sel) lbs[lv][lane] = kDone;
             __syncwarp();
             return sel;
@@ -218,20 +261,35 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                 if (nxt < 0) break;
                 sel = nxt;
                 cur = pf;
-                if (n_scan > max_scans || n_test > max_tests) break;
+                if (aborted || n_scan > max_scans || n_test > max_tests) break;
             }
-            if (n_scan > max_scans || n_test > max_tests) { aborted = true; break; }
+            if (aborted || n_scan > max_scans || n_test > max_tests) { aborted = true; break; }
         }
     }
     if (aborted) {
-        // work budget exceeded (a sparse group whose box is much larger than its neighbourhoods): hand the
-        // group's queries to the warp-per-query kernel, which re-does them in parallel
+        // work budget exceeded (a sparse group whose box is much larger than its neighbourhoods) or a mass of
+        // tied distances: hand the group's queries to the warp-per-query kernel, which re-does them in parallel
         if (lane == 0) overflow[1 + atomicAdd(overflow, 1u)] = (unsigned)group;
         if (ctr && lane == 0) {
             atomicAdd(ctr + 0, (unsigned long long)n_scan * kLeaf * n_active);
             atomicAdd(ctr + 6, 1ull);
         }
         return;
+    }
+
+    // ---- final selection: k (+ ties) candidates per lane, ranked by (float32 sqrt, index)
+    compact();
+    TopK<K> top;
+    top.init();
+    {
+        const int cnt = (int)((waddr - col_addr) >> 8);
+        const int nmax = __reduce_max_sync(kFullMask, cnt);
+        for (int e = 0; e < nmax; ++e) {
+            if (e < cnt) {
+                const uint2 ent = col[e * 32];
+                top.insert(pack_key(__fsqrt_rn(__uint_as_float(ent.x)), ent.y));
+            }
+        }
     }
 
     if (ctr && lane == 0) {
@@ -265,8 +323,6 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
     const long long n_groups = SELF ? v.n_leaf : (nq + 31) / 32;
-    const unsigned grid = (unsigned)((n_groups + kTileWarps - 1) / kTileWarps);
-    const unsigned block = kTileWarps * 32;
     unsigned long long *ctr = ctx->ctr();
     // overflow list: [0] = count, [1..] = group ids
     PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 1)));
@@ -274,7 +330,8 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned), ctx->stream));
     const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
     const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
-    static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS");   // developer overrides
+    static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS"),
+                      *e_trig = getenv("PCP_TILE_TRIGGER");   // developer overrides
     const unsigned max_scans = e_scans ? (unsigned)atoi(e_scans) : small_grid ? kScansPerSlot * std::max(K, 4) : 0xffffffffu;
     const unsigned max_tests = e_tests ? (unsigned)atoi(e_tests) : small_grid ? kTestsPerSlot * std::max(K, 4) : 0xffffffffu;
     unsigned *dbg = nullptr;
@@ -283,9 +340,22 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
         PCP_TRY(ctx->scratch[4].ensure(sizeof(unsigned) * 4 * (size_t)n_groups));
         dbg = ctx->scratch[4].as<unsigned>();
     }
-#define PCP_TILE(KK)                                                                                              \
-    knn_tile_kernel<KK, SELF><<<grid, block, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count, ctr, dbg, \
-                                                               overflow, max_scans, max_tests)
+#define PCP_TILE(KK)                                                                                                   \
+    do {                                                                                                               \
+        constexpr int W = TileCfg<KK>::kWarps, CAP = TileCfg<KK>::kCap;                                                \
+        const size_t smem = (size_t)W * CAP * 32 * sizeof(uint2);                                                      \
+        static bool attr_set = false;                                                                                  \
+        if (!attr_set) {                                                                                               \
+            PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            attr_set = true;                                                                                           \
+        }                                                                                                              \
+        /* compaction trigger: a column longer than this could overflow during the next chunk of evaluations */       \
+        const int trig = e_trig ? std::min(atoi(e_trig), CAP - kChunk) : CAP - kChunk;                                 \
+        const unsigned grid = (unsigned)((n_groups + W - 1) / W);                                                      \
+        knn_tile_kernel<KK, SELF><<<grid, W * 32, smem, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist,   \
+                                                                       d_count, ctr, dbg, overflow, max_scans,         \
+                                                                       max_tests, trig);                               \
+    } while (0)
     if (k == 1) PCP_TILE(1);
     else if (k == 2) PCP_TILE(2);
     else if (k <= 4) PCP_TILE(4);
