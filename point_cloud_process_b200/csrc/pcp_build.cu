@@ -8,7 +8,9 @@
 //   bbox_kernel        float3[n] -> 6 ordered-uint min/max words per segment  (np.amin/np.amax, octree.py:319-320)
 //   key_kernel         float3[n] -> (segment | 30-bit Morton key, row)        (child-code loop, octree.py:75-85)
 //   cub::DeviceRadixSort::SortPairs                                            (np.argsort, kdtree.py:46,76)
-//   gather_leaf_kernel sorted rows -> float4 bucket rows + bucket AABBs        (Node / Octant objects)
+//   refine_leaf_kernel sorted rows -> per 1024-point node: 5 levels of widest-axis median splits in shared
+//                      memory (the kd-tree's split rule, kdtree.py:74-97, applied below the Morton order)
+//                      -> float4 bucket rows + bucket AABBs                    (Node / Octant objects)
 //   node_box_kernel    32 child AABBs -> parent AABB, once per upper level
 #include <cub/device/device_radix_sort.cuh>
 
@@ -109,33 +111,143 @@ __global__ void __launch_bounds__(256) key_kernel(const float *__restrict__ xyz,
     vals[v.src_off + i] = static_cast<unsigned>(v.src_off + i);
 }
 
-// One warp per bucket: lane j takes sorted position leaf*32+j of its segment, gathers the point and
-// the warp reduces the bucket AABB.  Pad lanes of a segment's last bucket are written as NaN / index
-// -1 so that every distance against them is NaN and fails every "<=" gate.
-__global__ void __launch_bounds__(256) gather_leaf_kernel(const float *__restrict__ xyz, long long stride,
-                                                          const IndexView *__restrict__ views,
-                                                          const unsigned *__restrict__ sorted_rows) {
+// ---- kd refinement of one block of 1024 Morton-consecutive points ------------------------------
+// A run of 32 points in Morton order is a poor bucket: it straddles cell boundaries and its AABB is
+// 2-3x larger than the points' share of space.  Each block of 32 buckets (one level-1 node) is
+// therefore re-partitioned in shared memory with the reference kd-tree's rule -- split at the
+// median of the coordinate of largest extent, round-robin replaced by the widest axis
+// (kdtree.py:74-97) -- 5 levels deep: 1024 -> 2 x 512 -> ... -> 32 buckets of 32.  Every level is a
+// bitonic sort of (coordinate, slot) keys inside aligned power-of-two segments: strides below 32
+// exchange by warp shuffle, larger ones through shared memory.  Pad slots (beyond the cloud) carry
+// the largest key on every axis, so real points always stay at the front of their segment and
+// bucket b of the node holds sorted positions [32b, 32b+32) exactly as the hierarchy expects.
+constexpr int kRefine = 1024;                 // points per block == threads per CTA
+constexpr unsigned kPadKey = 0xffffffffu;
+
+struct RefineSmem {
+    float x[kRefine], y[kRefine], z[kRefine];
+    unsigned long long key[kRefine];
+    unsigned box[32][6];                       // per segment: ordered-uint min xyz, max xyz
+};
+
+// Thread t owns slot t.  In: its element's coordinates (valid = real point).  Out: the element id (0..1023,
+// the slot that loaded it) that ends up in slot t; coordinates stay addressable by id in sm.x/y/z.
+__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid) {
+    const unsigned t = threadIdx.x;
+    sm.x[t] = x; sm.y[t] = y; sm.z[t] = z;
+    unsigned id = t;
+    bool real = valid;
+#pragma unroll 1
+    for (int d = 0; d < 5; ++d) {
+        const unsigned S = kRefine >> d;       // segment size
+        const unsigned seg = t / S;
+        // ---- widest axis of every segment
+        if (t < 32 * 6) sm.box[t / 6][t % 6] = (t % 6) < 3 ? 0xffffffffu : 0u;
+        __syncthreads();                       // also orders the sm.x/y/z stores before the first gather
+        const float ex = sm.x[id], ey = sm.y[id], ez = sm.z[id];
+        const unsigned ox = float_to_ordered(ex), oy = float_to_ordered(ey), oz = float_to_ordered(ez);
+        {
+            // a warp never straddles segments (S >= 64)
+            const unsigned mnx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), mxx = __reduce_max_sync(kFullMask, real ? ox : 0u);
+            const unsigned mny = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), mxy = __reduce_max_sync(kFullMask, real ? oy : 0u);
+            const unsigned mnz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), mxz = __reduce_max_sync(kFullMask, real ? oz : 0u);
+            if ((t & 31) == 0) {
+                atomicMin(&sm.box[seg][0], mnx); atomicMin(&sm.box[seg][1], mny); atomicMin(&sm.box[seg][2], mnz);
+                atomicMax(&sm.box[seg][3], mxx); atomicMax(&sm.box[seg][4], mxy); atomicMax(&sm.box[seg][5], mxz);
+            }
+        }
+        __syncthreads();
+        const float wx = ordered_to_float(sm.box[seg][3]) - ordered_to_float(sm.box[seg][0]);
+        const float wy = ordered_to_float(sm.box[seg][4]) - ordered_to_float(sm.box[seg][1]);
+        const float wz = ordered_to_float(sm.box[seg][5]) - ordered_to_float(sm.box[seg][2]);
+        // empty segments give NaN / negative widths: any axis will do
+        const unsigned okey = (wx >= wy && wx >= wz) ? ox : (wy >= wz ? oy : oz);
+        unsigned long long key = ((unsigned long long)(real ? okey : kPadKey) << 32) | id;
+        // ---- bitonic sort of the segment (ascending)
+#pragma unroll 1
+        for (unsigned k = 2; k <= S; k <<= 1) {
+#pragma unroll 1
+            for (unsigned j = k >> 1; j > 0; j >>= 1) {
+                unsigned long long other;
+                if (j >= 32) {
+                    __syncthreads();
+                    sm.key[t] = key;
+                    __syncthreads();
+                    other = sm.key[t ^ j];
+                } else {
+                    other = __shfl_xor_sync(kFullMask, key, j);
+                }
+                const bool up = ((t & k) == 0) || k == S;
+                const bool lower = (t & j) == 0;
+                const unsigned long long mn = key < other ? key : other, mx = key < other ? other : key;
+                key = (up == lower) ? mn : mx;
+            }
+        }
+        id = (unsigned)key & (kRefine - 1);
+        real = (unsigned)(key >> 32) != kPadKey;
+    }
+    return id;
+}
+
+// One CTA per level-1 node: gather the node's points through the Morton order, refine, write the float4
+// bucket rows (pad lanes NaN / index -1, so that every distance against them is NaN and fails every "<="
+// gate) and the bucket AABBs.
+__global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__restrict__ xyz, long long stride,
+                                                               const IndexView *__restrict__ views,
+                                                               const unsigned *__restrict__ sorted_rows) {
+    __shared__ RefineSmem sm;
+    __shared__ unsigned s_idx[kRefine];
     const IndexView &v = views[blockIdx.y];
-    long long leaf = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (leaf >= v.n_leaf) return;
-    long long pos = leaf * kLeaf + lane;
+    const long long node = blockIdx.x;
+    if (node * kFan >= v.n_leaf) return;
+    const unsigned t = threadIdx.x;
+    const long long pos = node * kRefine + t;
     float x = nanf(""), y = x, z = x;
     unsigned idx = 0xffffffffu;
-    if (pos < v.n) {
+    const bool valid = pos < v.n;
+    if (valid) {
         const unsigned row = sorted_rows[v.src_off + pos];       // sorted by (segment, morton): rows of this segment
         const float *p = xyz + (long long)row * stride;
         x = p[0]; y = p[1]; z = p[2];
         idx = row - static_cast<unsigned>(v.src_off);
     }
+    s_idx[t] = idx;
+    const unsigned id = refine_block(sm, x, y, z, valid);
+    const long long leaf = pos >> 5;
+    if (leaf >= v.n_leaf) return;                                // whole warp: bucket beyond the cloud
+    x = sm.x[id]; y = sm.y[id]; z = sm.z[id];
+    idx = s_idx[id];
     const_cast<float4 *>(v.pts)[pos] = make_float4(x, y, z, __uint_as_float(idx));
-    // fminf/fmaxf return the non-NaN operand, so pad lanes do not disturb the box
-    float lx = warp_min(x), ly = warp_min(y), lz = warp_min(z);
-    float hx = warp_max(x), hy = warp_max(y), hz = warp_max(z);
-    if (lane == 0) {
-        const_cast<float4 *>(v.box_lo)[leaf] = make_float4(lx, ly, lz, 0.f);
-        const_cast<float4 *>(v.box_hi)[leaf] = make_float4(hx, hy, hz, 0.f);
+    const bool real = idx != 0xffffffffu;
+    const unsigned ox = float_to_ordered(x), oy = float_to_ordered(y), oz = float_to_ordered(z);
+    const unsigned lx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), hx = __reduce_max_sync(kFullMask, real ? ox : 0u);
+    const unsigned ly = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), hy = __reduce_max_sync(kFullMask, real ? oy : 0u);
+    const unsigned lz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), hz = __reduce_max_sync(kFullMask, real ? oz : 0u);
+    if ((t & 31) == 0) {
+        const_cast<float4 *>(v.box_lo)[leaf] = make_float4(ordered_to_float(lx), ordered_to_float(ly), ordered_to_float(lz), 0.f);
+        const_cast<float4 *>(v.box_hi)[leaf] = make_float4(ordered_to_float(hx), ordered_to_float(hy), ordered_to_float(hz), 0.f);
     }
+}
+
+// Same refinement for a sorted QUERY set: blocks of 1024 Morton-consecutive queries are re-grouped into 32
+// tight groups of 32 (one group = one warp of the tiled kNN kernel).  In place on the permutation.
+__global__ void __launch_bounds__(kRefine) refine_queries_kernel(const float *__restrict__ q, long long nq, long long stride,
+                                                                  unsigned *__restrict__ perm) {
+    __shared__ RefineSmem sm;
+    __shared__ unsigned s_idx[kRefine];
+    const unsigned t = threadIdx.x;
+    const long long pos = blockIdx.x * (long long)kRefine + t;
+    float x = 0.f, y = 0.f, z = 0.f;
+    unsigned row = 0xffffffffu;
+    const bool valid = pos < nq;
+    if (valid) {
+        row = perm[pos];
+        const float *p = q + (long long)row * stride;
+        x = p[0]; y = p[1]; z = p[2];
+    }
+    s_idx[t] = row;
+    const unsigned id = refine_block(sm, x, y, z, valid);
+    if (valid) perm[pos] = s_idx[id];          // real queries stay at the front of the block: slot t < nq - base is real
 }
 
 __global__ void __launch_bounds__(256) node_box_kernel(const IndexView *__restrict__ views, int level) {
@@ -295,8 +407,8 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
-        gather_leaf_kernel<<<dim3(grid_for(b->max_leaf * 32, 256), gy), 256, 0, st>>>(d_xyz, stride, dv + p0,
-                                                                                    b->vals_b.as<unsigned>());
+        refine_leaf_kernel<<<dim3((unsigned)((b->max_leaf + kFan - 1) / kFan), gy), kRefine, 0, st>>>(
+            d_xyz, stride, dv + p0, b->vals_b.as<unsigned>());
         ctx->launches += 1;
         for (int l = 1; l < b->max_levels; ++l) {
             node_box_kernel<<<dim3(grid_for(b->level_max_cnt[l] * 32, 256), gy), 256, 0, st>>>(dv + p0, l);
@@ -326,6 +438,8 @@ int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, ui
     query_key_kernel<<<grid_for(nq, 256), 256, 0, ctx->stream>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
     ctx->launches += 1;
     PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, 30));
+    refine_queries_kernel<<<grid_for(nq, kRefine), kRefine, 0, ctx->stream>>>(d_q, nq, stride, d_perm);
+    ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
 }
