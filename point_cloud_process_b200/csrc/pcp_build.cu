@@ -119,14 +119,14 @@ __global__ void __launch_bounds__(256) key_kernel(const float *__restrict__ xyz,
 // (kdtree.py:74-97) -- 5 levels deep: 1024 -> 2 x 512 -> ... -> 32 buckets of 32.  Every level is a
 // bitonic sort of (coordinate, slot) keys inside aligned power-of-two segments: strides below 32
 // exchange by warp shuffle, larger ones through shared memory.  Pad slots (beyond the cloud) carry
-// the largest key on every axis, so real points always stay at the front of their segment and
+// the largest key on every axis (no finite float maps to it), so real points always stay at the front of their segment and
 // bucket b of the node holds sorted positions [32b, 32b+32) exactly as the hierarchy expects.
 constexpr int kRefine = 1024;                 // points per block == threads per CTA
 constexpr unsigned kPadKey = 0xffffffffu;
 
 struct RefineSmem {
     float x[kRefine], y[kRefine], z[kRefine];
-    unsigned long long key[kRefine];
+    unsigned key[kRefine];
     unsigned box[32][6];                       // per segment: ordered-uint min xyz, max xyz
 };
 
@@ -162,13 +162,15 @@ __device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float 
         const float wz = ordered_to_float(sm.box[seg][5]) - ordered_to_float(sm.box[seg][2]);
         // empty segments give NaN / negative widths: any axis will do
         const unsigned okey = (wx >= wy && wx >= wz) ? ox : (wy >= wz ? oy : oz);
-        unsigned long long key = ((unsigned long long)(real ? okey : kPadKey) << 32) | id;
+        // 22 coordinate bits + 10 slot bits in one word: the split is a partition heuristic, the slot makes keys
+        // unique and the order deterministic; pads carry the largest key
+        unsigned key = ((real ? okey : kPadKey) & ~(kRefine - 1u)) | id;
         // ---- bitonic sort of the segment (ascending)
 #pragma unroll 1
         for (unsigned k = 2; k <= S; k <<= 1) {
 #pragma unroll 1
             for (unsigned j = k >> 1; j > 0; j >>= 1) {
-                unsigned long long other;
+                unsigned other;
                 if (j >= 32) {
                     __syncthreads();
                     sm.key[t] = key;
@@ -179,12 +181,11 @@ __device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float 
                 }
                 const bool up = ((t & k) == 0) || k == S;
                 const bool lower = (t & j) == 0;
-                const unsigned long long mn = key < other ? key : other, mx = key < other ? other : key;
-                key = (up == lower) ? mn : mx;
+                key = (up == lower) ? min(key, other) : max(key, other);
             }
         }
-        id = (unsigned)key & (kRefine - 1);
-        real = (unsigned)(key >> 32) != kPadKey;
+        id = key & (kRefine - 1u);
+        real = (key | (kRefine - 1u)) != kPadKey;
     }
     return id;
 }
@@ -283,15 +284,20 @@ __global__ void __launch_bounds__(256) query_key_kernel(const float *__restrict_
 
 template <class KeyT>
 int radix_sort_pairs(pcp_ctx *ctx, const KeyT *k_in, KeyT *k_out, const unsigned *v_in, unsigned *v_out, long long n,
-                     int end_bit) {
+                     int begin_bit, int end_bit) {
     size_t tmp_bytes = 0;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, end_bit, ctx->stream));
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit, ctx->stream));
     PCP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, 0, end_bit,
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit,
                                              ctx->stream));
-    ctx->launches += 2 + (end_bit + 7) / 8;   // onesweep: histogram + scan + one pass per 8-bit digit (CUB internal)
+    ctx->launches += 2 + (end_bit - begin_bit + 7) / 8;   // onesweep: histogram + scan + one pass per 8-bit digit (CUB internal)
     return PCP_OK;
 }
+
+// Low Morton bits that the sort may ignore: the order only has to make every run of 1024 points spatially
+// coherent (the kd refinement re-partitions inside the run), so cells holding ~4 points on average are fine
+// enough -- 16 significant bits up to 256 k points, 24 up to 64 M, all 30 beyond.  One radix pass per 8 bits.
+inline int morton_skip_bits(long long n) { return n <= (1LL << 18) ? 14 : n <= (1LL << 26) ? 6 : 0; }
 
 inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(std::max<long long>(1, (n + block - 1) / block)); }
 
@@ -400,10 +406,12 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         while ((1LL << seg_bits) < P) ++seg_bits;
         PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
                                                      b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
-                                                     b->vals_b.as<unsigned>(), b->total_n, 30 + seg_bits));
+                                                     b->vals_b.as<unsigned>(), b->total_n, morton_skip_bits(b->max_n),
+                                                     30 + seg_bits));
     } else {
         PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
-                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n, 30));
+                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n,
+                                           morton_skip_bits(b->total_n), 30));
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
@@ -437,7 +445,7 @@ int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, ui
     unsigned *va = ctx->scratch[2].as<unsigned>();
     query_key_kernel<<<grid_for(nq, 256), 256, 0, ctx->stream>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
     ctx->launches += 1;
-    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, 30));
+    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30));
     refine_queries_kernel<<<grid_for(nq, kRefine), kRefine, 0, ctx->stream>>>(d_q, nq, stride, d_perm);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
