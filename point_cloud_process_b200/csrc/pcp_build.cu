@@ -132,13 +132,13 @@ struct RefineSmem {
 
 // Thread t owns slot t.  In: its element's coordinates (valid = real point).  Out: the element id (0..1023,
 // the slot that loaded it) that ends up in slot t; coordinates stay addressable by id in sm.x/y/z.
-__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid) {
+__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid, int levels) {
     const unsigned t = threadIdx.x;
     sm.x[t] = x; sm.y[t] = y; sm.z[t] = z;
     unsigned id = t;
     bool real = valid;
 #pragma unroll 1
-    for (int d = 0; d < 5; ++d) {
+    for (int d = 0; d < levels; ++d) {     // levels = 5: segments of 32 (buckets / query groups); 6: halves of 16
         const unsigned S = kRefine >> d;       // segment size
         const unsigned seg = t / S;
         // ---- widest axis of every segment
@@ -147,7 +147,7 @@ __device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float 
         const float ex = sm.x[id], ey = sm.y[id], ez = sm.z[id];
         const unsigned ox = float_to_ordered(ex), oy = float_to_ordered(ey), oz = float_to_ordered(ez);
         {
-            // a warp never straddles segments (S >= 64)
+            // a warp never straddles segments (S >= 32)
             const unsigned mnx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), mxx = __reduce_max_sync(kFullMask, real ? ox : 0u);
             const unsigned mny = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), mxy = __reduce_max_sync(kFullMask, real ? oy : 0u);
             const unsigned mnz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), mxz = __reduce_max_sync(kFullMask, real ? oz : 0u);
@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
         idx = row - static_cast<unsigned>(v.src_off);
     }
     s_idx[t] = idx;
-    const unsigned id = refine_block(sm, x, y, z, valid);
+    const unsigned id = refine_block(sm, x, y, z, valid, 6);
     const long long leaf = pos >> 5;
     if (leaf >= v.n_leaf) return;                                // whole warp: bucket beyond the cloud
     x = sm.x[id]; y = sm.y[id]; z = sm.z[id];
@@ -227,6 +227,18 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
     if ((t & 31) == 0) {
         const_cast<float4 *>(v.box_lo)[leaf] = make_float4(ordered_to_float(lx), ordered_to_float(ly), ordered_to_float(lz), 0.f);
         const_cast<float4 *>(v.box_hi)[leaf] = make_float4(ordered_to_float(hx), ordered_to_float(hy), ordered_to_float(hz), 0.f);
+    }
+    // AABBs of the two 16-point halves (the sixth split): an empty half gets (+inf, -inf), infinitely far from everything
+    const unsigned hm = (t & 16) ? 0xffff0000u : 0x0000ffffu;
+    const unsigned alx = __reduce_min_sync(hm, real ? ox : 0xffffffffu), ahx = __reduce_max_sync(hm, real ? ox : 0u);
+    const unsigned aly = __reduce_min_sync(hm, real ? oy : 0xffffffffu), ahy = __reduce_max_sync(hm, real ? oy : 0u);
+    const unsigned alz = __reduce_min_sync(hm, real ? oz : 0xffffffffu), ahz = __reduce_max_sync(hm, real ? oz : 0u);
+    if ((t & 15) == 0) {
+        const bool any = alx != 0xffffffffu;
+        const float inf = __uint_as_float(0x7f800000u);
+        float4 *h = const_cast<float4 *>(v.half) + leaf * 4 + ((t & 16) ? 2 : 0);
+        h[0] = any ? make_float4(ordered_to_float(alx), ordered_to_float(aly), ordered_to_float(alz), 0.f) : make_float4(inf, inf, inf, 0.f);
+        h[1] = any ? make_float4(ordered_to_float(ahx), ordered_to_float(ahy), ordered_to_float(ahz), 0.f) : make_float4(-inf, -inf, -inf, 0.f);
     }
 }
 
@@ -247,7 +259,7 @@ __global__ void __launch_bounds__(kRefine) refine_queries_kernel(const float *__
         x = p[0]; y = p[1]; z = p[2];
     }
     s_idx[t] = row;
-    const unsigned id = refine_block(sm, x, y, z, valid);
+    const unsigned id = refine_block(sm, x, y, z, valid, 5);
     if (valid) perm[pos] = s_idx[id];          // real queries stay at the front of the block: slot t < nq - base is real
 }
 
@@ -304,7 +316,7 @@ inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(
 }  // namespace
 
 void BatchIndex::release() {
-    for (DevBuf *d : {&pts, &box_lo, &box_hi, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
+    for (DevBuf *d : {&pts, &box_lo, &box_hi, &half, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
     h_views.clear();
     P = 0;
 }
@@ -358,6 +370,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     PCP_TRY(b->pts.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_leaf) * kLeaf));
     PCP_TRY(b->box_lo.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
     PCP_TRY(b->box_hi.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
+    PCP_TRY(b->half.ensure(sizeof(float4) * 4 * (size_t)std::max<int64_t>(1, b->total_leaf)));
     PCP_TRY(b->bbox.ensure(sizeof(float) * kBboxWords * (size_t)P));
     PCP_TRY(b->views.ensure(sizeof(IndexView) * (size_t)P));
     for (int64_t p = 0; p < P; ++p) {
@@ -366,6 +379,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         v.pts = b->pts.as<float4>() + pt_off;
         v.box_lo = b->box_lo.as<float4>() + node_off;
         v.box_hi = b->box_hi.as<float4>() + node_off;
+        v.half = b->half.as<float4>() + pt_off / kLeaf * 4;
         v.bbox = b->bbox.as<float>() + p * kBboxWords;
     }
     // views are small (184 B per segment): pageable copy, staged by the driver before it returns

@@ -60,11 +60,13 @@ namespace pcp {
 // segment's own sub-arrays, so the same device code serves a single index and one pair of a batch.
 //   pts       float4[n_leaf*32]  Morton-sorted points, .w = index bits (row within the segment); pad lanes NaN / -1
 //   box_lo/hi float4[nodes]      AABB per node, level 0 (buckets) first, then level 1 ... root last
+//   half      float4[n_leaf*4]   AABBs of the two 16-point halves of every bucket (the kd refinement's last split)
 //   level_off[l] first node of level l in box_*; level_cnt[l] nodes on level l
 struct IndexView {
     const float4 *pts;
     const float4 *box_lo;
     const float4 *box_hi;
+    const float4 *half;     // float4[n_leaf*4]: per bucket {lo, hi} of points 0..15 and {lo, hi} of points 16..31 (empty: +inf/-inf)
     const float *bbox;      // lo.xyz, cells per unit, hi.xyz, extent
     long long src_off;      // first row of this segment in the source array handed to the build
     long long n;
@@ -84,7 +86,7 @@ struct BatchIndex {
     int max_levels = 0;
     int64_t level_max_cnt[kMaxLevels] = {0};
     std::vector<IndexView> h_views;
-    DevBuf pts, box_lo, box_hi, bbox, views, keys_a, keys_b, vals_a, vals_b;
+    DevBuf pts, box_lo, box_hi, half, bbox, views, keys_a, keys_b, vals_a, vals_b;
     const IndexView *d_views() const { return views.as<IndexView>(); }
     void release();
 };

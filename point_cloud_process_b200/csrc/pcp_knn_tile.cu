@@ -44,7 +44,7 @@ constexpr unsigned kTestsPerSlot = 12;
 // Candidate-buffer geometry per result capacity K: CAP entries per lane (a chunk of 8 evaluations appends at
 // most 8, a compaction leaves k + ties), WARPS groups per CTA.  Shared memory per CTA = WARPS * CAP * 256 B.
 constexpr int kChunk = 8;
-template <int K> struct TileCfg { static constexpr int kCap = 32, kWarps = 4; };
+template <int K> struct TileCfg { static constexpr int kCap = 30, kWarps = 4; };
 template <> struct TileCfg<16> { static constexpr int kCap = 40, kWarps = 4; };
 template <> struct TileCfg<32> { static constexpr int kCap = 72, kWarps = 2; };
 // Children whose box overlaps the group box (lower bound 0) are visited in the order of their centre distance:
@@ -81,13 +81,22 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     constexpr int kCap = TileCfg<K>::kCap;
     extern __shared__ uint2 s_cand[];                       // [kTileWarps][kCap][32]: (d2 bits, index) per lane column
     __shared__ float4 s_tile[kTileWarps][32];
-    __shared__ float4 s_box[kTileWarps][64];
+    __shared__ float4 s_box[kTileWarps][128];
     __shared__ unsigned s_lb[kTileWarps][kMaxLevels][32];
     __shared__ unsigned s_node[kTileWarps][kMaxLevels];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long group = blockIdx.x * (long long)kTileWarps + warp;
     const long long n_groups = SELF ? ix.n_leaf : (nq + 31) / 32;
-    if (group >= n_groups) return;
+    unsigned *sched = overflow + n_groups + 1;                  // next group to hand out (zeroed by the host)
+    // Persistent warps: groups are handed out dynamically, so the kernel ends within one group's work of the
+    // moment the queue runs dry instead of waiting for the unluckiest statically assigned warp.
+    for (;;) {
+    long long group;
+    {
+        unsigned g = 0;
+        if (lane == 0) g = atomicAdd(sched, 1u);
+        group = __shfl_sync(kFullMask, g, 0);
+    }
+    if (group >= n_groups) break;
 
     // ---- this lane's query
     float qx = 0.f, qy = 0.f, qz = 0.f;
@@ -114,12 +123,12 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     const float inf = __uint_as_float(kInfBits);
     float gate = active ? inf : -1.f;                           // squared-distance gate of this lane (inactive: nothing passes)
     unsigned group_gate = kInfBits;                             // bits of the loosest gate in the group
-    unsigned n_scan = 0, n_open = 0, n_test = 0, n_round = 0;
+    unsigned n_scan = 0, n_half = 0, n_open = 0, n_test = 0, n_round = 0;
     bool aborted = false;
     const unsigned n_active = __popc(__ballot_sync(kFullMask, active));
 
     float4 *tile = s_tile[warp];
-    float4 *boxes = s_box[warp];            // boxes of the 32 buckets below the open level-1 node: [2*c] = lo, [2*c+1] = hi
+    float4 *boxes = s_box[warp];            // half-bucket boxes below the open level-1 node: [4*c + 2*h] = lo, [4*c + 2*h + 1] = hi
     uint2 *col = s_cand + warp * (kCap * 32) + lane;            // this lane's column: entry e at col[e * 32]
     const unsigned col_addr = (unsigned)__cvta_generic_to_shared(col);
     unsigned waddr = col_addr;                                  // append position (shared-memory byte address; 256 B per entry)
@@ -162,20 +171,25 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
     };
 
-    // Exact per-lane lower bound against bucket c's box (shared-memory broadcast): can ANY lane still use it?
-    auto bucket_needed = [&](int c) -> bool {
+    // Exact per-lane lower bounds against the boxes of bucket c's two 16-point halves (shared-memory broadcast):
+    // bit h is set when ANY lane can still use half h.
+    auto bucket_needed = [&](int c) -> unsigned {
         ++n_test;
-        return __ballot_sync(kFullMask, box_lb2(qx, qy, qz, boxes[2 * c], boxes[2 * c + 1]) <= gate) != 0;
+        const bool a = box_lb2(qx, qy, qz, boxes[4 * c], boxes[4 * c + 1]) <= gate;
+        const bool b = box_lb2(qx, qy, qz, boxes[4 * c + 2], boxes[4 * c + 3]) <= gate;
+        return (__any_sync(kFullMask, a) ? 1u : 0u) | (__any_sync(kFullMask, b) ? 2u : 0u);
     };
-    // Scan one bucket whose points `pv` (lane j = point j) are already in registers.
-    auto scan_bucket = [&](const float4 pv) {
+    // Scan the needed halves of one bucket whose points `pv` (lane j = point j) are already in registers.
+    auto scan_bucket = [&](const float4 pv, unsigned halves) {
         ++n_scan;
+        n_half += __popc(halves);
         __syncwarp();
         tile[lane] = pv;
         __syncwarp();
         // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores
 #pragma unroll 1
         for (int j0 = 0; j0 < 32; j0 += kChunk) {
+            if (!((halves >> (j0 >> 4)) & 1u)) continue;
             float4 p[kChunk];
 #pragma unroll
             for (int j = 0; j < kChunk; ++j) p[j] = tile[j0 + j];
@@ -206,14 +220,24 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
             const long long c = (long long)node * kFan + lane;
             unsigned bits = kDone;
             if (c < ix.level_cnt[lv - 1]) {
-                const long long b = ix.level_off[lv - 1] + c;
-                const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
-                bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+                float4 lo, hi;
+                if (lv == 1) {
+                    // buckets: the boxes of the two halves; the bucket's bound is the smaller of theirs
+                    const float4 *h = ix.half + c * 4;
+                    const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
+                    boxes[4 * lane] = alo; boxes[4 * lane + 1] = ahi; boxes[4 * lane + 2] = blo; boxes[4 * lane + 3] = bhi;
+                    bits = min(__float_as_uint(boxbox_lb2(glo, ghi, alo, ahi)), __float_as_uint(boxbox_lb2(glo, ghi, blo, bhi)));
+                    lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+                    hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+                } else {
+                    const long long b = ix.level_off[lv - 1] + c;
+                    lo = __ldg(ix.box_lo + b); hi = __ldg(ix.box_hi + b);
+                    bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+                }
                 if (bits == 0u) {   // overlaps the group box: order by centre distance (a hint, never used to prune)
                     const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
                     bits = __float_as_uint(cx * cx + cy * cy + cz * cz) >> 9;
                 }
-                if (lv == 1) { boxes[2 * lane] = lo; boxes[2 * lane + 1] = hi; }
             }
             lbs[lv][lane] = bits;
             __syncwarp();
@@ -249,17 +273,20 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
             // loaded while the current one is scanned (the order depends only on the box bounds; the gates only
             // shrink, so a bucket rejected now stays rejected).
             const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
-            while (sel >= 0 && !bucket_needed(sel)) sel = pick(1);
+            unsigned halves = 0;
+            while (sel >= 0 && !(halves = bucket_needed(sel))) sel = pick(1);
             if (sel < 0) continue;
             float4 cur = __ldg(base + sel * kLeaf);
             while (true) {
                 int nxt = pick(1);
-                while (nxt >= 0 && !bucket_needed(nxt)) nxt = pick(1);
+                unsigned nxt_halves = 0;
+                while (nxt >= 0 && !(nxt_halves = bucket_needed(nxt))) nxt = pick(1);
                 float4 pf = cur;
                 if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
-                scan_bucket(cur);
+                scan_bucket(cur, halves);
                 if (nxt < 0) break;
                 sel = nxt;
+                halves = nxt_halves;
                 cur = pf;
                 if (aborted || n_scan > max_scans || n_test > max_tests) break;
             }
@@ -271,10 +298,11 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         // tied distances: hand the group's queries to the warp-per-query kernel, which re-does them in parallel
         if (lane == 0) overflow[1 + atomicAdd(overflow, 1u)] = (unsigned)group;
         if (ctr && lane == 0) {
-            atomicAdd(ctr + 0, (unsigned long long)n_scan * kLeaf * n_active);
+            atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
             atomicAdd(ctr + 6, 1ull);
         }
-        return;
+        __syncwarp();
+        continue;
     }
 
     // ---- final selection: k (+ ties) candidates per lane, ranked by (float32 sqrt, index)
@@ -293,7 +321,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     }
 
     if (ctr && lane == 0) {
-        atomicAdd(ctr + 0, (unsigned long long)n_scan * kLeaf * n_active);
+        atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
         atomicAdd(ctr + 1, (unsigned long long)n_open * kFan + n_test);
         atomicAdd(ctr + 2, (unsigned long long)n_open);
         atomicAdd(ctr + 3, (unsigned long long)n_round);
@@ -301,20 +329,23 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         atomicAdd(ctr + 5, (unsigned long long)n_scan);
         if (dbg) { dbg[group * 4 + 0] = n_scan; dbg[group * 4 + 1] = n_test; dbg[group * 4 + 2] = n_round; dbg[group * 4 + 3] = n_open; }
     }
-    if (!active) return;
-    int cnt = 0;
+    if (active) {
+        int cnt = 0;
 #pragma unroll
-    for (int i = 0; i < K; ++i) {
-        if (i < k) {
-            const unsigned id = key_index(top.key[i]);
-            const bool filled = id != 0xffffffffu;
-            cnt += filled ? 1 : 0;
-            // result_set.py:19-22: unfilled slots read (1e10, 0)
-            out_idx[qid * k + i] = filled ? (int)id : 0;
-            out_dist[qid * k + i] = filled ? key_dist(top.key[i]) : PCP_KNN_EMPTY_DIST;
+        for (int i = 0; i < K; ++i) {
+            if (i < k) {
+                const unsigned id = key_index(top.key[i]);
+                const bool filled = id != 0xffffffffu;
+                cnt += filled ? 1 : 0;
+                // result_set.py:19-22: unfilled slots read (1e10, 0)
+                out_idx[qid * k + i] = filled ? (int)id : 0;
+                out_dist[qid * k + i] = filled ? key_dist(top.key[i]) : PCP_KNN_EMPTY_DIST;
+            }
         }
+        if (out_cnt) out_cnt[qid] = cnt;
     }
-    if (out_cnt) out_cnt[qid] = cnt;
+    __syncwarp();
+    }   // next group
 }
 
 template <bool SELF>
@@ -325,9 +356,11 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     const long long n_groups = SELF ? v.n_leaf : (nq + 31) / 32;
     unsigned long long *ctr = ctx->ctr();
     // overflow list: [0] = count, [1..] = group ids
-    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 1)));
+    // [n_groups + 1] = next group of the persistent tile warps
+    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 2)));
     unsigned *overflow = ctx->scratch[5].as<unsigned>();
     PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned), ctx->stream));
+    PCP_CUDA(cudaMemsetAsync(overflow + n_groups + 1, 0, sizeof(unsigned), ctx->stream));
     const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
     const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
     static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS"),
@@ -344,14 +377,16 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     do {                                                                                                               \
         constexpr int W = TileCfg<KK>::kWarps, CAP = TileCfg<KK>::kCap;                                                \
         const size_t smem = (size_t)W * CAP * 32 * sizeof(uint2);                                                      \
-        static bool attr_set = false;                                                                                  \
-        if (!attr_set) {                                                                                               \
+        static int ctas_per_sm = 0;                                                                                    \
+        if (!ctas_per_sm) {                                                                                            \
             PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            attr_set = true;                                                                                           \
+            PCP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, knn_tile_kernel<KK, SELF>, W * 32, smem)); \
+            ctas_per_sm = std::max(ctas_per_sm, 1);                                                                    \
         }                                                                                                              \
         /* compaction trigger: a column longer than this could overflow during the next chunk of evaluations */       \
         const int trig = e_trig ? std::min(atoi(e_trig), CAP - kChunk) : CAP - kChunk;                                 \
-        const unsigned grid = (unsigned)((n_groups + W - 1) / W);                                                      \
+        /* persistent grid: every resident warp slot, or fewer when there are not that many groups */                  \
+        const unsigned grid = (unsigned)std::min<long long>((n_groups + W - 1) / W, (long long)ctx->sm_count * ctas_per_sm); \
         knn_tile_kernel<KK, SELF><<<grid, W * 32, smem, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist,   \
                                                                        d_count, ctr, dbg, overflow, max_scans,         \
                                                                        max_tests, trig);                               \
