@@ -61,6 +61,15 @@ PCP_API int pcp_version(void);
 PCP_API const char *pcp_last_error(void);
 PCP_API int pcp_device_count(int *count);
 
+/* ---- pinned host buffers ---------------------------------------------------------------------
+ * Page-locked host memory from a process-wide pool (size classes, cached on free).  PCP_HOST calls
+ * whose input / output pointers are page-locked (from here or from any cudaHostAlloc / torch
+ * pin_memory) are copied by DMA straight from / to the caller's buffer; pageable pointers are staged.
+ * The pybind11 layer returns its result arrays in such buffers (owned by Python, returned to the pool
+ * when the array is collected -- the "outputs owned by Python" rule of keypoints.cpp:240-298). */
+PCP_API int pcp_host_alloc(size_t bytes, void **out);
+PCP_API int pcp_host_free(void *ptr);
+
 /* ---- context ------------------------------------------------------------------------------- */
 PCP_API int pcp_ctx_create(int device, pcp_ctx **out);
 PCP_API int pcp_ctx_destroy(pcp_ctx *ctx);

@@ -29,6 +29,21 @@ void check(int status, const char *what) {
     throw std::runtime_error(msg);
 }
 
+// Result arrays: page-locked buffers from the library's pool (DMA target of the device->host copy), owned by
+// the returned numpy array and handed back to the pool when it is collected.  Small results use numpy's own
+// allocator.
+template <class T>
+py::array_t<T> result_array(std::vector<py::ssize_t> shape) {
+    size_t count = 1;
+    for (py::ssize_t d : shape) count *= (size_t)d;
+    const size_t bytes = count * sizeof(T);
+    if (bytes < (64u << 10)) return py::array_t<T>(shape);
+    void *p = nullptr;
+    check(pcp_host_alloc(bytes, &p), "pcp_host_alloc");
+    py::capsule owner(p, [](void *q) { pcp_host_free(q); });
+    return py::array_t<T>(shape, static_cast<T *>(p), owner);
+}
+
 // rows x cols float32 view; the reference's clouds are (N, 3) (benchmark.py:19); (N, >=3) rows with
 // extra columns (KITTI intensity, Oxford normals) are accepted and only x,y,z are read.
 struct Cloud {
@@ -100,9 +115,9 @@ class Index {
     py::tuple knn(const py::object &queries, int k) {
         Cloud q(queries, "queries");
         if (k < 1) throw py::value_error("k must be >= 1");
-        py::array_t<int32_t> idx({(py::ssize_t)q.n, (py::ssize_t)k});
-        py::array_t<float> dist({(py::ssize_t)q.n, (py::ssize_t)k});
-        py::array_t<int32_t> cnt((py::ssize_t)q.n);
+        auto idx = result_array<int32_t>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto dist = result_array<float>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto cnt = result_array<int32_t>({(py::ssize_t)q.n});
         {
             py::gil_scoped_release rel;
             check_nogil(pcp_knn(ix_, q.data(), q.n, q.stride, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(),
@@ -114,9 +129,9 @@ class Index {
     py::tuple knn_self(int k) {
         if (k < 1) throw py::value_error("k must be >= 1");
         const int64_t n = size();
-        py::array_t<int32_t> idx({(py::ssize_t)n, (py::ssize_t)k});
-        py::array_t<float> dist({(py::ssize_t)n, (py::ssize_t)k});
-        py::array_t<int32_t> cnt((py::ssize_t)n);
+        auto idx = result_array<int32_t>({(py::ssize_t)n, (py::ssize_t)k});
+        auto dist = result_array<float>({(py::ssize_t)n, (py::ssize_t)k});
+        auto cnt = result_array<int32_t>({(py::ssize_t)n});
         {
             py::gil_scoped_release rel;
             check_nogil(pcp_knn_self(ix_, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(), cnt.mutable_data()),
@@ -142,8 +157,8 @@ class Index {
         check(pcp_radius_count(ix_, q.data(), q.n, q.stride, (float)radius, PCP_HOST, offsets.mutable_data()),
               "pcp_radius_count");
         const int64_t m = offsets.data()[q.n];
-        py::array_t<int32_t> idx((py::ssize_t)m);
-        py::array_t<float> dist((py::ssize_t)m);
+        auto idx = result_array<int32_t>({(py::ssize_t)m});
+        auto dist = result_array<float>({(py::ssize_t)m});
         check(pcp_radius_fill(ix_, q.data(), q.n, q.stride, (float)radius, PCP_HOST, offsets.data(),
                               idx.mutable_data(), dist.mutable_data(), sorted ? 1 : 0), "pcp_radius_fill");
         return py::make_tuple(offsets, idx, dist);

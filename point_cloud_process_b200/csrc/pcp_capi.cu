@@ -2,7 +2,10 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <new>
+#include <unordered_map>
 
 #include "pcp_internal.cuh"
 
@@ -116,6 +119,78 @@ extern "C" {
 int pcp_version(void) { return PCP_VERSION; }
 
 const char *pcp_last_error(void) { return g_last_error.c_str(); }
+
+// ---------------------------------------------------------------------------------------------- pinned pool
+namespace {
+struct HostPool {
+    std::mutex mu;
+    std::map<size_t, std::vector<void *>> free_by_class;     // size class -> cached buffers
+    std::unordered_map<void *, size_t> live;                 // buffer -> size class
+    size_t cached_bytes = 0;
+    static constexpr size_t kMaxCached = size_t(4) << 30;
+    static size_t size_class(size_t bytes) {
+        const size_t big = size_t(64) << 20;                 // powers of two up to 64 MB, then multiples of 64 MB
+        if (bytes > big) return (bytes + big - 1) / big * big;
+        size_t c = 4096;
+        while (c < bytes) c <<= 1;
+        return c;
+    }
+};
+HostPool &host_pool() {
+    static HostPool *p = new HostPool();   // never destroyed: buffers may outlive static destruction order
+    return *p;
+}
+}  // namespace
+
+int pcp_host_alloc(size_t bytes, void **out) {
+    if (!out) return fail(PCP_ERR_INVALID, "pcp_host_alloc: out is NULL");
+    *out = nullptr;
+    HostPool &hp = host_pool();
+    const size_t cls = HostPool::size_class(bytes);
+    {
+        std::lock_guard<std::mutex> lk(hp.mu);
+        auto it = hp.free_by_class.find(cls);
+        if (it != hp.free_by_class.end() && !it->second.empty()) {
+            *out = it->second.back();
+            it->second.pop_back();
+            hp.cached_bytes -= cls;
+            hp.live[*out] = cls;
+            return PCP_OK;
+        }
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, cls, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? PCP_ERR_OOM : PCP_ERR_CUDA,
+                    std::string("pcp_host_alloc: ") + cudaGetErrorString(e));
+    }
+    std::lock_guard<std::mutex> lk(hp.mu);
+    hp.live[p] = cls;
+    *out = p;
+    return PCP_OK;
+}
+
+int pcp_host_free(void *ptr) {
+    if (!ptr) return PCP_OK;
+    HostPool &hp = host_pool();
+    size_t cls = 0;
+    {
+        std::lock_guard<std::mutex> lk(hp.mu);
+        auto it = hp.live.find(ptr);
+        if (it == hp.live.end()) return fail(PCP_ERR_INVALID, "pcp_host_free: pointer was not returned by pcp_host_alloc");
+        cls = it->second;
+        hp.live.erase(it);
+        if (hp.cached_bytes + cls <= HostPool::kMaxCached) {
+            hp.free_by_class[cls].push_back(ptr);
+            hp.cached_bytes += cls;
+            return PCP_OK;
+        }
+    }
+    cudaFreeHost(ptr);
+    cudaGetLastError();
+    return PCP_OK;
+}
 
 int pcp_device_count(int *count) {
     if (!count) return fail(PCP_ERR_INVALID, "pcp_device_count: count is NULL");
