@@ -33,6 +33,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 KITTI = os.path.join(ROOT, "tests", "golden", "kitti_000000_xyz.f32")
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE knn_tile_kernel launch, from the ncu --set full capture of
+# this workload committed under profiles/ (bytes); updated by hand when the capture is redone.
+NCU_TRAFFIC = {}
 SM_COUNT_B200 = 148
 FP32_LANES_PER_SM = 128
 
@@ -317,6 +320,7 @@ def main():
     sampler = ClockSampler(local_rank)
     barrier()
     launches0 = ctx.launch_count()
+    ctx.enable_kernel_timing(True)      # event pair around every launch of the dominant kernel (knn_tile_kernel)
     sampler.start()
     t_wall0 = time.perf_counter()
     for i in range(K):
@@ -326,10 +330,13 @@ def main():
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.result()
     launches = ctx.launch_count() - launches0
+    tile_ms_total, tile_launches = ctx.read_kernel_timing()
+    ctx.enable_kernel_timing(False)
     step_ms = [e[0].elapsed_time(e[2]) for e in evs]
     build_ms = [e[0].elapsed_time(e[1]) for e in evs]
     knn_ms = [e[1].elapsed_time(e[2]) for e in evs]
     total_ms = sum(step_ms)
+    total_ms_local = total_ms
     if dist is not None:
         t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -341,19 +348,27 @@ def main():
     ix.knn_device(d_pts.data_ptr(), n, 3, k, idx.data_ptr(), dst.data_ptr(), cnt.data_ptr())
     ctrs = ctx.read_counters()
     ctx.enable_counters(False)
-    evals = int(ctrs[0])
+    evals_all = int(ctrs[0])
+    evals = evals_all - int(ctrs[7])            # evaluated by the tiled kernel itself (the rest: overflow groups)
     knn_s = statistics.mean(knn_ms) * 1e-3
+    tile_s = tile_ms_total / max(tile_launches, 1) * 1e-3
     sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
     fp32_peak = sm_count * FP32_LANES_PER_SM * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12   # T unfused FP32 op/s
-    achieved = 8.0 * evals / knn_s / 1e12
+    achieved = 8.0 * evals / tile_s / 1e12
     hbm_bytes = 16 * n + 12 * n + 8 * k * n + 4 * n
     roofline = {
-        "bound": "fp32", "kernel": "knn", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s (unfused FP32 ops; 8 per distance evaluation)",
-        "frac": achieved / fp32_peak, "traffic": None,
+        "bound": "fp32", "kernel": "knn_tile_kernel", "achieved": achieved, "peak": fp32_peak,
+        "unit": "TFLOP/s (unfused FP32 ops; 8 per distance evaluation)",
+        "frac": achieved / fp32_peak, "traffic": NCU_TRAFFIC.get(args.workload),
         "peak_source": f"{sm_count} SMs x 128 FP32 lanes x sm_max_mhz ({peaks_kind} MEASURED_PEAKS.json clock); no FP32 peak is measured by the driver",
-        "distance_evaluations_per_launch": evals, "evals_per_query": evals / n, "kernel_ms": knn_s * 1e3,
-        "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / knn_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
-                "frac": hbm_bytes / knn_s / 1e9 / peaks.get("hbm_gbs", 6533.8)},
+        "distance_evaluations_per_launch": evals, "evals_per_query": evals / n,
+        "kernel_ms": tile_s * 1e3, "kernel_launches_timed": int(tile_launches),
+        "kernel_share_of_step": tile_ms_total / total_ms_local,
+        "timer": "CUDA events recorded by the library on its own stream around every knn_tile_kernel launch of the timed region",
+        "whole_search": {"ms": knn_s * 1e3, "evals": evals_all, "fp32_frac": 8.0 * evals_all / knn_s / 1e12 / fp32_peak,
+                         "note": "query Morton sort + kd regrouping + tiled kernel + overflow kernel"},
+        "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / tile_s / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
+                "frac": hbm_bytes / tile_s / 1e9 / peaks.get("hbm_gbs", 6533.8)},
     }
 
     # ---- end to end through the public API with pinned host buffers (H2D + D2H inside)

@@ -79,12 +79,19 @@ PCP_API void *pcp_ctx_stream(pcp_ctx *ctx);
 /* Number of kernels this library has launched on the context since creation (bench bookkeeping). */
 PCP_API int64_t pcp_ctx_launch_count(pcp_ctx *ctx);
 
+/* Device time of the dominant search kernel (the tiled kNN kernel) alone: when enabled, every launch of it is
+ * bracketed by CUDA events on the context stream; pcp_ctx_read_kernel_timing synchronises, returns the summed
+ * milliseconds and the number of launches since the last read, and resets.  Bench bookkeeping (roofline). */
+PCP_API int pcp_ctx_enable_kernel_timing(pcp_ctx *ctx, int enable);
+PCP_API int pcp_ctx_read_kernel_timing(pcp_ctx *ctx, double *total_ms, int64_t *launches);
+
 /* Work counters -- the analogue of the reference's comparison_counter (result_set.py:24,36,70,79).
  * When enabled, search kernels accumulate into 8 device-side 64-bit words, read back (and reset)
  * by pcp_ctx_read_counters:
  *   [0] distance evaluations (query, point) pairs   [1] bucket lower-bound tests (per group / query)
  *   [2] hierarchy nodes opened                      [3] top-k drain rounds
- *   [4] query groups (kNN) or queries (radius)      [5] buckets scanned        [6..7] reserved
+ *   [4] query groups (kNN) or queries (radius)      [5] buckets scanned
+ *   [6] query groups handed to the warp-per-query kernel   [7] the part of [0] evaluated by that kernel
  * Counting costs a few instructions per bucket; it is OFF by default and off in timed runs. */
 PCP_API int pcp_ctx_enable_counters(pcp_ctx *ctx, int enable);
 PCP_API int pcp_ctx_read_counters(pcp_ctx *ctx, uint64_t out[8]);

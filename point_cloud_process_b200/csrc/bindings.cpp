@@ -73,6 +73,13 @@ class Context {
     int64_t launch_count() const { return pcp_ctx_launch_count(ctx_); }
     uintptr_t stream() const { return reinterpret_cast<uintptr_t>(pcp_ctx_stream(ctx_)); }
     void enable_counters(bool on) { check(pcp_ctx_enable_counters(ctx_, on ? 1 : 0), "pcp_ctx_enable_counters"); }
+    void enable_kernel_timing(bool on) { check(pcp_ctx_enable_kernel_timing(ctx_, on ? 1 : 0), "pcp_ctx_enable_kernel_timing"); }
+    py::tuple read_kernel_timing() {
+        double ms = 0.0;
+        int64_t n = 0;
+        check(pcp_ctx_read_kernel_timing(ctx_, &ms, &n), "pcp_ctx_read_kernel_timing");
+        return py::make_tuple(ms, n);
+    }
     std::vector<uint64_t> read_counters() {
         std::vector<uint64_t> v(8);
         check(pcp_ctx_read_counters(ctx_, v.data()), "pcp_ctx_read_counters");
@@ -302,7 +309,9 @@ PYBIND11_MODULE(_pcp, m) {
         .def("launch_count", &Context::launch_count)
         .def("stream", &Context::stream)
         .def("enable_counters", &Context::enable_counters, py::arg("on") = true)
-        .def("read_counters", &Context::read_counters);
+        .def("read_counters", &Context::read_counters)
+        .def("enable_kernel_timing", &Context::enable_kernel_timing)
+        .def("read_kernel_timing", &Context::read_kernel_timing);
 
     py::class_<Index>(m, "Index")
         .def(py::init<std::shared_ptr<Context>, const py::object &>(), py::arg("ctx"), py::arg("points"))

@@ -242,6 +242,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     ctx->icp_sources.release();
     for (auto &b : ctx->scratch) b.release();
     for (auto &b : ctx->pin) b.release();
+    for (auto &e : ctx->timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PCP_OK;
@@ -257,6 +258,29 @@ int pcp_ctx_synchronize(pcp_ctx *ctx) {
 void *pcp_ctx_stream(pcp_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 
 int64_t pcp_ctx_launch_count(pcp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int pcp_ctx_enable_kernel_timing(pcp_ctx *ctx, int enable) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ctx_enable_kernel_timing: ctx is NULL");
+    ctx->time_kernels = enable != 0;
+    ctx->timing_used = 0;
+    return PCP_OK;
+}
+
+int pcp_ctx_read_kernel_timing(pcp_ctx *ctx, double *total_ms, int64_t *launches) {
+    if (!ctx || !total_ms || !launches) return fail(PCP_ERR_INVALID, "pcp_ctx_read_kernel_timing: NULL argument");
+    DeviceGuard g(ctx->device);
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    double sum = 0.0;
+    for (size_t i = 0; i < ctx->timing_used; ++i) {
+        float ms = 0.f;
+        PCP_CUDA(cudaEventElapsedTime(&ms, ctx->timing_events[i].first, ctx->timing_events[i].second));
+        sum += ms;
+    }
+    *total_ms = sum;
+    *launches = (int64_t)ctx->timing_used;
+    ctx->timing_used = 0;
+    return PCP_OK;
+}
 
 int pcp_ctx_enable_counters(pcp_ctx *ctx, int enable) {
     if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ctx_enable_counters: ctx is NULL");

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "pcp.h"
@@ -108,6 +109,11 @@ struct pcp_ctx {
     pcp::BatchIndex icp_sources;   // Morton buckets of the ICP source clouds (query groups of the tiled association)
     pcp::BatchIndex icp_targets;   // hierarchies of the ICP target clouds (pcp_icp_batch), reused across calls
     bool count_work = false;
+    // optional timing of the dominant kernel (pcp_ctx_enable_kernel_timing): event pairs around every
+    // knn_tile_kernel launch, summed by pcp_ctx_read_kernel_timing
+    bool time_kernels = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
+    size_t timing_used = 0;
     unsigned long long *ctr() const { return count_work ? counters.as<unsigned long long>() : nullptr; }
 };
 

@@ -160,11 +160,17 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         }
         // candidates whose float32 sqrt can still tie the k-th distance stay (canonical (distance, index) order)
         if (l[K - 1] < inf) gate = fminf(gate, d2_gate(__fsqrt_rn(l[K - 1])));
+        // in place: the write position never passes the read position, so loading 4 entries ahead of the stores
+        // they may alias is safe (and lets the loads overlap)
         unsigned w = 0;
-#pragma unroll 2
-        for (int e = 0; e < nmax; ++e) {
-            const uint2 ent = col[e * 32];
-            if (e < cnt && __uint_as_float(ent.x) <= gate) { col[w] = ent; w += 32; }
+#pragma unroll 1
+        for (int e0 = 0; e0 < nmax; e0 += 4) {
+            uint2 ent[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ent[i] = e0 + i < nmax ? col[(e0 + i) * 32] : make_uint2(kInfBits, 0u);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (e0 + i < cnt && __uint_as_float(ent[i].x) <= gate) { col[w] = ent[i]; w += 32; }
         }
         waddr = col_addr + w * 8;
         n_old = (int)(w >> 5);
@@ -391,6 +397,18 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
                                                                        d_count, ctr, dbg, overflow, max_scans,         \
                                                                        max_tests, trig);                               \
     } while (0)
+    cudaEvent_t ev_end = nullptr;
+    if (ctx->time_kernels) {
+        if (ctx->timing_used == ctx->timing_events.size()) {
+            cudaEvent_t a, b;
+            PCP_CUDA(cudaEventCreate(&a));
+            PCP_CUDA(cudaEventCreate(&b));
+            ctx->timing_events.emplace_back(a, b);
+        }
+        PCP_CUDA(cudaEventRecord(ctx->timing_events[ctx->timing_used].first, ctx->stream));
+        ev_end = ctx->timing_events[ctx->timing_used].second;
+        ++ctx->timing_used;
+    }
     if (k == 1) PCP_TILE(1);
     else if (k == 2) PCP_TILE(2);
     else if (k <= 4) PCP_TILE(4);
@@ -398,6 +416,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     else if (k <= 16) PCP_TILE(16);
     else PCP_TILE(32);
 #undef PCP_TILE
+    if (ev_end) PCP_CUDA(cudaEventRecord(ev_end, ctx->stream));
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     if (dump) {
