@@ -126,67 +126,106 @@ constexpr unsigned kPadKey = 0xffffffffu;
 
 struct RefineSmem {
     float x[kRefine], y[kRefine], z[kRefine];
-    unsigned key[kRefine];
+    unsigned key[2][kRefine];                  // double-buffered exchange: one barrier per cross-warp stage
     unsigned box[32][6];                       // per segment: ordered-uint min xyz, max xyz
 };
 
-// Thread t owns slot t.  In: its element's coordinates (valid = real point).  Out: the element id (0..1023,
-// the slot that loaded it) that ends up in slot t; coordinates stay addressable by id in sm.x/y/z.
-__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid, int levels) {
+// One compare-exchange stage of the direction-free bitonic network: slot t against slot t ^ MASK, the slot
+// whose BIT is clear keeps the smaller key.  Masks below 32 exchange by shuffle, larger ones through shared memory.
+template <unsigned MASK, unsigned BIT>
+__device__ __forceinline__ void refine_stage(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
+    unsigned other;
+    if (MASK >= 32) {
+        sm.key[phase][t] = key;
+        __syncthreads();
+        other = sm.key[phase][t ^ MASK];
+        phase ^= 1u;                           // the next exchange writes the other buffer: no second barrier
+    } else {
+        other = __shfl_xor_sync(kFullMask, key, MASK);
+    }
+    key = (t & BIT) == 0 ? min(key, other) : max(key, other);
+}
+
+// merge step K of the network (blocks of K become sorted): mirror stage, then strides K/4 ... 1
+template <unsigned K, unsigned J>
+struct RefineMerge {
+    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
+        refine_stage<J, J>(sm, key, t, phase);
+        RefineMerge<K, J / 2>::run(sm, key, t, phase);
+    }
+};
+template <unsigned K>
+struct RefineMerge<K, 0> {
+    static __device__ __forceinline__ void run(RefineSmem &, unsigned &, unsigned, unsigned &) {}
+};
+// ascending sort of every aligned segment of S slots, fully unrolled: K = 2, 4, ..., S
+template <unsigned S, unsigned K = 2>
+struct RefineSort {
+    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
+        refine_stage<K - 1, K / 2>(sm, key, t, phase);          // slot i of a block against slot K-1-i
+        RefineMerge<K, K / 4>::run(sm, key, t, phase);
+        RefineSort<S, K * 2>::run(sm, key, t, phase);
+    }
+};
+template <unsigned S>
+struct RefineSort<S, 2 * S> {
+    static __device__ __forceinline__ void run(RefineSmem &, unsigned &, unsigned, unsigned &) {}
+};
+
+// One level of the kd refinement: every aligned segment of S slots is sorted along its widest axis, which splits
+// it at the median into two segments of S/2.
+template <unsigned S>
+__device__ __forceinline__ void refine_level(RefineSmem &sm, unsigned &id, bool &real, unsigned &phase) {
     const unsigned t = threadIdx.x;
-    sm.x[t] = x; sm.y[t] = y; sm.z[t] = z;
-    unsigned id = t;
-    bool real = valid;
-#pragma unroll 1
-    for (int d = 0; d < levels; ++d) {     // levels = 5: segments of 32 (buckets / query groups); 6: halves of 16
-        const unsigned S = kRefine >> d;       // segment size
-        const unsigned seg = t / S;
-        // ---- widest axis of every segment
-        if (t < 32 * 6) sm.box[t / 6][t % 6] = (t % 6) < 3 ? 0xffffffffu : 0u;
-        __syncthreads();                       // also orders the sm.x/y/z stores before the first gather
-        const float ex = sm.x[id], ey = sm.y[id], ez = sm.z[id];
-        const unsigned ox = float_to_ordered(ex), oy = float_to_ordered(ey), oz = float_to_ordered(ez);
-        {
-            // a warp never straddles segments (S >= 32)
-            const unsigned mnx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), mxx = __reduce_max_sync(kFullMask, real ? ox : 0u);
-            const unsigned mny = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), mxy = __reduce_max_sync(kFullMask, real ? oy : 0u);
-            const unsigned mnz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), mxz = __reduce_max_sync(kFullMask, real ? oz : 0u);
-            if ((t & 31) == 0) {
+    const unsigned seg = t / S;
+    // ---- widest axis of every segment
+    if (t < 32 * 6) sm.box[t / 6][t % 6] = (t % 6) < 3 ? 0xffffffffu : 0u;
+    __syncthreads();                           // also orders the sm.x/y/z stores before the first gather
+    const unsigned ox = float_to_ordered(sm.x[id]), oy = float_to_ordered(sm.y[id]), oz = float_to_ordered(sm.z[id]);
+    {
+        // a warp never straddles segments (S >= 32)
+        const unsigned mnx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), mxx = __reduce_max_sync(kFullMask, real ? ox : 0u);
+        const unsigned mny = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), mxy = __reduce_max_sync(kFullMask, real ? oy : 0u);
+        const unsigned mnz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), mxz = __reduce_max_sync(kFullMask, real ? oz : 0u);
+        if ((t & 31) == 0) {
+            if (S > 32) {
                 atomicMin(&sm.box[seg][0], mnx); atomicMin(&sm.box[seg][1], mny); atomicMin(&sm.box[seg][2], mnz);
                 atomicMax(&sm.box[seg][3], mxx); atomicMax(&sm.box[seg][4], mxy); atomicMax(&sm.box[seg][5], mxz);
+            } else {
+                sm.box[seg][0] = mnx; sm.box[seg][1] = mny; sm.box[seg][2] = mnz;
+                sm.box[seg][3] = mxx; sm.box[seg][4] = mxy; sm.box[seg][5] = mxz;
             }
         }
-        __syncthreads();
-        const float wx = ordered_to_float(sm.box[seg][3]) - ordered_to_float(sm.box[seg][0]);
-        const float wy = ordered_to_float(sm.box[seg][4]) - ordered_to_float(sm.box[seg][1]);
-        const float wz = ordered_to_float(sm.box[seg][5]) - ordered_to_float(sm.box[seg][2]);
-        // empty segments give NaN / negative widths: any axis will do
-        const unsigned okey = (wx >= wy && wx >= wz) ? ox : (wy >= wz ? oy : oz);
-        // 22 coordinate bits + 10 slot bits in one word: the split is a partition heuristic, the slot makes keys
-        // unique and the order deterministic; pads carry the largest key
-        unsigned key = ((real ? okey : kPadKey) & ~(kRefine - 1u)) | id;
-        // ---- bitonic sort of the segment (ascending)
-#pragma unroll 1
-        for (unsigned k = 2; k <= S; k <<= 1) {
-#pragma unroll 1
-            for (unsigned j = k >> 1; j > 0; j >>= 1) {
-                unsigned other;
-                if (j >= 32) {
-                    __syncthreads();
-                    sm.key[t] = key;
-                    __syncthreads();
-                    other = sm.key[t ^ j];
-                } else {
-                    other = __shfl_xor_sync(kFullMask, key, j);
-                }
-                const bool up = ((t & k) == 0) || k == S;
-                const bool lower = (t & j) == 0;
-                key = (up == lower) ? min(key, other) : max(key, other);
-            }
-        }
-        id = key & (kRefine - 1u);
-        real = (key | (kRefine - 1u)) != kPadKey;
     }
+    __syncthreads();
+    const float wx = ordered_to_float(sm.box[seg][3]) - ordered_to_float(sm.box[seg][0]);
+    const float wy = ordered_to_float(sm.box[seg][4]) - ordered_to_float(sm.box[seg][1]);
+    const float wz = ordered_to_float(sm.box[seg][5]) - ordered_to_float(sm.box[seg][2]);
+    // empty segments give NaN / negative widths: any axis will do
+    const unsigned okey = (wx >= wy && wx >= wz) ? ox : (wy >= wz ? oy : oz);
+    // 22 coordinate bits + 10 slot bits in one word: the split is a partition heuristic, the slot makes keys
+    // unique and the order deterministic; pads carry the largest key
+    unsigned key = ((real ? okey : kPadKey) & ~(kRefine - 1u)) | id;
+    RefineSort<S>::run(sm, key, t, phase);
+    id = key & (kRefine - 1u);
+    real = (key | (kRefine - 1u)) != kPadKey;
+}
+
+// Thread t owns slot t.  In: its element's coordinates (valid = real point).  Out: the element id (0..1023,
+// the slot that loaded it) that ends up in slot t; coordinates stay addressable by id in sm.x/y/z.
+// HALVES: a sixth level splits the 32-slot segments (buckets) into halves of 16.
+template <bool HALVES>
+__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid) {
+    const unsigned t = threadIdx.x;
+    sm.x[t] = x; sm.y[t] = y; sm.z[t] = z;
+    unsigned id = t, phase = 0;
+    bool real = valid;
+    refine_level<1024>(sm, id, real, phase);
+    refine_level<512>(sm, id, real, phase);
+    refine_level<256>(sm, id, real, phase);
+    refine_level<128>(sm, id, real, phase);
+    refine_level<64>(sm, id, real, phase);
+    if (HALVES) refine_level<32>(sm, id, real, phase);
     return id;
 }
 
@@ -213,7 +252,7 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
         idx = row - static_cast<unsigned>(v.src_off);
     }
     s_idx[t] = idx;
-    const unsigned id = refine_block(sm, x, y, z, valid, 6);
+    const unsigned id = refine_block<true>(sm, x, y, z, valid);
     const long long leaf = pos >> 5;
     if (leaf >= v.n_leaf) return;                                // whole warp: bucket beyond the cloud
     x = sm.x[id]; y = sm.y[id]; z = sm.z[id];
@@ -259,7 +298,7 @@ __global__ void __launch_bounds__(kRefine) refine_queries_kernel(const float *__
         x = p[0]; y = p[1]; z = p[2];
     }
     s_idx[t] = row;
-    const unsigned id = refine_block(sm, x, y, z, valid, 5);
+    const unsigned id = refine_block<false>(sm, x, y, z, valid);
     if (valid) perm[pos] = s_idx[id];          // real queries stay at the front of the block: slot t < nq - base is real
 }
 
