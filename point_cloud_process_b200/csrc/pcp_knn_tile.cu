@@ -44,7 +44,7 @@ constexpr unsigned kTestsPerSlot = 12;
 // Candidate-buffer geometry per result capacity K: CAP entries per lane (a chunk of 8 evaluations appends at
 // most 8, a compaction leaves k + ties), WARPS groups per CTA.  Shared memory per CTA = WARPS * CAP * 256 B.
 constexpr int kChunk = 8;
-template <int K> struct TileCfg { static constexpr int kCap = 30, kWarps = 4; };
+template <int K> struct TileCfg { static constexpr int kCap = 29, kWarps = 4; };
 template <> struct TileCfg<16> { static constexpr int kCap = 40, kWarps = 4; };
 template <> struct TileCfg<32> { static constexpr int kCap = 72, kWarps = 2; };
 // Children whose box overlaps the group box (lower bound 0) are visited in the order of their centre distance:
@@ -146,11 +146,14 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         const int cnt = (int)((waddr - col_addr) >> 8);
         const int n_new = __reduce_max_sync(kFullMask, cnt - n_old);
         const int nmax = __reduce_max_sync(kFullMask, cnt);
-        n_round += n_new;
         const uint2 *src_new = col + n_old * 32;
 #pragma unroll 2
         for (int e = 0; e < n_new; ++e) {
             float v = n_old + e < cnt ? __uint_as_float(src_new[e * 32].x) : inf;
+            // the lists tighten as the merge proceeds: a round in which no lane's candidate still beats its
+            // k-th distance changes nothing
+            if (!__any_sync(kFullMask, v < l[K - 1])) continue;
+            ++n_round;
 #pragma unroll
             for (int i = 0; i < K; ++i) {
                 const float lo = fminf(v, l[i]);
@@ -160,20 +163,26 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         }
         // candidates whose float32 sqrt can still tie the k-th distance stay (canonical (distance, index) order)
         if (l[K - 1] < inf) gate = fminf(gate, d2_gate(__fsqrt_rn(l[K - 1])));
-        // in place: the write position never passes the read position, so loading 4 entries ahead of the stores
-        // they may alias is safe (and lets the loads overlap)
-        unsigned w = 0;
+        // In-place filter.  The write position never passes the read position, so loading 4 entries ahead of the
+        // stores they may alias is safe (and lets the loads overlap); the loads may run up to 3 entries past the
+        // longest column (the buffer is padded for it), the `< end` test discards them.
+        unsigned w = col_addr;
+        const unsigned end = waddr;
 #pragma unroll 1
-        for (int e0 = 0; e0 < nmax; e0 += 4) {
-            uint2 ent[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) ent[i] = e0 + i < nmax ? col[(e0 + i) * 32] : make_uint2(kInfBits, 0u);
+        for (unsigned r = col_addr; r < col_addr + (unsigned)nmax * 256u; r += 4 * 256u) {
+            float d[4], x[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                if (e0 + i < cnt && __uint_as_float(ent[i].x) <= gate) { col[w] = ent[i]; w += 32; }
+                asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(d[i]), "=f"(x[i]) : "r"(r + i * 256u) : "memory");
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (r + i * 256u < end && d[i] <= gate) {
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(w), "f"(d[i]), "f"(x[i]) : "memory");
+                    w += 256u;
+                }
         }
-        waddr = col_addr + w * 8;
-        n_old = (int)(w >> 5);
+        waddr = w;
+        n_old = (int)((w - col_addr) >> 8);
         group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
     };
 
@@ -382,7 +391,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
 #define PCP_TILE(KK)                                                                                                   \
     do {                                                                                                               \
         constexpr int W = TileCfg<KK>::kWarps, CAP = TileCfg<KK>::kCap;                                                \
-        const size_t smem = (size_t)W * CAP * 32 * sizeof(uint2);                                                      \
+        const size_t smem = (size_t)W * CAP * 32 * sizeof(uint2) + 3 * 32 * sizeof(uint2); /* + filter read-ahead */   \
         static int ctas_per_sm = 0;                                                                                    \
         if (!ctas_per_sm) {                                                                                            \
             PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
