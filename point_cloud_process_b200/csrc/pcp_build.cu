@@ -483,6 +483,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
 int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride) {
     if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_index_build: more than 2^31-1 points");
     ix->n = n;
+    ++ix->serial;
     ix->b.ctx = ix->ctx;
     const int64_t offs[2] = {0, n};
     return batch_build_device(&ix->b, d_xyz, stride, 1, offs);

@@ -238,6 +238,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     ctx->cub_tmp.release();
     ctx->counters.release();
+    ctx->radius_perm.release();
     ctx->icp_targets.release();
     ctx->icp_sources.release();
     for (auto &b : ctx->scratch) b.release();

@@ -108,6 +108,10 @@ struct pcp_ctx {
     pcp::DevBuf counters;          // 8 x u64 work counters (pcp_ctx_enable_counters)
     pcp::BatchIndex icp_sources;   // Morton buckets of the ICP source clouds (query groups of the tiled association)
     pcp::BatchIndex icp_targets;   // hierarchies of the ICP target clouds (pcp_icp_batch), reused across calls
+    // Morton/kd regrouping of the query set of the last pcp_radius_count, reused by the pcp_radius_fill that
+    // follows it (the two-phase API passes the same queries twice): valid while the tag matches
+    pcp::DevBuf radius_perm;
+    struct { const void *q = nullptr; int64_t nq = 0, stride = 0; const void *ix = nullptr; uint64_t serial = 0; } radius_perm_tag;
     bool count_work = false;
     // optional timing of the dominant kernel (pcp_ctx_enable_kernel_timing): event pairs around every
     // knn_tile_kernel launch, summed by pcp_ctx_read_kernel_timing
@@ -120,6 +124,7 @@ struct pcp_ctx {
 struct pcp_index {
     pcp_ctx *ctx = nullptr;
     int64_t n = 0;
+    uint64_t serial = 0;     // bumped by every (re)build
     pcp::BatchIndex b;       // P == 1
     pcp::DevBuf src_copy;
 };
@@ -149,6 +154,9 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
                         int64_t *d_offsets);
 int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
                        const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted);
+// tiled kernel (pcp_radius_tile.cu): COUNT when d_counts != nullptr, else FILL
+int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
+                       long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist);
 
 // icp (pcp_icp.cu)
 int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, const float *d_src,

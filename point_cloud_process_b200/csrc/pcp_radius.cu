@@ -15,6 +15,8 @@
 #include <cub/device/device_segmented_sort.cuh>
 
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 
 #include "pcp_device.cuh"
 #include "pcp_internal.cuh"
@@ -120,6 +122,37 @@ radius_kernel(const IndexView ix, const float *__restrict__ queries, long long n
 // counts (nq) -> offsets (nq+1) with offsets[0] = 0
 __global__ void set_zero_kernel(long long *p) { *p = 0; }
 
+// Below this many queries the warp-per-query kernel wins (no query sort, 32x more warps).
+constexpr int64_t kTileMinQueries = 8192;
+
+// 0 = by query count, 1 = warp-per-query, 2 = tiled (PCP_RADIUS_KERNEL=warp|tile, for tests)
+int radius_kernel_choice() {
+    static const int choice = [] {
+        const char *e = getenv("PCP_RADIUS_KERNEL");
+        if (!e) return 0;
+        return strcmp(e, "warp") == 0 ? 1 : strcmp(e, "tile") == 0 ? 2 : 0;
+    }();
+    return choice;
+}
+bool use_tile(int64_t nq) {
+    const int c = radius_kernel_choice();
+    return c == 2 || (c == 0 && nq >= kTileMinQueries);
+}
+
+// Regrouped order of the query set (sort_queries), cached between the count and the fill pass.
+int radius_query_perm(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, bool reuse, const uint32_t **out) {
+    pcp_ctx *ctx = ix->ctx;
+    auto &tag = ctx->radius_perm_tag;
+    const bool valid = reuse && tag.q == d_q && tag.nq == nq && tag.stride == stride && tag.ix == ix && tag.serial == ix->serial;
+    if (!valid) {
+        PCP_TRY(ctx->radius_perm.ensure(sizeof(uint32_t) * (size_t)nq));
+        PCP_TRY(sort_queries(ix, d_q, nq, stride, ctx->radius_perm.as<uint32_t>()));
+        tag.q = d_q; tag.nq = nq; tag.stride = stride; tag.ix = ix; tag.serial = ix->serial;
+    }
+    *out = ctx->radius_perm.as<uint32_t>();
+    return PCP_OK;
+}
+
 }  // namespace
 
 int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
@@ -136,10 +169,16 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
     }
     const float d2max = exact_d2_threshold(radius);
     const IndexView v = make_view(ix);
-    const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-    radius_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
-                                                                     nullptr, nullptr, ctx->ctr());
-    ctx->launches += 1;
+    if (use_tile(nq)) {
+        const uint32_t *perm = nullptr;
+        PCP_TRY(radius_query_perm(ix, d_q, nq, stride, false, &perm));
+        PCP_TRY(radius_tile_device(ix, d_q, nq, stride, perm, d2max, counts, nullptr, nullptr, nullptr));
+    } else {
+        const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
+        radius_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
+                                                                         nullptr, nullptr, ctx->ctr());
+        ctx->launches += 1;
+    }
     size_t tmp = 0;
     PCP_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp, counts, reinterpret_cast<long long *>(d_offsets) + 1, nq,
                                            ctx->stream));
@@ -173,10 +212,22 @@ int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
     if (nq == 0 || ix->n == 0) return PCP_OK;
     const float d2max = exact_d2_threshold(radius);
     const IndexView v = make_view(ix);
-    const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-    radius_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
-        v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr());
-    ctx->launches += 1;
+    // The tiled FILL writes every hit with a scattered 4-byte store (one cursor per lane): on dense results
+    // (KITTI r = 1.0: 644 hits per query) that is 5x slower than the warp kernel's ballot-compacted coalesced
+    // rows, on sparse ones (uniform r = 0.5: 32 hits) it is a tie -- so the warp kernel fills unless
+    // PCP_RADIUS_FILL=tile (tests keep the path alive).
+    static const bool tile_fill = [] { const char *e = getenv("PCP_RADIUS_FILL"); return e && strcmp(e, "tile") == 0; }();
+    if (use_tile(nq) && tile_fill) {
+        const uint32_t *perm = nullptr;
+        PCP_TRY(radius_query_perm(ix, d_q, nq, stride, true, &perm));
+        PCP_TRY(radius_tile_device(ix, d_q, nq, stride, perm, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets),
+                                   d_idx, d_dist));
+    } else {
+        const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
+        radius_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
+            v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr());
+        ctx->launches += 1;
+    }
     PCP_CUDA(cudaGetLastError());
     if (!sorted) return PCP_OK;
     // ascending (distance, index) inside every CSR segment: what RadiusNNResultSet.__str__ prints

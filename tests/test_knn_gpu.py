@@ -193,3 +193,68 @@ def test_knn_uniform_1m_properties(pcp):
     from oracle import knn_oracle
     b_dist, b_idx, _ = knn_oracle.bruteforce_knn(db, db[qi[:256]], 16, threads=8)
     assert np.array_equal(dist[qi[:256]], b_dist) and np.array_equal(idx[qi[:256]], b_idx.astype(np.int32))
+
+
+def test_knn_mass_ties_tile_kernel(pcp):
+    """Tiled kernel with masses of exactly tied distances (every point repeated 40 times): the candidate
+    columns stay full after a compaction and the group must take the overflow path; canonical
+    (distance, index) order vs brute force."""
+    from oracle import knn_oracle
+    rng = np.random.default_rng(11)
+    base = (rng.random((400, 3)) * 10).astype(np.float32)
+    db = np.repeat(base, 40, axis=0)
+    db = db[rng.permutation(len(db))]
+    assert len(db) >= 8192                                   # large enough for the tiled path
+    idx, dist, cnt = pcp.SearchIndex(db).knn(db, 8)
+    sel = rng.choice(len(db), 1024, replace=False)
+    b_dist, b_idx, b_cnt = knn_oracle.bruteforce_knn(db, db[sel], 8, threads=8)
+    assert np.array_equal(dist[sel], b_dist) and np.array_equal(idx[sel], b_idx.astype(np.int32))
+    assert (cnt == 8).all() and (dist == 0).all()
+
+
+def test_result_arrays_outlive_index_and_pool_reuse(pcp, kitti):
+    """Results come back in page-locked pool buffers owned by the numpy arrays: they stay valid after the
+    index is gone, and a collected result hands its buffer back (a second call must not corrupt a live one)."""
+    ix = pcp.SearchIndex(kitti)
+    idx1, dist1, cnt1 = ix.knn(kitti, 8)
+    keep = idx1.copy(), dist1.copy()
+    idx2, dist2, _ = ix.knn(kitti[::-1].copy(), 8)           # new buffers while the first results are alive
+    del ix
+    assert np.array_equal(idx1, keep[0]) and np.array_equal(dist1, keep[1])
+    assert np.array_equal(idx2[::-1], idx1)
+    del idx2, dist2
+    idx3, dist3, _ = pcp.SearchIndex(kitti).knn(kitti, 8)    # reuses the freed pool buffers
+    assert np.array_equal(idx3, keep[0]) and np.array_equal(idx1, keep[0])
+
+
+def test_kernel_timing_api(pcp, kitti):
+    ctx = pcp.native.Context(0)
+    ix = pcp.native.Index(ctx, kitti)
+    ctx.enable_kernel_timing(True)
+    ix.knn(kitti, 8)
+    ix.knn(kitti, 8)
+    ms, n = ctx.read_kernel_timing()
+    assert n == 2 and 0.0 < ms < 50.0
+    ms, n = ctx.read_kernel_timing()
+    assert n == 0 and ms == 0.0
+    ctx.enable_kernel_timing(False)
+
+
+def test_radius_tiled_fill_matches(kitti):
+    """PCP_RADIUS_FILL=tile (the tiled FILL pass, off by default) gives the same CSR as the default path."""
+    import os, subprocess, sys, tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import point_cloud_process_b200 as pcp;"
+            "k = np.fromfile(%r, np.float32).reshape(-1, 3); q = k[::8];"
+            "off, idx, dist = pcp.SearchIndex(k).radius(q, 1.0, sorted=True);"
+            "np.savez(sys.argv[1], off=off, idx=idx, dist=dist)") % (root, os.path.join(root, "tests", "golden", "kitti_000000_xyz.f32"))
+    outs = []
+    with tempfile.TemporaryDirectory() as tmp:
+        for mode in ("warp", "tile"):
+            path = os.path.join(tmp, mode + ".npz")
+            env = dict(os.environ, PCP_RADIUS_FILL=mode, PCP_RADIUS_KERNEL="tile")
+            r = subprocess.run([sys.executable, "-c", code, path], env=env, capture_output=True, text=True, timeout=300)
+            assert r.returncode == 0, r.stderr[-2000:]
+            outs.append(dict(np.load(path)))
+    for key in ("off", "idx", "dist"):
+        assert np.array_equal(outs[0][key], outs[1][key]), key
