@@ -243,18 +243,20 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long group = (long long)chunk * kTileAssocWarps + warp;
     const IndexView &ix = tgt_views[pair];
-    double acc[kSums];
-#pragma unroll
-    for (int i = 0; i < kSums; ++i) acc[i] = 0.0;
+    // the matched pair of this lane (set by the search below); the 16 sums are formed only afterwards so that
+    // they do not occupy registers during the search
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    float bx = 0.f, by = 0.f, bz = 0.f;
+    bool matched = false;
 
     if (group < sx.n_leaf) {                                   // warp-uniform
         const float4 sp = __ldg(sx.pts + group * kLeaf + lane);
         const bool active = (int)__float_as_uint(sp.w) >= 0;   // pad lanes carry index -1
         // main.py:110 in float64: composed pose applied to the original point
         const double x = (double)sp.x, y = (double)sp.y, z = (double)sp.z;
-        const double ax = st.applied[0] * x + st.applied[1] * y + st.applied[2] * z + st.applied[3];
-        const double ay = st.applied[4] * x + st.applied[5] * y + st.applied[6] * z + st.applied[7];
-        const double az = st.applied[8] * x + st.applied[9] * y + st.applied[10] * z + st.applied[11];
+        ax = st.applied[0] * x + st.applied[1] * y + st.applied[2] * z + st.applied[3];
+        ay = st.applied[4] * x + st.applied[5] * y + st.applied[6] * z + st.applied[7];
+        az = st.applied[8] * x + st.applied[9] * y + st.applied[10] * z + st.applied[11];
         const float qx = (float)ax, qy = (float)ay, qz = (float)az;
         const float E = __double2float_ru(1.04e-7 * (fabs(ax) + fabs(ay) + fabs(az)));
         float3 glo, ghi;
@@ -264,7 +266,6 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
 
         double best = dist_thres;                              // only d^2 < dist_thres matters (main.py:119)
         unsigned best_id = kDone;
-        float bx = 0.f, by = 0.f, bz = 0.f;
         float gate = active ? nn1_gate_fast(best, E) : -1.f;
         unsigned group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
 
@@ -273,16 +274,34 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
         auto bucket_needed = [&](int c) -> bool {
             return __ballot_sync(kFullMask, box_lb2(qx, qy, qz, boxes[2 * c], boxes[2 * c + 1]) <= gate) != 0;
         };
+        float m32 = __int_as_float(0x7f800000);                // smallest float32 d^2 this lane has seen
         auto scan_bucket = [&](const float4 pv) {
             __syncwarp();
             tile[lane] = pv;
             __syncwarp();
             unsigned mask = 0;
+            // 8 points at a time.  The gate is tightened INSIDE the scan from the running float32 minimum: a point
+            // whose float32 d^2 is m has a true d^2 <= (sqrt(m) + 2.5 E)^2 (1 + 6 eps), and whatever beats or ties it
+            // has a float32 d^2 <= (sqrt(m) + 3.5 E)^2 (1 + 12 eps) -- bounded here by (sqrt(m)(1 + 2e-6) + 4 E)^2
+            // rounded up.  Only "record setters" of the float32 scan reach the float64 evaluation below (a handful
+            // per bucket instead of every point inside the initial dist_thres ball).
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const float4 p = tile[j];
-                const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
-                if (d2 <= gate) mask |= 1u << j;               // NaN pads never pass
+            for (int j0 = 0; j0 < 32; j0 += 8) {
+                float d2[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 p = tile[j0 + j];
+                    d2[j] = ref_d2(qx, qy, qz, p.x, p.y, p.z);
+                }
+                float cm = fminf(fminf(fminf(d2[0], d2[1]), fminf(d2[2], d2[3])), fminf(fminf(d2[4], d2[5]), fminf(d2[6], d2[7])));
+                if (cm < m32) {                                  // NaN pads never lower the minimum
+                    m32 = cm;
+                    const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(cm), 1.000002f), __fmul_ru(4.f, E));
+                    gate = fminf(gate, __fmul_ru(r, r));
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (d2[j] <= gate) mask |= 1u << (j0 + j);   // NaN pads never pass
             }
             bool changed = false;
             while (__any_sync(kFullMask, mask != 0)) {
@@ -299,7 +318,7 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                     }
                 }
             }
-            if (changed) gate = nn1_gate_fast(best, E);
+            if (changed) gate = fminf(gate, nn1_gate_fast(best, E));
             group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
         };
 
@@ -370,15 +389,19 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                 }
             }
         }
-        if (active && best_id != kDone && best < dist_thres) {   // main.py:119
-            const double tx = (double)bx, ty = (double)by, tz = (double)bz;
-            acc[0] = 1.0;
-            acc[1] = ax; acc[2] = ay; acc[3] = az;
-            acc[4] = tx; acc[5] = ty; acc[6] = tz;
-            acc[7] = tx * ax; acc[8] = tx * ay; acc[9] = tx * az;
-            acc[10] = ty * ax; acc[11] = ty * ay; acc[12] = ty * az;
-            acc[13] = tz * ax; acc[14] = tz * ay; acc[15] = tz * az;
-        }
+        matched = active && best_id != kDone && best < dist_thres;   // main.py:119
+    }
+    double acc[kSums];
+#pragma unroll
+    for (int i = 0; i < kSums; ++i) acc[i] = 0.0;
+    if (matched) {
+        const double tx = (double)bx, ty = (double)by, tz = (double)bz;
+        acc[0] = 1.0;
+        acc[1] = ax; acc[2] = ay; acc[3] = az;
+        acc[4] = tx; acc[5] = ty; acc[6] = tz;
+        acc[7] = tx * ax; acc[8] = tx * ay; acc[9] = tx * az;
+        acc[10] = ty * ax; acc[11] = ty * ay; acc[12] = ty * az;
+        acc[13] = tz * ax; acc[14] = tz * ay; acc[15] = tz * az;
     }
     // fixed-shape reductions: xor-shuffle tree inside the warp, warps in order inside the CTA -> deterministic
 #pragma unroll
