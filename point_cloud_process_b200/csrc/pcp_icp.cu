@@ -225,7 +225,7 @@ __device__ __forceinline__ float nn1_gate_fast(double best, float E) {
     return __fadd_ru(__fadd_ru(b, __fmul_ru(__fmul_ru(2.f, r), E)), __fmul_ru(E, E));
 }
 
-__global__ void __launch_bounds__(kTileAssocWarps * 32)
+__global__ void __launch_bounds__(kTileAssocWarps * 32, 4)
 icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *__restrict__ src_views,
                       const IcpState *__restrict__ states, double *__restrict__ partials, int chunks_per_pair,
                       double dist_thres) {
