@@ -100,6 +100,23 @@ int upload(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t byte
     return PCP_OK;
 }
 
+// Host -> device copy of a QUERY set (scratch destination that no queued kernel reads: every PCP_HOST search
+// call synchronises before it returns).  A page-locked source is copied on the side stream, so that the copy
+// overlaps whatever is still queued on the main stream (typically the index build of a pcp_index_rebuild that
+// returned as soon as its own upload was done); the main stream then waits for the copy.
+int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes) {
+    PCP_TRY(dst.ensure(bytes));
+    if (bytes == 0) return PCP_OK;
+    cudaPointerAttributes attr;
+    const bool pinned = cudaPointerGetAttributes(&attr, src) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (!pinned) return upload(ctx, pin_slot, dst, src, bytes);
+    PCP_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    PCP_CUDA(cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
+    PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+    return PCP_OK;
+}
+
 // device -> host, synchronous on return
 int download(pcp_ctx *ctx, void *dst, const void *src, size_t bytes) {
     if (bytes == 0) return PCP_OK;
@@ -228,6 +245,12 @@ int pcp_ctx_create(int device, pcp_ctx **out) {
         delete ctx;
         return cuda_fail(e, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
     }
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();
+        pcp_ctx_destroy(ctx);
+        return fail(PCP_ERR_CUDA, "pcp_ctx_create: cannot create the copy stream");
+    }
     *out = ctx;
     return PCP_OK;
 }
@@ -244,6 +267,8 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     for (auto &b : ctx->scratch) b.release();
     for (auto &b : ctx->pin) b.release();
     for (auto &e : ctx->timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PCP_OK;
@@ -327,8 +352,11 @@ int pcp_index_rebuild(pcp_index *ix, const float *xyz, int64_t n, int64_t stride
         PCP_TRY(upload(ctx, 0, ix->src_copy, xyz, sizeof(float) * (size_t)n * (size_t)stride));
         d_xyz = ix->src_copy.as<float>();
     }
+    if (mem == PCP_HOST && n > 0) PCP_CUDA(cudaEventRecord(ctx->ev_copy, ctx->stream));
     PCP_TRY(index_build_device(ix, d_xyz, n, stride));
-    if (mem == PCP_HOST) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    // PCP_HOST: the caller's buffer is free once the upload is done; the build itself stays queued (every later
+    // call on this context is ordered behind it on the stream)
+    if (mem == PCP_HOST && n > 0) PCP_CUDA(cudaEventSynchronize(ctx->ev_copy));
     return PCP_OK;
 }
 
@@ -389,7 +417,7 @@ int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int
     float *d_dist = dist;
     const size_t nres = (size_t)nq * (size_t)k;
     if (mem == PCP_HOST) {
-        PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        PCP_TRY(upload_side(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
         d_q = ctx->scratch[6].as<float>();
         // one result slab: idx | dist | count
         PCP_TRY(ctx->scratch[7].ensure(nres * 8 + sizeof(int32_t) * (size_t)nq));

@@ -101,6 +101,8 @@ struct pcp_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // host->device copies of query sets: overlap the work already queued on `stream`
+    cudaEvent_t ev_copy = nullptr;        // end of the last copy on copy_stream / of the last cloud upload on stream
     int64_t launches = 0;
     pcp::DevBuf cub_tmp;           // CUB temporary storage
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
