@@ -335,12 +335,13 @@ __global__ void __launch_bounds__(256) query_key_kernel(const float *__restrict_
 
 template <class KeyT>
 int radix_sort_pairs(pcp_ctx *ctx, const KeyT *k_in, KeyT *k_out, const unsigned *v_in, unsigned *v_out, long long n,
-                     int begin_bit, int end_bit) {
+                     int begin_bit, int end_bit, cudaStream_t st = nullptr, DevBuf *tmp_buf = nullptr) {
+    if (!st) st = ctx->stream;
+    DevBuf &cub_tmp = tmp_buf ? *tmp_buf : ctx->cub_tmp;
     size_t tmp_bytes = 0;
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit, ctx->stream));
-    PCP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit,
-                                             ctx->stream));
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit, st));
+    PCP_TRY(cub_tmp.ensure(tmp_bytes));
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tmp_bytes, k_in, k_out, v_in, v_out, n, begin_bit, end_bit, st));
     ctx->launches += 2 + (end_bit - begin_bit + 7) / 8;   // onesweep: histogram + scan + one pass per 8-bit digit (CUB internal)
     return PCP_OK;
 }
@@ -355,6 +356,7 @@ inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(
 }  // namespace
 
 void BatchIndex::release() {
+    if (ev_bbox) { cudaEventDestroy(ev_bbox); ev_bbox = nullptr; }
     for (DevBuf *d : {&pts, &box_lo, &box_hi, &half, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
     h_views.clear();
     P = 0;
@@ -444,6 +446,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     }
     bbox_finish_kernel<<<grid_for(P, 128), 128, 0, st>>>(b->bbox.as<float>(), P);
     ctx->launches += 1;
+    if (b->ev_bbox) PCP_CUDA(cudaEventRecord(b->ev_bbox, st));   // query keys only need the boxes, not the sorted cloud
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
         if (wide)
@@ -484,26 +487,32 @@ int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t str
     if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_index_build: more than 2^31-1 points");
     ix->n = n;
     ++ix->serial;
+    ix->built_from = d_xyz;
+    ix->built_stride = stride;
+    if (!ix->b.ev_bbox) PCP_CUDA(cudaEventCreateWithFlags(&ix->b.ev_bbox, cudaEventDisableTiming));
     ix->b.ctx = ix->ctx;
     const int64_t offs[2] = {0, n};
     return batch_build_device(&ix->b, d_xyz, stride, 1, offs);
 }
 
-int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm) {
+int sort_queries_on(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm, cudaStream_t st,
+                    DevBuf *keys, DevBuf &cub_tmp) {
     pcp_ctx *ctx = ix->ctx;
     if (nq == 0) return PCP_OK;
-    PCP_TRY(ctx->scratch[0].ensure(sizeof(unsigned) * (size_t)nq));
-    PCP_TRY(ctx->scratch[1].ensure(sizeof(unsigned) * (size_t)nq));
-    PCP_TRY(ctx->scratch[2].ensure(sizeof(unsigned) * (size_t)nq));
-    unsigned *ka = ctx->scratch[0].as<unsigned>(), *kb = ctx->scratch[1].as<unsigned>();
-    unsigned *va = ctx->scratch[2].as<unsigned>();
-    query_key_kernel<<<grid_for(nq, 256), 256, 0, ctx->stream>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
+    for (int i = 0; i < 3; ++i) PCP_TRY(keys[i].ensure(sizeof(unsigned) * (size_t)nq));
+    unsigned *ka = keys[0].as<unsigned>(), *kb = keys[1].as<unsigned>(), *va = keys[2].as<unsigned>();
+    query_key_kernel<<<grid_for(nq, 256), 256, 0, st>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
     ctx->launches += 1;
-    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30));
-    refine_queries_kernel<<<grid_for(nq, kRefine), kRefine, 0, ctx->stream>>>(d_q, nq, stride, d_perm);
+    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30, st, &cub_tmp));
+    refine_queries_kernel<<<grid_for(nq, kRefine), kRefine, 0, st>>>(d_q, nq, stride, d_perm);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
+}
+
+int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm) {
+    pcp_ctx *ctx = ix->ctx;
+    return sort_queries_on(ix, d_q, nq, stride, d_perm, ctx->stream, ctx->scratch, ctx->cub_tmp);
 }
 
 }  // namespace pcp

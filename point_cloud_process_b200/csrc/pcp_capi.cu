@@ -104,7 +104,8 @@ int upload(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t byte
 // call synchronises before it returns).  A page-locked source is copied on the side stream, so that the copy
 // overlaps whatever is still queued on the main stream (typically the index build of a pcp_index_rebuild that
 // returned as soon as its own upload was done); the main stream then waits for the copy.
-int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes) {
+int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes, bool *on_side = nullptr) {
+    if (on_side) *on_side = false;
     PCP_TRY(dst.ensure(bytes));
     if (bytes == 0) return PCP_OK;
     cudaPointerAttributes attr;
@@ -114,6 +115,7 @@ int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t
     PCP_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
     PCP_CUDA(cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
     PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+    if (on_side) *on_side = true;
     return PCP_OK;
 }
 
@@ -246,7 +248,9 @@ int pcp_ctx_create(int device, pcp_ctx **out) {
         return cuda_fail(e, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
     }
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_q_ready, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_search_end, cudaEventDisableTiming) != cudaSuccess) {
         cudaGetLastError();
         pcp_ctx_destroy(ctx);
         return fail(PCP_ERR_CUDA, "pcp_ctx_create: cannot create the copy stream");
@@ -267,7 +271,13 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     for (auto &b : ctx->scratch) b.release();
     for (auto &b : ctx->pin) b.release();
     for (auto &e : ctx->timing_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    for (auto &b : ctx->q_keys) b.release();
+    ctx->q_perm.release();
+    ctx->cub_tmp_side.release();
     if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
+    if (ctx->ev_q_ready) cudaEventDestroy(ctx->ev_q_ready);
+    if (ctx->ev_search_end) cudaEventDestroy(ctx->ev_search_end);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -416,8 +426,9 @@ int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int
     int32_t *d_idx = idx, *d_cnt = count;
     float *d_dist = dist;
     const size_t nres = (size_t)nq * (size_t)k;
+    bool side_ok = false;      // queries were uploaded on the side stream: their regrouping may run there too
     if (mem == PCP_HOST) {
-        PCP_TRY(upload_side(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        PCP_TRY(upload_side(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride, &side_ok));
         d_q = ctx->scratch[6].as<float>();
         // one result slab: idx | dist | count
         PCP_TRY(ctx->scratch[7].ensure(nres * 8 + sizeof(int32_t) * (size_t)nq));
@@ -427,7 +438,7 @@ int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int
     }
     // one warp per query: queries are independent, no reordering pass is needed
     const uint32_t *d_perm = nullptr;
-    PCP_TRY(knn_device(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_cnt));
+    PCP_TRY(knn_device(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_cnt, side_ok));
     if (mem == PCP_HOST) {
         PCP_TRY(download(ctx, idx, d_idx, nres * 4));
         PCP_TRY(download(ctx, dist, d_dist, nres * 4));

@@ -87,6 +87,7 @@ struct BatchIndex {
     int max_levels = 0;
     int64_t level_max_cnt[kMaxLevels] = {0};
     std::vector<IndexView> h_views;
+    cudaEvent_t ev_bbox = nullptr;   // optional: recorded on the build stream once the segment bounding boxes are final
     DevBuf pts, box_lo, box_hi, half, bbox, views, keys_a, keys_b, vals_a, vals_b;
     const IndexView *d_views() const { return views.as<IndexView>(); }
     void release();
@@ -103,6 +104,11 @@ struct pcp_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;   // host->device copies of query sets: overlap the work already queued on `stream`
     cudaEvent_t ev_copy = nullptr;        // end of the last copy on copy_stream / of the last cloud upload on stream
+    // Query regrouping on the side stream (Morton keys, radix sort, kd regrouping of a kNN query set), concurrent
+    // with an index build still queued on `stream`: own key buffers and CUB storage, ordered by two events
+    pcp::DevBuf q_keys[3], q_perm, cub_tmp_side;
+    cudaEvent_t ev_q_ready = nullptr;     // side stream: permutation of the current query set complete
+    cudaEvent_t ev_search_end = nullptr;  // main stream: last search that read q_perm has finished
     int64_t launches = 0;
     pcp::DevBuf cub_tmp;           // CUB temporary storage
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
@@ -127,6 +133,8 @@ struct pcp_index {
     pcp_ctx *ctx = nullptr;
     int64_t n = 0;
     uint64_t serial = 0;     // bumped by every (re)build
+    const float *built_from = nullptr;   // device pointer / shape of the cloud of the last build
+    int64_t built_stride = 0;
     pcp::BatchIndex b;       // P == 1
     pcp::DevBuf src_copy;
 };
@@ -139,10 +147,15 @@ inline const IndexView &make_view(const pcp_index *ix) { return ix->b.h_views[0]
 int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t stride);
 // Morton keys of arbitrary query points in the index's frame, sorted: writes perm (nq) to d_perm
 int sort_queries(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm);
+// the same on an arbitrary stream with caller-provided key buffers (3) and CUB storage
+int sort_queries_on(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, uint32_t *d_perm, cudaStream_t st,
+                    DevBuf *keys, DevBuf &cub_tmp);
 
 // search (pcp_knn.cu / pcp_radius.cu); all pointers are device pointers
+// side_ok: the query data is known to be complete in the side stream's order (uploaded there by the library) --
+// the regrouping may then run beside an index build that is still queued
 int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
-               int32_t *d_idx, float *d_dist, int32_t *d_count);
+               int32_t *d_idx, float *d_dist, int32_t *d_count, bool side_ok = false);
 int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count);
 // tiled kernel (pcp_knn_tile.cu): one warp per group of 32 Morton-adjacent queries
 int knn_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,

@@ -124,13 +124,28 @@ int knn_kernel_choice() {
 constexpr int64_t kTileMinQueries = 8192;
 
 int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
-               int32_t *d_idx, float *d_dist, int32_t *d_count) {
+               int32_t *d_idx, float *d_dist, int32_t *d_count, bool side_ok) {
     (void)d_perm;
     if (nq == 0) return PCP_OK;
     pcp_ctx *ctx = ix->ctx;
     const int choice = knn_kernel_choice();
     if (ix->n > 0 && (choice == 2 || (choice == 0 && nq >= kTileMinQueries))) {
         // group queries by Morton order in the index's frame, 32 per warp
+        // The regrouping needs the index's bounding box only.  When the query data is certainly complete --
+        // uploaded by the library on the side stream, or the very array the index was built from -- it runs on
+        // the side stream, beside the rest of an index build that may still be queued on the main stream.
+        if (side_ok || (d_q == ix->built_from && stride == ix->built_stride && nq == ix->n)) {
+            PCP_TRY(ctx->q_perm.ensure(sizeof(uint32_t) * (size_t)nq));
+            cudaStream_t side = ctx->copy_stream;
+            PCP_CUDA(cudaStreamWaitEvent(side, ix->b.ev_bbox, 0));          // boxes of THIS index final
+            PCP_CUDA(cudaStreamWaitEvent(side, ctx->ev_search_end, 0));     // last reader of q_perm done
+            PCP_TRY(sort_queries_on(ix, d_q, nq, stride, ctx->q_perm.as<uint32_t>(), side, ctx->q_keys, ctx->cub_tmp_side));
+            PCP_CUDA(cudaEventRecord(ctx->ev_q_ready, side));
+            PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_q_ready, 0));
+            PCP_TRY(knn_tile_device(ix, d_q, nq, stride, ctx->q_perm.as<uint32_t>(), k, d_idx, d_dist, d_count));
+            PCP_CUDA(cudaEventRecord(ctx->ev_search_end, ctx->stream));
+            return PCP_OK;
+        }
         PCP_TRY(ctx->scratch[3].ensure(sizeof(uint32_t) * (size_t)nq));
         PCP_TRY(sort_queries(ix, d_q, nq, stride, ctx->scratch[3].as<uint32_t>()));
         return knn_tile_device(ix, d_q, nq, stride, ctx->scratch[3].as<uint32_t>(), k, d_idx, d_dist, d_count);
