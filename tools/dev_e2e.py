@@ -16,6 +16,10 @@ def t(fn, reps=50):
     for _ in range(reps): fn()
     return (time.perf_counter() - t0) / reps * 1e6
 
+def both():
+    ix.rebuild(h); return ix.knn(h, k)
+for _ in range(3):
+    print("rebuild + knn (host pinned) %.1f us" % t(both))
 print("rebuild(host pinned)      %.1f us" % t(lambda: ix.rebuild(h)))
 print("knn(host pinned)          %.1f us" % t(lambda: ix.knn(h, k)))
 print("knn_self (D2H only)       %.1f us" % t(lambda: ix.knn_self(k)))
