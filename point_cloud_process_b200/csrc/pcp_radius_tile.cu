@@ -139,8 +139,8 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
             __syncwarp();     // the boxes of this node are dead: the next open may overwrite them
         }
         if (!FILL && active) counts[qid] = cursor;
+        const unsigned n_active = __popc(__ballot_sync(kFullMask, active));   // (all lanes: a full-mask vote)
         if (ctr && lane == 0) {
-            const unsigned n_active = __popc(__ballot_sync(kFullMask, active));
             atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
             atomicAdd(ctr + 1, (unsigned long long)n_open * kFan);
             atomicAdd(ctr + 2, (unsigned long long)n_open);

@@ -258,3 +258,30 @@ def test_radius_tiled_fill_matches(kitti):
             outs.append(dict(np.load(path)))
     for key in ("off", "idx", "dist"):
         assert np.array_equal(outs[0][key], outs[1][key]), key
+
+
+@pytest.mark.timeout(120)
+def test_work_counters_all_search_kernels(pcp, kitti):
+    """pcp_ctx_enable_counters on every search kernel (tiled and warp-per-query, kNN and radius): the counted
+    runs must finish (a divergent full-mask vote in a counter branch once hung the tiled radius kernel) and
+    give the same results as the uncounted ones."""
+    ctx = pcp.native.Context(0)
+    ix = pcp.native.Index(ctx, kitti)
+    q = kitti[::4].copy()                                   # 31 167 queries: tiled kernels
+    ref_knn = ix.knn(q, 8)
+    ref_rad = ix.radius(q, 0.5, True)
+    small = kitti[:100].copy()                              # warp-per-query kernels
+    ref_small = ix.knn(small, 8), ix.radius(small, 0.5, True)
+    ctx.enable_counters(True)
+    got_knn, got_rad = ix.knn(q, 8), ix.radius(q, 0.5, True)
+    c_big = ctx.read_counters()
+    got_small = ix.knn(small, 8), ix.radius(small, 0.5, True)
+    c_small = ctx.read_counters()
+    ix.knn_self(8)
+    c_self = ctx.read_counters()
+    ctx.enable_counters(False)
+    for a, b in zip(ref_knn + ref_rad, got_knn + got_rad):
+        assert np.array_equal(a, b)
+    for a, b in zip(ref_small[0] + ref_small[1], got_small[0] + got_small[1]):
+        assert np.array_equal(a, b)
+    assert c_big[0] > 0 and c_small[0] > 0 and c_self[0] > 0
