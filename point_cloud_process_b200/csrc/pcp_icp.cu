@@ -215,7 +215,7 @@ icp_assoc_kernel(const IndexView *__restrict__ views, const float *__restrict__ 
 // Same structure as knn_tile_kernel (pcp_knn_tile.cu) with K = 1: the group walks the pair's TARGET hierarchy once,
 // buckets are staged in shared memory and every lane evaluates its own (transformed) point against the 32 staged
 // points in float32; survivors of the proven-margin filter are re-evaluated in float64 (nn1 semantics above).
-constexpr int kTileAssocWarps = 8;
+constexpr int kTileAssocWarps = 2;
 
 __device__ __forceinline__ float nn1_gate_fast(double best, float E) {
     // upper bound of best (1 + 2^-20) + 2 sqrt(best) E + E^2 in float, every step rounded up
@@ -225,7 +225,7 @@ __device__ __forceinline__ float nn1_gate_fast(double best, float E) {
     return __fadd_ru(__fadd_ru(b, __fmul_ru(__fmul_ru(2.f, r), E)), __fmul_ru(E, E));
 }
 
-__global__ void __launch_bounds__(kTileAssocWarps * 32, 4)
+__global__ void __launch_bounds__(kTileAssocWarps * 32, 32 / kTileAssocWarps)
 icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *__restrict__ src_views,
                       const IcpState *__restrict__ states, double *__restrict__ partials, int chunks_per_pair,
                       double dist_thres) {
