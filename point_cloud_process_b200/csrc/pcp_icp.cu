@@ -230,7 +230,7 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                       const IcpState *__restrict__ states, double *__restrict__ partials, int chunks_per_pair,
                       double dist_thres) {
     __shared__ float4 s_tile[kTileAssocWarps][32];
-    __shared__ float4 s_box[kTileAssocWarps][64];
+    __shared__ float4 s_box[kTileAssocWarps][128];   // half-bucket boxes of the open level-1 node
     __shared__ unsigned s_lb[kTileAssocWarps][kMaxLevels][32];
     __shared__ unsigned s_cd[kTileAssocWarps][kMaxLevels][32];
     __shared__ unsigned s_node[kTileAssocWarps][kMaxLevels];
@@ -271,11 +271,14 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
 
         float4 *tile = s_tile[warp];
         float4 *boxes = s_box[warp];
-        auto bucket_needed = [&](int c) -> bool {
-            return __ballot_sync(kFullMask, box_lb2(qx, qy, qz, boxes[2 * c], boxes[2 * c + 1]) <= gate) != 0;
+        // bit h: some lane can still use the 16-point half h of bucket c (exact per-lane bounds)
+        auto bucket_needed = [&](int c) -> unsigned {
+            const bool a = box_lb2(qx, qy, qz, boxes[4 * c], boxes[4 * c + 1]) <= gate;
+            const bool b = box_lb2(qx, qy, qz, boxes[4 * c + 2], boxes[4 * c + 3]) <= gate;
+            return (__any_sync(kFullMask, a) ? 1u : 0u) | (__any_sync(kFullMask, b) ? 2u : 0u);
         };
         float m32 = __int_as_float(0x7f800000);                // smallest float32 d^2 this lane has seen
-        auto scan_bucket = [&](const float4 pv) {
+        auto scan_bucket = [&](const float4 pv, unsigned halves) {
             __syncwarp();
             tile[lane] = pv;
             __syncwarp();
@@ -287,6 +290,7 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
             // per bucket instead of every point inside the initial dist_thres ball).
 #pragma unroll
             for (int j0 = 0; j0 < 32; j0 += 8) {
+                if (!((halves >> (j0 >> 4)) & 1u)) continue;
                 float d2[8];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
@@ -333,11 +337,21 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                 unsigned bits = kDone, cbits = kDone;
                 if (c < ix.level_cnt[lv - 1]) {
                     const long long b = ix.level_off[lv - 1] + c;
-                    const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
-                    bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+                    float4 lo, hi;
+                    if (lv == 1) {
+                        // buckets: the boxes of the two 16-point halves; the bucket's bound is the smaller of theirs
+                        const float4 *h = ix.half + c * 4;
+                        const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
+                        boxes[4 * lane] = alo; boxes[4 * lane + 1] = ahi; boxes[4 * lane + 2] = blo; boxes[4 * lane + 3] = bhi;
+                        bits = min(__float_as_uint(boxbox_lb2(glo, ghi, alo, ahi)), __float_as_uint(boxbox_lb2(glo, ghi, blo, bhi)));
+                        lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+                        hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+                    } else {
+                        lo = __ldg(ix.box_lo + b); hi = __ldg(ix.box_hi + b);
+                        bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+                    }
                     const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
                     cbits = __float_as_uint(cx * cx + cy * cy + cz * cz);
-                    if (lv == 1) { boxes[2 * lane] = lo; boxes[2 * lane + 1] = hi; }
                 }
                 lbs[lv][lane] = bits;
                 cds[lv][lane] = cbits;
@@ -374,17 +388,20 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                     continue;
                 }
                 const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
-                while (sel >= 0 && !bucket_needed(sel)) sel = pick(1);
+                unsigned halves = 0;
+                while (sel >= 0 && !(halves = bucket_needed(sel))) sel = pick(1);
                 if (sel < 0) continue;
                 float4 cur = __ldg(base + sel * kLeaf);
                 while (true) {
                     int nxt = pick(1);
-                    while (nxt >= 0 && !bucket_needed(nxt)) nxt = pick(1);
+                    unsigned nxt_halves = 0;
+                    while (nxt >= 0 && !(nxt_halves = bucket_needed(nxt))) nxt = pick(1);
                     float4 pf = cur;
                     if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
-                    scan_bucket(cur);
+                    scan_bucket(cur, halves);
                     if (nxt < 0) break;
                     sel = nxt;
+                    halves = nxt_halves;
                     cur = pf;
                 }
             }
