@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
 knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, int k,
                 int *__restrict__ out_idx, float *__restrict__ out_dist, int *__restrict__ out_cnt,
                 unsigned long long *__restrict__ ctr, const unsigned *__restrict__ list,
-                const unsigned *__restrict__ perm) {
+                const unsigned *__restrict__ perm, const float *__restrict__ hints, unsigned hint_groups) {
     // per-level traversal state: lane j keeps the pending lower bound of child j of the open node
     __shared__ unsigned s_lb[kWarpsPerCta][kMaxLevels][32];
     __shared__ unsigned s_cd[kWarpsPerCta][kMaxLevels][32];   // squared distance to the child's box centre
@@ -59,7 +59,10 @@ knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long
         const float *q = queries + qid * stride;
         st.qx = __ldg(q); st.qy = __ldg(q + 1); st.qz = __ldg(q + 2);
     }
-    warpq::search(ix, st, lane, k, s_lb[warp], s_cd[warp], s_node[warp]);
+    // LIST: the gate the tiled kernel had reached for this query when it gave the group up (first hint_groups entries)
+    float gate0 = __int_as_float(0x7f800000);
+    if (LIST && (item >> 5) < (long long)hint_groups) gate0 = hints[item];
+    warpq::search(ix, st, lane, k, s_lb[warp], s_cd[warp], s_node[warp], gate0);
 
     if (ctr && lane == 0) {
         atomicAdd(ctr + 0, (unsigned long long)st.n_scan * kLeaf);
@@ -96,16 +99,19 @@ __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, in
 
 // Overflow groups of the tiled kernel, one warp per query, persistent grid.
 int knn_warp_list_device(pcp_index *ix, bool self, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
-                         const uint32_t *d_list, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
+                         const uint32_t *d_list, const float *d_hints, uint32_t hint_groups, int k, int32_t *d_idx,
+                         float *d_dist, int32_t *d_count) {
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
     const unsigned grid = (unsigned)ctx->sm_count * 8;
     if (self)
         knn_warp_kernel<true, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
-                                                                                d_count, ctx->ctr(), d_list, nullptr);
+                                                                                d_count, ctx->ctr(), d_list, nullptr, d_hints,
+                                                                                hint_groups);
     else
         knn_warp_kernel<false, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
-                                                                                 d_count, ctx->ctr(), d_list, d_perm);
+                                                                                 d_count, ctx->ctr(), d_list, d_perm, d_hints,
+                                                                                 hint_groups);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
@@ -160,7 +166,7 @@ int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, cons
     const IndexView v = make_view(ix);
     const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
     knn_warp_kernel<false, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
-                                                                               d_count, ctx->ctr(), nullptr, nullptr);
+                                                                               d_count, ctx->ctr(), nullptr, nullptr, nullptr, 0u);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
@@ -175,7 +181,7 @@ int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t
     const long long n_work = v.n_leaf * kLeaf;
     const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
     knn_warp_kernel<true, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
-                                                                              d_count, ctx->ctr(), nullptr, nullptr);
+                                                                              d_count, ctx->ctr(), nullptr, nullptr, nullptr, 0u);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;

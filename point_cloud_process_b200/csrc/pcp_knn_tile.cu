@@ -40,13 +40,39 @@ constexpr unsigned kInfBits = 0x7f800000u;
 // larger than its queries' neighbourhoods) are 8x the mean.  Larger inputs run unbounded.
 constexpr unsigned kScansPerSlot = 4;
 constexpr unsigned kTestsPerSlot = 12;
+// Tail hand-over: with the queue dry and fewer groups in flight than this share of the warp slots, the groups
+// still running are handed over too (see the kernel).
+constexpr double kTailShare = 0.05;
+constexpr long long kHintGroups = 1 << 16;     // overflow groups whose gates are passed on (8 MB of scratch)
 
-// Candidate-buffer geometry per result capacity K: CAP entries per lane (a chunk of 8 evaluations appends at
-// most 8, a compaction leaves k + ties), WARPS groups per CTA.  Shared memory per CTA = WARPS * CAP * 256 B.
-constexpr int kChunk = 8;
-template <int K> struct TileCfg { static constexpr int kCap = 29, kWarps = 4; };
-template <> struct TileCfg<16> { static constexpr int kCap = 40, kWarps = 4; };
-template <> struct TileCfg<32> { static constexpr int kCap = 72, kWarps = 2; };
+// Candidate-buffer geometry per result capacity K: CAP entries per lane (a half-chunk of 4 evaluations appends
+// at most 4, a compaction leaves k + ties), WARPS groups per CTA.  The per-warp shared-memory state is
+//   CAP * 256 B candidate columns + 512 B staged bucket + 1536 B half-bucket boxes + 128 B per tree level + 32 B,
+// sized so that K <= 8 runs 28 warps per SM (7 CTAs; 72 registers) and K = 16 runs 20 (5 CTAs; 96 registers):
+// the kernel is latency-bound, and at 28 warps/SM the 3 896 groups of a KITTI scan are all resident at once.
+constexpr int kChunk = 8;                      // points loaded per step; the overflow check runs every kChunk / 2
+template <int K> struct TileCfg { static constexpr int kCap = 21, kWarps = 4, kCtas = 7; };
+template <> struct TileCfg<16> { static constexpr int kCap = 34, kWarps = 4, kCtas = 5; };
+template <> struct TileCfg<32> { static constexpr int kCap = 68, kWarps = 2, kCtas = 8; };
+constexpr int kBoxFloats = 64 * 6;             // 64 half boxes x (lo.xyz, hi.xyz)
+__host__ __device__ constexpr size_t tile_warp_bytes(int cap, int levels) {
+    return (size_t)cap * 256 + 512 + kBoxFloats * 4 + (size_t)levels * 128 + 32;
+}
+// lower bound against a box stored as 6 floats (same arithmetic as box_lb2)
+__device__ __forceinline__ float box6_lb2(float qx, float qy, float qz, const float *b) {
+    const float2 l01 = *reinterpret_cast<const float2 *>(b), l2h0 = *reinterpret_cast<const float2 *>(b + 2),
+                 h12 = *reinterpret_cast<const float2 *>(b + 4);
+    float dx = fmaxf(fmaxf(__fsub_rn(l01.x, qx), __fsub_rn(qx, l2h0.y)), 0.f);
+    float dy = fmaxf(fmaxf(__fsub_rn(l01.y, qy), __fsub_rn(qy, h12.x)), 0.f);
+    float dz = fmaxf(fmaxf(__fsub_rn(l2h0.x, qz), __fsub_rn(qz, h12.y)), 0.f);
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+// free-running device timer in 32 ns units (wraps after 137 s; compared with wrap-safe differences)
+__device__ __forceinline__ unsigned timer32() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return (unsigned)(t >> 5);
+}
 // Children whose box overlaps the group box (lower bound 0) are visited in the order of their centre distance:
 // the slot then holds the distance's float bits >> 9, i.e. a value below kMinNormalBits that never prunes.
 constexpr unsigned kMinNormalBits = 0x00800000u;
@@ -72,41 +98,56 @@ struct TopK {
 };
 
 template <int K, bool SELF>
-__global__ void __launch_bounds__(TileCfg<K>::kWarps * 32)
+__global__ void __launch_bounds__(TileCfg<K>::kWarps * 32, TileCfg<K>::kCtas)
 knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm, long long nq,
                 long long stride, int k, int *__restrict__ out_idx, float *__restrict__ out_dist,
                 int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg,
-                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests, int trigger) {
+                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests, int trigger,
+                unsigned tail_slots, unsigned *__restrict__ sched, unsigned n_groups, float *__restrict__ hints,
+                unsigned hint_groups) {
     constexpr int kTileWarps = TileCfg<K>::kWarps;
     constexpr int kCap = TileCfg<K>::kCap;
-    extern __shared__ uint2 s_cand[];                       // [kTileWarps][kCap][32]: (d2 bits, index) per lane column
-    __shared__ float4 s_tile[kTileWarps][32];
-    __shared__ float4 s_box[kTileWarps][128];
-    __shared__ unsigned s_lb[kTileWarps][kMaxLevels][32];
-    __shared__ unsigned s_node[kTileWarps][kMaxLevels];
+    // dynamic shared memory: [kTileWarps][kCap][32] candidate columns (d2 bits, index) first -- the filter's
+    // read-ahead past the last column lands in the arrays behind them --, then per warp: staged bucket,
+    // half-bucket boxes, one row of child bounds per tree level, open node per level
+    extern __shared__ uint2 s_cand[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long n_groups = SELF ? ix.n_leaf : (nq + 31) / 32;
-    unsigned *sched = overflow + n_groups + 1;                  // next group to hand out (zeroed by the host)
+    const int n_lv = ix.n_levels > 1 ? ix.n_levels - 1 : 1;
+    unsigned char *s_rest = reinterpret_cast<unsigned char *>(s_cand + kTileWarps * kCap * 32) +
+                            (size_t)warp * (tile_warp_bytes(0, n_lv));
+    // sched (behind the overflow list): [0] next group to hand out, [1] groups finished (zeroed by the host);
+    // it and n_groups are kernel parameters so that the tail poll below holds no registers across the hot loops
     // Persistent warps: groups are handed out dynamically, so the kernel ends within one group's work of the
     // moment the queue runs dry instead of waiting for the unluckiest statically assigned warp.
+    // Tail hand-over (tail_slots != 0): once the queue is dry the kernel lasts as long as its slowest group
+    // while most warp slots idle (a group whose 32 queries straddle a jump of the Morton curve tests thousands of
+    // boxes and runs 10x the mean).  sched[1] counts finished groups; when fewer than tail_slots groups are still
+    // in flight the stragglers hand their queries to the warp-per-query kernel (32 warps per group instead of 1).
     for (;;) {
-    long long group;
+    unsigned group;
     {
         unsigned g = 0;
         if (lane == 0) g = atomicAdd(sched, 1u);
         group = __shfl_sync(kFullMask, g, 0);
     }
     if (group >= n_groups) break;
+    if (dbg && lane == 0) {                                     // developer timeline (PCP_DUMP_GROUPS)
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        dbg[(size_t)group * 8 + 4] = timer32();
+        dbg[(size_t)group * 8 + 6] = smid;
+        dbg[(size_t)group * 8 + 7] = 0u;
+    }
 
     // ---- this lane's query
     float qx = 0.f, qy = 0.f, qz = 0.f;
     long long qid = -1;
     if (SELF) {
-        const float4 p = __ldg(ix.pts + group * kLeaf + lane);
+        const float4 p = __ldg(ix.pts + (long long)group * kLeaf + lane);
         qx = p.x; qy = p.y; qz = p.z;
         qid = (long long)(int)__float_as_uint(p.w);            // -1 on pad lanes
     } else {
-        const long long pos = group * 32 + lane;
+        const long long pos = (long long)group * 32 + lane;
         if (pos < nq) {
             qid = perm ? (long long)perm[pos] : pos;
             const float *q = queries + qid * stride;
@@ -127,8 +168,8 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     bool aborted = false;
     const unsigned n_active = __popc(__ballot_sync(kFullMask, active));
 
-    float4 *tile = s_tile[warp];
-    float4 *boxes = s_box[warp];            // half-bucket boxes below the open level-1 node: [4*c + 2*h] = lo, [4*c + 2*h + 1] = hi
+    float4 *tile = reinterpret_cast<float4 *>(s_rest);
+    float *boxes = reinterpret_cast<float *>(s_rest + 512);   // half boxes below the open level-1 node: 6 floats at [(2*c + h) * 6]
     uint2 *col = s_cand + warp * (kCap * 32) + lane;            // this lane's column: entry e at col[e * 32]
     const unsigned col_addr = (unsigned)__cvta_generic_to_shared(col);
     unsigned waddr = col_addr;                                  // append position (shared-memory byte address; 256 B per entry)
@@ -186,12 +227,21 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
     };
 
+    // Tail hand-over poll (every 4th scan / open): queue dry and fewer than tail_slots groups still in flight?
+    auto poll_tail = [&]() {
+        if (!tail_slots) return;
+        uint2 w = make_uint2(0u, 0u);
+        if (lane == 0) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(w.x), "=r"(w.y) : "l"(sched));
+        // (sched[0] runs past n_groups by at most one per warp; sched[1] <= n_groups)
+        if (__shfl_sync(kFullMask, (w.x >= n_groups && n_groups - w.y < tail_slots) ? 1 : 0, 0)) aborted = true;
+    };
+
     // Exact per-lane lower bounds against the boxes of bucket c's two 16-point halves (shared-memory broadcast):
     // bit h is set when ANY lane can still use half h.
     auto bucket_needed = [&](int c) -> unsigned {
         ++n_test;
-        const bool a = box_lb2(qx, qy, qz, boxes[4 * c], boxes[4 * c + 1]) <= gate;
-        const bool b = box_lb2(qx, qy, qz, boxes[4 * c + 2], boxes[4 * c + 3]) <= gate;
+        const bool a = box6_lb2(qx, qy, qz, boxes + c * 12) <= gate;
+        const bool b = box6_lb2(qx, qy, qz, boxes + c * 12 + 6) <= gate;
         return (__any_sync(kFullMask, a) ? 1u : 0u) | (__any_sync(kFullMask, b) ? 2u : 0u);
     };
     // Scan the needed halves of one bucket whose points `pv` (lane j = point j) are already in registers.
@@ -201,7 +251,8 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         __syncwarp();
         tile[lane] = pv;
         __syncwarp();
-        // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores
+        // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores; the
+        // columns are checked after every 4 evaluations, so only 4 entries of headroom are reserved
 #pragma unroll 1
         for (int j0 = 0; j0 < 32; j0 += kChunk) {
             if (!((halves >> (j0 >> 4)) & 1u)) continue;
@@ -209,28 +260,33 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
 #pragma unroll
             for (int j = 0; j < kChunk; ++j) p[j] = tile[j0 + j];
 #pragma unroll
-            for (int j = 0; j < kChunk; ++j) {
-                const float d2 = ref_d2(qx, qy, qz, p[j].x, p[j].y, p[j].z);
-                if (d2 <= gate) {                                // NaN pads never pass
-                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(d2), "f"(p[j].w) : "memory");
-                    waddr += 256;
+            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                for (int j = h * (kChunk / 2); j < (h + 1) * (kChunk / 2); ++j) {
+                    const float d2 = ref_d2(qx, qy, qz, p[j].x, p[j].y, p[j].z);
+                    if (d2 <= gate) {                            // NaN pads never pass
+                        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(d2), "f"(p[j].w) : "memory");
+                        waddr += 256;
+                    }
+                }
+                // a column that could overflow during the next 4 evaluations: compact all columns of the warp
+                if (__any_sync(kFullMask, waddr > col_addr + (unsigned)trigger * 256)) {
+                    compact();
+                    // still too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
+                    if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kChunk / 2) * 256)) aborted = true;
                 }
             }
-            // a column that could overflow during the next chunk: compact all columns of the warp
-            if (__any_sync(kFullMask, waddr > col_addr + (unsigned)trigger * 256)) {
-                compact();
-                // still too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
-                if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kChunk) * 256)) { aborted = true; break; }
-            }
+            if (aborted) break;
         }
     };
 
     const int top_level = ix.n_levels - 1;      // >= 1 for every non-empty index (pcp_build.cu)
     if (top_level > 0) {
-        unsigned(*lbs)[32] = s_lb[warp];
-        unsigned *nodes = s_node[warp];
+        unsigned(*lbs)[32] = reinterpret_cast<unsigned(*)[32]>(s_rest + 512 + kBoxFloats * 4) - 1;   // row lv - 1
+        unsigned *nodes = reinterpret_cast<unsigned *>(s_rest + 512 + kBoxFloats * 4 + (size_t)n_lv * 128) - 1;
         auto open_node = [&](int lv, unsigned node) {
             ++n_open;
+            if (lv == 1 && (n_open & 3u) == 0u) poll_tail();
             if (lane == 0) nodes[lv] = node;
             const long long c = (long long)node * kFan + lane;
             unsigned bits = kDone;
@@ -240,7 +296,9 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                     // buckets: the boxes of the two halves; the bucket's bound is the smaller of theirs
                     const float4 *h = ix.half + c * 4;
                     const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
-                    boxes[4 * lane] = alo; boxes[4 * lane + 1] = ahi; boxes[4 * lane + 2] = blo; boxes[4 * lane + 3] = bhi;
+                    float2 *bw = reinterpret_cast<float2 *>(boxes + lane * 12);
+                    bw[0] = make_float2(alo.x, alo.y); bw[1] = make_float2(alo.z, ahi.x); bw[2] = make_float2(ahi.y, ahi.z);
+                    bw[3] = make_float2(blo.x, blo.y); bw[4] = make_float2(blo.z, bhi.x); bw[5] = make_float2(bhi.y, bhi.z);
                     bits = min(__float_as_uint(boxbox_lb2(glo, ghi, alo, ahi)), __float_as_uint(boxbox_lb2(glo, ghi, blo, bhi)));
                     lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
                     hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
@@ -271,7 +329,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         };
         int level = top_level;
         open_node(top_level, 0u);
-        while (true) {
+        while (!aborted) {
             int sel = pick(level);
             if (sel < 0) {
                 if (level == top_level) break;
@@ -299,6 +357,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                 float4 pf = cur;
                 if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
                 scan_bucket(cur, halves);
+                if ((n_scan & 3u) == 0u) poll_tail();
                 if (nxt < 0) break;
                 sel = nxt;
                 halves = nxt_halves;
@@ -311,10 +370,19 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     if (aborted) {
         // work budget exceeded (a sparse group whose box is much larger than its neighbourhoods) or a mass of
         // tied distances: hand the group's queries to the warp-per-query kernel, which re-does them in parallel
-        if (lane == 0) overflow[1 + atomicAdd(overflow, 1u)] = (unsigned)group;
+        unsigned pos = 0;
+        if (lane == 0) {
+            pos = atomicAdd(overflow, 1u);
+            overflow[1 + pos] = group;
+            atomicAdd(sched + 1, 1u);
+        }
+        // the gates reached so far seed the searches of the warp-per-query kernel
+        pos = __shfl_sync(kFullMask, pos, 0);
+        if (pos < hint_groups) hints[(size_t)pos * 32 + lane] = gate;
         if (ctr && lane == 0) {
             atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
             atomicAdd(ctr + 6, 1ull);
+            if (dbg) { dbg[(size_t)group * 8 + 0] = n_scan; dbg[(size_t)group * 8 + 1] = n_test; dbg[(size_t)group * 8 + 5] = timer32(); dbg[(size_t)group * 8 + 7] = 1u; }
         }
         __syncwarp();
         continue;
@@ -335,6 +403,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         }
     }
 
+    if (lane == 0) atomicAdd(sched + 1, 1u);
     if (ctr && lane == 0) {
         atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
         atomicAdd(ctr + 1, (unsigned long long)n_open * kFan + n_test);
@@ -342,7 +411,10 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         atomicAdd(ctr + 3, (unsigned long long)n_round);
         atomicAdd(ctr + 4, 1ull);
         atomicAdd(ctr + 5, (unsigned long long)n_scan);
-        if (dbg) { dbg[group * 4 + 0] = n_scan; dbg[group * 4 + 1] = n_test; dbg[group * 4 + 2] = n_round; dbg[group * 4 + 3] = n_open; }
+        if (dbg) {
+            dbg[(size_t)group * 8 + 0] = n_scan; dbg[(size_t)group * 8 + 1] = n_test; dbg[(size_t)group * 8 + 2] = n_round; dbg[(size_t)group * 8 + 3] = n_open;
+            dbg[(size_t)group * 8 + 5] = timer32();
+        }
     }
     if (active) {
         int cnt = 0;
@@ -371,40 +443,55 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     const long long n_groups = SELF ? v.n_leaf : (nq + 31) / 32;
     unsigned long long *ctr = ctx->ctr();
     // overflow list: [0] = count, [1..] = group ids
-    // [n_groups + 1] = next group of the persistent tile warps
-    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 2)));
+    // behind the list, 8-byte aligned: next group of the persistent tile warps, number of finished groups
+    // and the gates of the first kHintGroups overflow groups (32 floats each)
+    const long long sched_at = (n_groups + 2) & ~1LL, hints_at = (sched_at + 2 + 31) & ~31LL;
+    const unsigned hint_groups = (unsigned)std::min<long long>(n_groups, kHintGroups);
+    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(hints_at + 32LL * hint_groups)));
     unsigned *overflow = ctx->scratch[5].as<unsigned>();
+    float *hints = reinterpret_cast<float *>(overflow + hints_at);
     PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned), ctx->stream));
-    PCP_CUDA(cudaMemsetAsync(overflow + n_groups + 1, 0, sizeof(unsigned), ctx->stream));
+    PCP_CUDA(cudaMemsetAsync(overflow + sched_at, 0, 2 * sizeof(unsigned), ctx->stream));
     const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
     const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
     static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS"),
-                      *e_trig = getenv("PCP_TILE_TRIGGER");   // developer overrides
+                      *e_trig = getenv("PCP_TILE_TRIGGER"), *e_tail = getenv("PCP_TILE_TAIL");   // developer overrides
+    const double tail_share = e_tail ? atof(e_tail) : kTailShare;   // share of the warp slots; 0 = off
     const unsigned max_scans = e_scans ? (unsigned)atoi(e_scans) : small_grid ? kScansPerSlot * std::max(K, 4) : 0xffffffffu;
     const unsigned max_tests = e_tests ? (unsigned)atoi(e_tests) : small_grid ? kTestsPerSlot * std::max(K, 4) : 0xffffffffu;
     unsigned *dbg = nullptr;
     const char *dump = ctr ? getenv("PCP_DUMP_GROUPS") : nullptr;     // developer aid: per-group work counters
     if (dump) {
-        PCP_TRY(ctx->scratch[4].ensure(sizeof(unsigned) * 4 * (size_t)n_groups));
+        PCP_TRY(ctx->scratch[4].ensure(sizeof(unsigned) * 8 * (size_t)n_groups));
         dbg = ctx->scratch[4].as<unsigned>();
     }
 #define PCP_TILE(KK)                                                                                                   \
     do {                                                                                                               \
         constexpr int W = TileCfg<KK>::kWarps, CAP = TileCfg<KK>::kCap;                                                \
-        const size_t smem = (size_t)W * CAP * 32 * sizeof(uint2) + 3 * 32 * sizeof(uint2); /* + filter read-ahead */   \
-        static int ctas_per_sm = 0;                                                                                    \
+        const int n_lv = v.n_levels > 1 ? v.n_levels - 1 : 1;                                                          \
+        const size_t smem = (size_t)W * tile_warp_bytes(CAP, n_lv);                                                   \
+        static int occ_by_levels[kMaxLevels + 1] = {0};   /* resident CTAs per SM, per tree depth */                   \
+        int &ctas_per_sm = occ_by_levels[n_lv];                                                                        \
         if (!ctas_per_sm) {                                                                                            \
-            PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            static size_t attr_smem = 0;                                                                               \
+            if (smem > attr_smem) {                                                                                    \
+                PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+                attr_smem = smem;                                                                                      \
+            }                                                                                                          \
             PCP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, knn_tile_kernel<KK, SELF>, W * 32, smem)); \
             ctas_per_sm = std::max(ctas_per_sm, 1);                                                                    \
+            if (getenv("PCP_VERBOSE")) fprintf(stderr, "knn_tile_kernel<%d>: %zu B smem, %d CTAs/SM\n", KK, smem, ctas_per_sm); \
         }                                                                                                              \
         /* compaction trigger: a column longer than this could overflow during the next chunk of evaluations */       \
-        const int trig = e_trig ? std::min(atoi(e_trig), CAP - kChunk) : CAP - kChunk;                                 \
+        const int trig = e_trig ? std::min(atoi(e_trig), CAP - kChunk / 2) : CAP - kChunk / 2;                         \
         /* persistent grid: every resident warp slot, or fewer when there are not that many groups */                  \
         const unsigned grid = (unsigned)std::min<long long>((n_groups + W - 1) / W, (long long)ctx->sm_count * ctas_per_sm); \
+        const unsigned tail_slots = (unsigned)(tail_share * (double)grid * W);                                        \
         knn_tile_kernel<KK, SELF><<<grid, W * 32, smem, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist,   \
                                                                        d_count, ctr, dbg, overflow, max_scans,         \
-                                                                       max_tests, trig);                               \
+                                                                       max_tests, trig, tail_slots,                    \
+                                                                       overflow + sched_at, (unsigned)n_groups, hints, \
+                                                                       hint_groups);                                   \
     } while (0)
     cudaEvent_t ev_end = nullptr;
     if (ctx->time_kernels) {
@@ -429,13 +516,13 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     if (dump) {
-        std::vector<unsigned> h(4 * (size_t)n_groups);
+        std::vector<unsigned> h(8 * (size_t)n_groups);
         PCP_CUDA(cudaMemcpyAsync(h.data(), dbg, sizeof(unsigned) * h.size(), cudaMemcpyDeviceToHost, ctx->stream));
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
         if (FILE *f = fopen(dump, "wb")) { fwrite(h.data(), sizeof(unsigned), h.size(), f); fclose(f); }
     }
     // groups that ran out of budget: one warp per query, persistent grid sized by the device-side count
-    return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, k, d_idx, d_dist, d_count);
+    return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, hints, hint_groups, k, d_idx, d_dist, d_count);
 }
 
 }  // namespace

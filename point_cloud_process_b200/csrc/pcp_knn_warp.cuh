@@ -89,14 +89,16 @@ __device__ __forceinline__ void scan_bucket(QueryState &st, const IndexView &ix,
             }
         }
     }
-    st.gate = d2_gate(key_dist(shfl64(st.key, k - 1)));
+    st.gate = fminf(st.gate, d2_gate(key_dist(shfl64(st.key, k - 1))));   // (a seeded gate stays until beaten)
 }
 
 // Search: `st` holds the query (qx, qy, qz) on entry and the sorted result list (st.key, lane i = i-th best) on
 // return.  lbs / cds: [kMaxLevels][32] words of per-warp shared memory, nodes: [kMaxLevels].
+// gate0: a squared-distance gate already known to hold the k nearest neighbours and everything tied with the
+// k-th (+inf when nothing is known): boxes and points beyond it are never looked at.
 __device__ __forceinline__ void search(const IndexView &ix, QueryState &st, int lane, int k, unsigned (*lbs)[32],
-                                       unsigned (*cds)[32], unsigned *nodes) {
-    st.gate = __int_as_float(0x7f800000);
+                                       unsigned (*cds)[32], unsigned *nodes, float gate0) {
+    st.gate = gate0;
     st.key = kEmptyKey;
     st.first = true;
     st.n_test = st.n_scan = st.n_ins = st.n_open = 0;
