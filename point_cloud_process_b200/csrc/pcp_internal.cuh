@@ -171,6 +171,9 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
 int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
                        const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted);
 // tiled kernel (pcp_radius_tile.cu): COUNT when d_counts != nullptr, else FILL
+int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
+                            const uint32_t *d_list, float d2max, long long *d_counts, const long long *d_offsets,
+                            int32_t *d_idx, float *d_dist);
 int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
                        long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist);
 

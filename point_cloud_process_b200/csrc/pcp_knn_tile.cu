@@ -253,9 +253,9 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         __syncwarp();
         // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores; the
         // columns are checked after every 4 evaluations, so only 4 entries of headroom are reserved
+        const int j_end = (halves & 2u) ? 32 : 16;             // (halves != 0: at least one of the two is scanned)
 #pragma unroll 1
-        for (int j0 = 0; j0 < 32; j0 += kChunk) {
-            if (!((halves >> (j0 >> 4)) & 1u)) continue;
+        for (int j0 = (halves & 1u) ? 0 : 16; j0 < j_end; j0 += kChunk) {
             float4 p[kChunk];
 #pragma unroll
             for (int j = 0; j < kChunk; ++j) p[j] = tile[j0 + j];
@@ -480,6 +480,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
             }                                                                                                          \
             PCP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, knn_tile_kernel<KK, SELF>, W * 32, smem)); \
             ctas_per_sm = std::max(ctas_per_sm, 1);                                                                    \
+            if (const char *e = getenv("PCP_TILE_CTAS")) ctas_per_sm = std::max(1, std::min(ctas_per_sm, atoi(e)));     \
             if (getenv("PCP_VERBOSE")) fprintf(stderr, "knn_tile_kernel<%d>: %zu B smem, %d CTAs/SM\n", KK, smem, ctas_per_sm); \
         }                                                                                                              \
         /* compaction trigger: a column longer than this could overflow during the next chunk of evaluations */       \

@@ -43,15 +43,26 @@ float exact_d2_threshold(float r) {
     return x;
 }
 
-template <bool FILL>
+// LIST = false: warp w of the grid takes query w.
+// LIST = true:  persistent warps drain the hand-over list of the tiled kernel (pcp_radius_tile.cu): list[0] =
+//               number of groups, list[1..] = group ids; item w -> regrouped position list[1 + w / 32] * 32 + w % 32.
+template <bool FILL, bool LIST>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 radius_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, float d2max,
               long long *__restrict__ counts, const long long *__restrict__ offsets, int *__restrict__ out_idx,
-              float *__restrict__ out_dist, unsigned long long *__restrict__ ctr) {
+              float *__restrict__ out_dist, unsigned long long *__restrict__ ctr, const unsigned *__restrict__ list,
+              const unsigned *__restrict__ perm) {
     __shared__ unsigned s_stack[kWarpsPerCta][kStack];   // entries: (level << 27) | node   (level >= 1)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long qi = blockIdx.x * (long long)kWarpsPerCta + warp;
-    if (qi >= nq) return;
+    const long long n_work = LIST ? (long long)list[0] * 32 : nq;
+    for (long long item = blockIdx.x * (long long)kWarpsPerCta + warp; item < n_work;
+         item += LIST ? gridDim.x * (long long)kWarpsPerCta : n_work) {
+    long long qi = item;
+    if (LIST) {
+        const long long pos = (long long)list[1 + (item >> 5)] * 32 + (item & 31);
+        if (pos >= nq) continue;
+        qi = perm ? (long long)perm[pos] : pos;
+    }
     const float *q = queries + qi * stride;
     const float qx = __ldg(q), qy = __ldg(q + 1), qz = __ldg(q + 2);
     unsigned *stack = s_stack[warp];
@@ -117,6 +128,8 @@ radius_kernel(const IndexView ix, const float *__restrict__ queries, long long n
         atomicAdd(ctr + 4, 1ull);
         atomicAdd(ctr + 5, (unsigned long long)n_scan);
     }
+    __syncwarp();
+    }
 }
 
 // counts (nq) -> offsets (nq+1) with offsets[0] = 0
@@ -124,6 +137,7 @@ __global__ void set_zero_kernel(long long *p) { *p = 0; }
 
 // Below this many queries the warp-per-query kernel wins (no query sort, 32x more warps).
 constexpr int64_t kTileMinQueries = 8192;
+constexpr int64_t kTileFillMinQueries = 262144;   // FILL pass: tiled kernel from here on (see radius_fill_device)
 
 // 0 = by query count, 1 = warp-per-query, 2 = tiled (PCP_RADIUS_KERNEL=warp|tile, for tests)
 int radius_kernel_choice() {
@@ -155,6 +169,24 @@ int radius_query_perm(pcp_index *ix, const float *d_q, int64_t nq, int64_t strid
 
 }  // namespace
 
+// Groups the tiled kernel handed over (its stragglers), one warp per query, persistent grid.
+int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
+                            const uint32_t *d_list, float d2max, long long *d_counts, const long long *d_offsets,
+                            int32_t *d_idx, float *d_dist) {
+    pcp_ctx *ctx = ix->ctx;
+    const IndexView v = make_view(ix);
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    if (d_counts)
+        radius_kernel<false, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, d_counts, nullptr,
+                                                                               nullptr, nullptr, ctx->ctr(), d_list, d_perm);
+    else
+        radius_kernel<true, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, nullptr, d_offsets,
+                                                                              d_idx, d_dist, ctx->ctr(), d_list, d_perm);
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
 int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
                         int64_t *d_offsets) {
     pcp_ctx *ctx = ix->ctx;
@@ -175,8 +207,9 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
         PCP_TRY(radius_tile_device(ix, d_q, nq, stride, perm, d2max, counts, nullptr, nullptr, nullptr));
     } else {
         const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-        radius_kernel<false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
-                                                                         nullptr, nullptr, ctx->ctr());
+        radius_kernel<false, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
+                                                                                nullptr, nullptr, ctx->ctr(), nullptr,
+                                                                                nullptr);
         ctx->launches += 1;
     }
     size_t tmp = 0;
@@ -212,11 +245,16 @@ int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
     if (nq == 0 || ix->n == 0) return PCP_OK;
     const float d2max = exact_d2_threshold(radius);
     const IndexView v = make_view(ix);
-    // The tiled FILL writes every hit with a scattered 4-byte store (one cursor per lane): on dense results
-    // (KITTI r = 1.0: 644 hits per query) that is 5x slower than the warp kernel's ballot-compacted coalesced
-    // rows, on sparse ones (uniform r = 0.5: 32 hits) it is a tie -- so the warp kernel fills unless
-    // PCP_RADIUS_FILL=tile (tests keep the path alive).
-    static const bool tile_fill = [] { const char *e = getenv("PCP_RADIUS_FILL"); return e && strcmp(e, "tile") == 0; }();
+    // FILL kernel choice.  The tiled FILL stages hits in shared memory and writes 64-byte runs; it walks the
+    // hierarchy once per 32 queries and wins on large query sets at every result density (1 M uniform queries:
+    // 0.56-... ms against 0.99-2.64 ms).  On a KITTI-sized set (3 896 groups: half the warp slots idle) the
+    // warp-per-query kernel with its ballot-compacted rows is faster (r = 1.0: 80 M pairs at 1.9 TB/s).
+    // PCP_RADIUS_FILL=tile|warp forces one (tests keep both paths alive).
+    static const int fill_choice = [] {
+        const char *e = getenv("PCP_RADIUS_FILL");
+        return !e ? 0 : strcmp(e, "tile") == 0 ? 2 : strcmp(e, "warp") == 0 ? 1 : 0;
+    }();
+    const bool tile_fill = fill_choice == 2 || (fill_choice == 0 && nq >= kTileFillMinQueries);
     if (use_tile(nq) && tile_fill) {
         const uint32_t *perm = nullptr;
         PCP_TRY(radius_query_perm(ix, d_q, nq, stride, true, &perm));
@@ -224,8 +262,9 @@ int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
                                    d_idx, d_dist));
     } else {
         const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-        radius_kernel<true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
-            v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr());
+        radius_kernel<true, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
+            v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr(),
+            nullptr, nullptr);
         ctx->launches += 1;
     }
     PCP_CUDA(cudaGetLastError());

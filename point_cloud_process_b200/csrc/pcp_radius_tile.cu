@@ -13,6 +13,7 @@
 // (RadiusNNResultSet keeps visiting order too, result_set.py:84; `sorted` is applied afterwards).
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 
 #include "pcp_device.cuh"
 #include "pcp_internal.cuh"
@@ -21,35 +22,46 @@ namespace pcp {
 
 namespace {
 
-constexpr int kRtWarps = 8;
 constexpr int kRtStack = kMaxLevels * kFan;
 constexpr int kRtChunk = 8;
+// FILL: hits are staged per lane in shared memory (kRtCap entries, rows padded to kRtCap + 1 so that the 64-bit
+// appends of a half-warp fall into distinct banks) and flushed by the whole warp, half a warp per lane's run:
+// coalesced runs of up to 64 B instead of one scattered 4-byte store per hit.
+constexpr int kRtCap = 16;
+template <bool FILL> struct RtCfg { static constexpr int kWarps = FILL ? 4 : 8; };
 
 template <bool FILL>
-__global__ void __launch_bounds__(kRtWarps * 32)
+__global__ void __launch_bounds__(RtCfg<FILL>::kWarps * 32)
 radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm,
                    long long nq, long long stride, float d2max, long long *__restrict__ counts,
                    const long long *__restrict__ offsets, int *__restrict__ out_idx, float *__restrict__ out_dist,
-                   unsigned long long *__restrict__ ctr, unsigned *__restrict__ sched) {
+                   unsigned long long *__restrict__ ctr, unsigned *__restrict__ sched, unsigned *__restrict__ handover,
+                   unsigned n_groups, unsigned tail_slots) {
+    constexpr int kRtWarps = RtCfg<FILL>::kWarps;
     __shared__ float4 s_tile[kRtWarps][32];
     __shared__ float4 s_box[kRtWarps][128];            // half-bucket boxes of the open level-1 node
     __shared__ unsigned s_stack[kRtWarps][kRtStack];   // entries: (level << 27) | node   (level >= 1)
+    __shared__ uint2 s_hit[FILL ? kRtWarps : 1][FILL ? 32 * (kRtCap + 1) : 1];   // staged (index, d2 bits)
+    __shared__ long long s_cur[FILL ? kRtWarps : 1][32];
+    __shared__ int s_cnt[FILL ? kRtWarps : 1][32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long n_groups = (nq + 31) / 32;
     const unsigned lt_mask = (1u << lane) - 1u;
     float4 *tile = s_tile[warp];
     float4 *boxes = s_box[warp];
     unsigned *stack = s_stack[warp];
 
+    // sched[0] = next group to hand out, sched[1] = groups finished.  Tail hand-over as in knn_tile_kernel: with
+    // the queue dry and fewer than tail_slots groups in flight, the stragglers (a group whose queries straddle a
+    // jump of the Morton curve opens thousands of nodes) go on the `handover` list for the warp-per-query kernel.
     for (;;) {
-        long long group;
+        unsigned group;
         {
             unsigned g = 0;
             if (lane == 0) g = atomicAdd(sched, 1u);
             group = __shfl_sync(kFullMask, g, 0);
         }
         if (group >= n_groups) break;
-        const long long pos = group * 32 + lane;
+        const long long pos = (long long)group * 32 + lane;
         long long qid = -1;
         float qx = 0.f, qy = 0.f, qz = 0.f;
         if (pos < nq) {
@@ -64,16 +76,47 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
         ghi.x = warp_max(active ? qx : -FLT_MAX); ghi.y = warp_max(active ? qy : -FLT_MAX); ghi.z = warp_max(active ? qz : -FLT_MAX);
         long long cursor = (FILL && active) ? offsets[qid] : 0;   // COUNT: hits so far; FILL: next output slot
         unsigned n_half = 0, n_open = 0;
+        // FILL: this lane's staging row and its append position (shared-memory byte address), entries pending
+        const unsigned row_addr = (unsigned)__cvta_generic_to_shared(&s_hit[FILL ? warp : 0][FILL ? lane * (kRtCap + 1) : 0]);
+        unsigned waddr = row_addr;
+        auto flush = [&]() {
+            const int n_pend = (int)((waddr - row_addr) >> 3);
+            s_cnt[FILL ? warp : 0][lane] = n_pend;
+            s_cur[FILL ? warp : 0][lane] = cursor;
+            __syncwarp();
+            const int j = lane & 15;
+#pragma unroll 4
+            for (int src = lane >> 4; src < 32; src += 2) {       // half a warp writes one lane's run
+                if (j < s_cnt[FILL ? warp : 0][src]) {
+                    const uint2 e = s_hit[FILL ? warp : 0][src * (kRtCap + 1) + j];
+                    const long long o = s_cur[FILL ? warp : 0][src] + j;
+                    out_idx[o] = (int)e.x;
+                    out_dist[o] = __fsqrt_rn(__uint_as_float(e.y));
+                }
+            }
+            __syncwarp();
+            cursor += n_pend;
+            waddr = row_addr;
+        };
 
         const int top = ix.n_levels - 1;                 // >= 1 for every non-empty index
         int sp = 1;
         if (lane == 0) stack[0] = ((unsigned)top << 27);
         __syncwarp();
+        bool aborted = false;
         while (sp > 0) {
             const unsigned e = stack[sp - 1];
             --sp;
             __syncwarp();
             ++n_open;
+            if (tail_slots && (n_open & 7u) == 0u) {
+                uint2 w = make_uint2(0u, 0u);
+                if (lane == 0) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(w.x), "=r"(w.y) : "l"(sched));
+                if (__shfl_sync(kFullMask, (w.x >= n_groups && n_groups - w.y < tail_slots) ? 1 : 0, 0)) {
+                    aborted = true;
+                    break;
+                }
+            }
             const int lv = (int)(e >> 27);
             const unsigned node = e & 0x07ffffffu;
             const long long c = (long long)node * kFan + lane;
@@ -120,6 +163,8 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
 #pragma unroll 1
                 for (int j0 = 0; j0 < 32; j0 += kRtChunk) {
                     if (!((halves >> (j0 >> 4)) & 1u)) continue;
+                    // a row that could overflow during the next chunk: the warp flushes all rows
+                    if (FILL && __any_sync(kFullMask, waddr > row_addr + (kRtCap - kRtChunk) * 8)) flush();
                     float4 p[kRtChunk];
 #pragma unroll
                     for (int i = 0; i < kRtChunk; ++i) p[i] = tile[j0 + i];
@@ -128,17 +173,23 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
                         const float d2 = ref_d2(qx, qy, qz, p[i].x, p[i].y, p[i].z);
                         if (d2 <= gate) {                            // NaN pads never hit
                             if (FILL) {
-                                out_idx[cursor] = (int)__float_as_uint(p[i].w);
-                                out_dist[cursor] = __fsqrt_rn(d2);
+                                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(p[i].w), "f"(d2) : "memory");
+                                waddr += 8;
+                            } else {
+                                ++cursor;
                             }
-                            ++cursor;
                         }
                     }
                 }
             }
             __syncwarp();     // the boxes of this node are dead: the next open may overwrite them
         }
-        if (!FILL && active) counts[qid] = cursor;
+        if (FILL && !aborted) flush();
+        if (lane == 0) {
+            if (aborted) handover[1 + atomicAdd(handover, 1u)] = group;
+            atomicAdd(sched + 1, 1u);
+        }
+        if (!FILL && active && !aborted) counts[qid] = cursor;
         const unsigned n_active = __popc(__ballot_sync(kFullMask, active));   // (all lanes: a full-mask vote)
         if (ctr && lane == 0) {
             atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
@@ -159,19 +210,26 @@ int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
     const long long n_groups = (nq + 31) / 32;
-    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * 4));
+    // scratch: [0] next group, [1] groups finished, [2] hand-over count, [3..] hand-over list
+    PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(n_groups + 4)));
     unsigned *sched = ctx->scratch[5].as<unsigned>();
-    PCP_CUDA(cudaMemsetAsync(sched, 0, sizeof(unsigned), ctx->stream));
-    const unsigned grid = (unsigned)std::min<long long>((n_groups + kRtWarps - 1) / kRtWarps, (long long)ctx->sm_count * 6);
+    unsigned *handover = sched + 2;
+    PCP_CUDA(cudaMemsetAsync(sched, 0, 3 * sizeof(unsigned), ctx->stream));
+    const int warps = d_counts ? RtCfg<false>::kWarps : RtCfg<true>::kWarps;
+    const unsigned grid = (unsigned)std::min<long long>((n_groups + warps - 1) / warps, (long long)ctx->sm_count * 6);
+    static const char *e_tail = getenv("PCP_TILE_TAIL");   // developer override (share of the warp slots; 0 = off)
+    const unsigned tail_slots = (unsigned)((e_tail ? atof(e_tail) : 0.05) * (double)grid * warps);
     if (d_counts)
-        radius_tile_kernel<false><<<grid, kRtWarps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, d_counts,
-                                                                          nullptr, nullptr, nullptr, ctx->ctr(), sched);
+        radius_tile_kernel<false><<<grid, warps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, d_counts,
+                                                                          nullptr, nullptr, nullptr, ctx->ctr(), sched,
+                                                                          handover, (unsigned)n_groups, tail_slots);
     else
-        radius_tile_kernel<true><<<grid, kRtWarps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, nullptr,
-                                                                         d_offsets, d_idx, d_dist, ctx->ctr(), sched);
+        radius_tile_kernel<true><<<grid, warps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, nullptr,
+                                                                         d_offsets, d_idx, d_dist, ctx->ctr(), sched,
+                                                                         handover, (unsigned)n_groups, tail_slots);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
-    return PCP_OK;
+    return radius_warp_list_device(ix, d_q, nq, stride, d_perm, handover, d2max, d_counts, d_offsets, d_idx, d_dist);
 }
 
 }  // namespace pcp
