@@ -35,8 +35,8 @@ if ROOT not in sys.path:
 KITTI = os.path.join(ROOT, "tests", "golden", "kitti_000000_xyz.f32")
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE knn_tile_kernel launch, from the ncu --set full capture of
 # this workload committed under profiles/ (bytes); updated by hand when the capture is redone.
-NCU_TRAFFIC = {"kitti_knn8": 4271360 + 0,                # profiles/r1_ncu_knn_tile_kitti_k8.txt
-               "uniform1m_knn16": 40746496 + 98114048}   # profiles/r1_ncu_knn_tile_uniform1m_k16.txt
+NCU_TRAFFIC = {"kitti_knn8": 4288512 + 0,                # profiles/r1_ncu_knn_tile_kitti_k8.txt
+               "uniform1m_knn16": 40651008 + 97467136}   # profiles/r1_ncu_knn_tile_uniform1m_k16.txt
 SM_COUNT_B200 = 148
 FP32_LANES_PER_SM = 128
 
