@@ -104,17 +104,17 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                 int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg,
                 unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests, int trigger,
                 unsigned tail_slots, unsigned *__restrict__ sched, unsigned n_groups, float *__restrict__ hints,
-                unsigned hint_groups) {
+                unsigned hint_groups, unsigned warp_stride) {
     constexpr int kTileWarps = TileCfg<K>::kWarps;
     constexpr int kCap = TileCfg<K>::kCap;
     // dynamic shared memory: [kTileWarps][kCap][32] candidate columns (d2 bits, index) first -- the filter's
     // read-ahead past the last column lands in the arrays behind them --, then per warp: staged bucket,
-    // half-bucket boxes, one row of child bounds per tree level, open node per level
+    // half-bucket boxes, open node per level, one row of child bounds per tree level
     extern __shared__ uint2 s_cand[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_lv = ix.n_levels > 1 ? ix.n_levels - 1 : 1;
-    unsigned char *s_rest = reinterpret_cast<unsigned char *>(s_cand + kTileWarps * kCap * 32) +
-                            (size_t)warp * (tile_warp_bytes(0, n_lv));
+    // (warp_stride = tile_warp_bytes(0, levels), a kernel parameter: the per-warp arrays sit at constant offsets
+    // from one base that costs a single multiply-add to re-derive)
+    unsigned char *s_rest = reinterpret_cast<unsigned char *>(s_cand + kTileWarps * kCap * 32) + warp * warp_stride;
     // sched (behind the overflow list): [0] next group to hand out, [1] groups finished (zeroed by the host);
     // it and n_groups are kernel parameters so that the tail poll below holds no registers across the hot loops
     // Persistent warps: groups are handed out dynamically, so the kernel ends within one group's work of the
@@ -282,8 +282,8 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
 
     const int top_level = ix.n_levels - 1;      // >= 1 for every non-empty index (pcp_build.cu)
     if (top_level > 0) {
-        unsigned(*lbs)[32] = reinterpret_cast<unsigned(*)[32]>(s_rest + 512 + kBoxFloats * 4) - 1;   // row lv - 1
-        unsigned *nodes = reinterpret_cast<unsigned *>(s_rest + 512 + kBoxFloats * 4 + (size_t)n_lv * 128) - 1;
+        unsigned *nodes = reinterpret_cast<unsigned *>(s_rest + 512 + kBoxFloats * 4) - 1;               // [lv - 1]
+        unsigned(*lbs)[32] = reinterpret_cast<unsigned(*)[32]>(s_rest + 512 + kBoxFloats * 4 + 32) - 1;   // row lv - 1
         auto open_node = [&](int lv, unsigned node) {
             ++n_open;
             if (lv == 1 && (n_open & 3u) == 0u) poll_tail();
@@ -492,7 +492,8 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
                                                                        d_count, ctr, dbg, overflow, max_scans,         \
                                                                        max_tests, trig, tail_slots,                    \
                                                                        overflow + sched_at, (unsigned)n_groups, hints, \
-                                                                       hint_groups);                                   \
+                                                                       hint_groups,                                    \
+                                                                       (unsigned)tile_warp_bytes(0, n_lv));            \
     } while (0)
     cudaEvent_t ev_end = nullptr;
     if (ctx->time_kernels) {
