@@ -31,21 +31,17 @@ constexpr int kMaxGridY = 65535;
 // per segment: 8 floats (lo.xyz, scale, hi.xyz, extent) followed by 8 ordered-uint accumulators
 constexpr int kBboxWords = 16;
 
-__global__ void bbox_init_kernel(float *bbox_all, long long P) {
-    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= P * 8) return;
-    unsigned *acc = reinterpret_cast<unsigned *>(bbox_all + (i >> 3) * kBboxWords + 8);
-    int t = (int)(i & 7);
-    acc[t] = t < 3 ? 0xffffffffu : 0u;        // min slots / max slots
-}
-
+// Bounding box of every segment in ONE launch.  Accumulators: words 8..13 of the segment's record, merged with
+// atomicMax only -- the minima are kept complemented -- so that all-zero words are the identity; word 14 counts
+// the CTAs that are done.  The last CTA of a segment turns the accumulators into the record morton30() reads
+// {lo.xyz, cells-per-unit, hi.xyz, extent} and zeroes them again for the next build (the buffer is zeroed once
+// when it is allocated).
 __global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz, long long stride,
                                                    const IndexView *__restrict__ views) {
     const IndexView &v = views[blockIdx.y];
     const long long n = v.n;
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     const long long first = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (blockIdx.x * (long long)blockDim.x >= n) return;
     for (long long i = first; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float *p = xyz + (v.src_off + i) * stride;
 #pragma unroll
@@ -61,40 +57,43 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz
         hi[a] = warp_max(hi[a]);
     }
     // warp results -> shared memory -> one set of 6 atomics per CTA (thousands of same-address atomics
-    // from every warp serialise in L2: 18.8 us -> measured in profiles/ for the 124 668-point scan)
+    // from every warp serialise in L2)
     __shared__ float s_lo[8][3], s_hi[8][3];
+    __shared__ bool s_last;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane == 0) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) { s_lo[warp][a] = lo[a]; s_hi[warp][a] = hi[a]; }
     }
     __syncthreads();
-    if (threadIdx.x < 6) {
+    float *bbox = const_cast<float *>(v.bbox);
+    unsigned *acc = reinterpret_cast<unsigned *>(bbox + 8);
+    if (threadIdx.x < 6 && blockIdx.x * (long long)blockDim.x < n) {
         const int a = threadIdx.x % 3;
         const bool is_hi = threadIdx.x >= 3;
         float r = is_hi ? s_hi[0][a] : s_lo[0][a];
         for (int w = 1; w < 8; ++w) r = is_hi ? fmaxf(r, s_hi[w][a]) : fminf(r, s_lo[w][a]);
-        unsigned *acc = reinterpret_cast<unsigned *>(const_cast<float *>(v.bbox) + 8);
-        if (is_hi) atomicMax(&acc[3 + a], float_to_ordered(r));
-        else atomicMin(&acc[a], float_to_ordered(r));
+        atomicMax(&acc[threadIdx.x], is_hi ? float_to_ordered(r) : ~float_to_ordered(r));
+        __threadfence();
     }
-}
-
-// accumulator words -> {lo.x, lo.y, lo.z, cells-per-unit, hi.xyz, extent} used by morton30()
-__global__ void bbox_finish_kernel(float *bbox_all, long long P) {
-    long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (s >= P) return;
-    float *bbox = bbox_all + s * kBboxWords;
-    const unsigned *acc = reinterpret_cast<const unsigned *>(bbox + 8);
-    float lo[3], hi[3];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&acc[6], 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last || threadIdx.x != 0) return;
+    __threadfence();
+    float l[3], h[3];
     for (int a = 0; a < 3; ++a) {
-        lo[a] = ordered_to_float(acc[a]);
-        hi[a] = ordered_to_float(acc[3 + a]);
+        l[a] = ordered_to_float(~atomicExch(&acc[a], 0u));         // (empty segment: ~0 and 0, as before)
+        h[a] = ordered_to_float(atomicExch(&acc[3 + a], 0u));
     }
-    float ext = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), hi[2] - lo[2]);
+    acc[6] = 0u;
+    float ext = fmaxf(fmaxf(h[0] - l[0], h[1] - l[1]), h[2] - l[2]);
     float scale = (ext > 0.f && isfinite(ext)) ? 1024.f / (ext * 1.0001f) : 0.f;
-    bbox[0] = lo[0]; bbox[1] = lo[1]; bbox[2] = lo[2]; bbox[3] = scale;
-    bbox[4] = hi[0]; bbox[5] = hi[1]; bbox[6] = hi[2]; bbox[7] = ext;
+    bbox[0] = l[0]; bbox[1] = l[1]; bbox[2] = l[2]; bbox[3] = scale;
+    bbox[4] = h[0]; bbox[5] = h[1]; bbox[6] = h[2]; bbox[7] = ext;
 }
 
 template <class KeyT>
@@ -237,10 +236,12 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
                                                                const unsigned *__restrict__ sorted_rows) {
     __shared__ RefineSmem sm;
     __shared__ unsigned s_idx[kRefine];
+    __shared__ unsigned s_node[6];                               // AABB of the whole block = the level-1 node
     const IndexView &v = views[blockIdx.y];
     const long long node = blockIdx.x;
     if (node * kFan >= v.n_leaf) return;
     const unsigned t = threadIdx.x;
+    if (t < 6) s_node[t] = t < 3 ? 0xffffffffu : 0u;             // (ordered by the barriers inside refine_block)
     const long long pos = node * kRefine + t;
     float x = nanf(""), y = x, z = x;
     unsigned idx = 0xffffffffu;
@@ -254,7 +255,7 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
     s_idx[t] = idx;
     const unsigned id = refine_block<true>(sm, x, y, z, valid);
     const long long leaf = pos >> 5;
-    if (leaf >= v.n_leaf) return;                                // whole warp: bucket beyond the cloud
+    if (leaf < v.n_leaf) {                                       // (whole warp) else: bucket beyond the cloud
     x = sm.x[id]; y = sm.y[id]; z = sm.z[id];
     idx = s_idx[id];
     const_cast<float4 *>(v.pts)[pos] = make_float4(x, y, z, __uint_as_float(idx));
@@ -266,6 +267,8 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
     if ((t & 31) == 0) {
         const_cast<float4 *>(v.box_lo)[leaf] = make_float4(ordered_to_float(lx), ordered_to_float(ly), ordered_to_float(lz), 0.f);
         const_cast<float4 *>(v.box_hi)[leaf] = make_float4(ordered_to_float(hx), ordered_to_float(hy), ordered_to_float(hz), 0.f);
+        atomicMin(&s_node[0], lx); atomicMin(&s_node[1], ly); atomicMin(&s_node[2], lz);
+        atomicMax(&s_node[3], hx); atomicMax(&s_node[4], hy); atomicMax(&s_node[5], hz);
     }
     // AABBs of the two 16-point halves (the sixth split): an empty half gets (+inf, -inf), infinitely far from everything
     const unsigned hm = (t & 16) ? 0xffff0000u : 0x0000ffffu;
@@ -278,6 +281,15 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
         float4 *h = const_cast<float4 *>(v.half) + leaf * 4 + ((t & 16) ? 2 : 0);
         h[0] = any ? make_float4(ordered_to_float(alx), ordered_to_float(aly), ordered_to_float(alz), 0.f) : make_float4(inf, inf, inf, 0.f);
         h[1] = any ? make_float4(ordered_to_float(ahx), ordered_to_float(ahy), ordered_to_float(ahz), 0.f) : make_float4(-inf, -inf, -inf, 0.f);
+    }
+    }
+    // the block is one level-1 node: its box is the union of the bucket boxes (same values node_box_kernel
+    // would compute: min / max of the same floats)
+    __syncthreads();
+    if (t == 0 && v.n_levels > 1) {
+        const long long at = v.level_off[1] + node;
+        const_cast<float4 *>(v.box_lo)[at] = make_float4(ordered_to_float(s_node[0]), ordered_to_float(s_node[1]), ordered_to_float(s_node[2]), 0.f);
+        const_cast<float4 *>(v.box_hi)[at] = make_float4(ordered_to_float(s_node[3]), ordered_to_float(s_node[4]), ordered_to_float(s_node[5]), 0.f);
     }
 }
 
@@ -320,6 +332,32 @@ __global__ void __launch_bounds__(256) node_box_kernel(const IndexView *__restri
     if (lane == 0) {
         box_lo[v.level_off[level] + node] = make_float4(lx, ly, lz, 0.f);
         box_hi[v.level_off[level] + node] = make_float4(hx, hy, hz, 0.f);
+    }
+}
+
+// Levels first_level .. top of every segment in one launch (one CTA per segment): used once a level is small
+// enough (<= kFusedLevelNodes nodes) that a launch per level costs more than the serial walk.
+constexpr long long kFusedLevelNodes = 256;
+__global__ void __launch_bounds__(256) upper_boxes_kernel(const IndexView *__restrict__ views, int first_level) {
+    const IndexView &v = views[blockIdx.y];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float4 *box_lo = const_cast<float4 *>(v.box_lo), *box_hi = const_cast<float4 *>(v.box_hi);
+    for (int level = first_level; level < v.n_levels; ++level) {
+        for (long long node = warp; node < v.level_cnt[level]; node += 8) {
+            const long long c = node * kFan + lane;
+            float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+            if (c < v.level_cnt[level - 1]) {
+                lo = box_lo[v.level_off[level - 1] + c];
+                hi = box_hi[v.level_off[level - 1] + c];
+            }
+            const float lx = warp_min(lo.x), ly = warp_min(lo.y), lz = warp_min(lo.z);
+            const float hx = warp_max(hi.x), hy = warp_max(hi.y), hz = warp_max(hi.z);
+            if (lane == 0) {
+                box_lo[v.level_off[level] + node] = make_float4(lx, ly, lz, 0.f);
+                box_hi[v.level_off[level] + node] = make_float4(hx, hy, hz, 0.f);
+            }
+        }
+        __syncthreads();                       // the next level reads what this one wrote (same CTA)
     }
 }
 
@@ -412,7 +450,12 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     PCP_TRY(b->box_lo.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
     PCP_TRY(b->box_hi.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
     PCP_TRY(b->half.ensure(sizeof(float4) * 4 * (size_t)std::max<int64_t>(1, b->total_leaf)));
-    PCP_TRY(b->bbox.ensure(sizeof(float) * kBboxWords * (size_t)P));
+    {
+        const size_t before = b->bbox.cap;
+        PCP_TRY(b->bbox.ensure(sizeof(float) * kBboxWords * (size_t)P));
+        // fresh allocation: zero = the identity of bbox_kernel's accumulators (which clean up after themselves)
+        if (b->bbox.cap != before) PCP_CUDA(cudaMemsetAsync(b->bbox.p, 0, b->bbox.cap, st));
+    }
     PCP_TRY(b->views.ensure(sizeof(IndexView) * (size_t)P));
     for (int64_t p = 0; p < P; ++p) {
         IndexView &v = b->h_views[(size_t)p];
@@ -435,8 +478,6 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     PCP_TRY(b->vals_b.ensure(sizeof(unsigned) * (size_t)b->total_n));
     const IndexView *dv = b->d_views();
 
-    bbox_init_kernel<<<grid_for(P * 8, 256), 256, 0, st>>>(b->bbox.as<float>(), P);
-    ctx->launches += 1;
     const unsigned bx = (unsigned)std::min<long long>(grid_for(b->max_n, 256),
                                                       P == 1 ? (long long)ctx->sm_count * 2 : 16);
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
@@ -444,8 +485,6 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         bbox_kernel<<<dim3(bx, gy), 256, 0, st>>>(d_xyz, stride, dv + p0);
         ctx->launches += 1;
     }
-    bbox_finish_kernel<<<grid_for(P, 128), 128, 0, st>>>(b->bbox.as<float>(), P);
-    ctx->launches += 1;
     if (b->ev_bbox) PCP_CUDA(cudaEventRecord(b->ev_bbox, st));   // query keys only need the boxes, not the sorted cloud
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
@@ -474,7 +513,13 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         refine_leaf_kernel<<<dim3((unsigned)((b->max_leaf + kFan - 1) / kFan), gy), kRefine, 0, st>>>(
             d_xyz, stride, dv + p0, b->vals_b.as<unsigned>());
         ctx->launches += 1;
-        for (int l = 1; l < b->max_levels; ++l) {
+        // level 1 came out of refine_leaf_kernel; wide levels get a launch each, the small ones above share one
+        for (int l = 2; l < b->max_levels; ++l) {
+            if (b->level_max_cnt[l] <= kFusedLevelNodes) {
+                upper_boxes_kernel<<<dim3(1, gy), 256, 0, st>>>(dv + p0, l);
+                ctx->launches += 1;
+                break;
+            }
             node_box_kernel<<<dim3(grid_for(b->level_max_cnt[l] * 32, 256), gy), 256, 0, st>>>(dv + p0, l);
             ctx->launches += 1;
         }

@@ -275,6 +275,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
                     // still too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
                     if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kChunk / 2) * 256)) aborted = true;
                 }
+                if (aborted) break;      // (before the second half appends past the end of the columns)
             }
             if (aborted) break;
         }

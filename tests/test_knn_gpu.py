@@ -202,14 +202,20 @@ def test_knn_mass_ties_tile_kernel(pcp):
     from oracle import knn_oracle
     rng = np.random.default_rng(11)
     base = (rng.random((400, 3)) * 10).astype(np.float32)
-    db = np.repeat(base, 40, axis=0)
-    db = db[rng.permutation(len(db))]
+    owner = np.repeat(np.arange(400), 40)
+    order = rng.permutation(len(owner))
+    owner = owner[order]
+    db = base[owner]
     assert len(db) >= 8192                                   # large enough for the tiled path
     idx, dist, cnt = pcp.SearchIndex(db).knn(db, 8)
     sel = rng.choice(len(db), 1024, replace=False)
     b_dist, b_idx, b_cnt = knn_oracle.bruteforce_knn(db, db[sel], 8, threads=8)
     assert np.array_equal(dist[sel], b_dist) and np.array_equal(idx[sel], b_idx.astype(np.int32))
     assert (cnt == 8).all() and (dist == 0).all()
+    # every query: the 8 lowest row numbers among its 40 copies (a group that gives up must not disturb the
+    # candidate columns of the groups next to it)
+    rows = np.argsort(owner, kind="stable").reshape(400, 40)[:, :8]      # ascending rows per base point
+    assert np.array_equal(idx, rows[owner].astype(np.int32))
 
 
 def test_result_arrays_outlive_index_and_pool_reuse(pcp, kitti):
