@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "pcp_device.cuh"
@@ -96,17 +97,19 @@ __global__ void __launch_bounds__(256) bbox_kernel(const float *__restrict__ xyz
     bbox[4] = h[0]; bbox[5] = h[1]; bbox[6] = h[2]; bbox[7] = ext;
 }
 
+// key = (segment << seg_shift) | (morton30 >> skip): one index sorts plain 30-bit codes (skip = seg_shift = 0, the
+// radix passes start at the first significant bit); a batch packs segment id and the significant Morton bits
+// into as few bits as they need, so that 1 024 clouds of 20 000 points sort as 24-bit keys in 3 passes.
 template <class KeyT>
 __global__ void __launch_bounds__(256) key_kernel(const float *__restrict__ xyz, long long stride,
-                                                  const IndexView *__restrict__ views, long long seg0,
-                                                  KeyT *__restrict__ keys, unsigned *__restrict__ vals) {
+                                                  const IndexView *__restrict__ views, long long seg0, int skip,
+                                                  int seg_shift, KeyT *__restrict__ keys, unsigned *__restrict__ vals) {
     const IndexView &v = views[blockIdx.y];
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= v.n) return;
     const float *p = xyz + (v.src_off + i) * stride;
     const KeyT seg = static_cast<KeyT>(seg0 + blockIdx.y);
-    // sizeof(KeyT) == 4 only when there is a single segment
-    keys[v.src_off + i] = (sizeof(KeyT) == 4 ? KeyT(0) : static_cast<KeyT>(seg << 30)) | morton30(p[0], p[1], p[2], v.bbox);
+    keys[v.src_off + i] = static_cast<KeyT>(seg << seg_shift) | static_cast<KeyT>(morton30(p[0], p[1], p[2], v.bbox) >> skip);
     vals[v.src_off + i] = static_cast<unsigned>(v.src_off + i);
 }
 
@@ -387,7 +390,11 @@ int radix_sort_pairs(pcp_ctx *ctx, const KeyT *k_in, KeyT *k_out, const unsigned
 // Low Morton bits that the sort may ignore: the order only has to make every run of 1024 points spatially
 // coherent (the kd refinement re-partitions inside the run), so cells holding ~4 points on average are fine
 // enough -- 16 significant bits up to 256 k points, 24 up to 64 M, all 30 beyond.  One radix pass per 8 bits.
-inline int morton_skip_bits(long long n) { return n <= (1LL << 18) ? 14 : n <= (1LL << 26) ? 6 : 0; }
+inline int morton_skip_bits(long long n) {
+    static const char *e = getenv("PCP_MORTON_SKIP");   // developer override
+    if (e) return atoi(e);
+    return n <= (1LL << 18) ? 14 : n <= (1LL << 26) ? 6 : 0;
+}
 
 inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(std::max<long long>(1, (n + block - 1) / block)); }
 
@@ -470,8 +477,20 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     PCP_CUDA(cudaMemcpyAsync(b->views.p, b->h_views.data(), sizeof(IndexView) * (size_t)P, cudaMemcpyHostToDevice, st));
     if (b->total_n == 0) return PCP_OK;
 
+    // Key layout.  Batch: segment id above the significant Morton bits -- per cloud one bit fewer than
+    // ceil(log2 n) (~2 points per cell, what 16 bits are to the KITTI scan; never more than a single index of that
+    // size would sort) -- in 32-bit keys when both fit, else 64-bit keys.
     const bool wide = P > 1;
-    const size_t key_bytes = wide ? 8 : 4;
+    int seg_bits = 0, mbits = 30 - morton_skip_bits(wide ? b->max_n : b->total_n);
+    if (wide) {
+        seg_bits = 1;
+        while ((1LL << seg_bits) < P) ++seg_bits;
+        int lg = 0;
+        while ((1LL << lg) < b->max_n) ++lg;
+        mbits = std::max(8, std::min(mbits, lg - 1));
+    }
+    const bool wide64 = wide && seg_bits + mbits > 32;
+    const size_t key_bytes = wide64 ? 8 : 4;
     PCP_TRY(b->keys_a.ensure(key_bytes * (size_t)b->total_n));
     PCP_TRY(b->keys_b.ensure(key_bytes * (size_t)b->total_n));
     PCP_TRY(b->vals_a.ensure(sizeof(unsigned) * (size_t)b->total_n));
@@ -488,25 +507,27 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     if (b->ev_bbox) PCP_CUDA(cudaEventRecord(b->ev_bbox, st));   // query keys only need the boxes, not the sorted cloud
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
-        if (wide)
+        if (wide64)
             key_kernel<unsigned long long><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
-                d_xyz, stride, dv + p0, p0, b->keys_a.as<unsigned long long>(), b->vals_a.as<unsigned>());
+                d_xyz, stride, dv + p0, p0, 30 - mbits, mbits, b->keys_a.as<unsigned long long>(), b->vals_a.as<unsigned>());
         else
             key_kernel<unsigned><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
-                d_xyz, stride, dv + p0, p0, b->keys_a.as<unsigned>(), b->vals_a.as<unsigned>());
+                d_xyz, stride, dv + p0, p0, wide ? 30 - mbits : 0, wide ? mbits : 0, b->keys_a.as<unsigned>(),
+                b->vals_a.as<unsigned>());
         ctx->launches += 1;
     }
-    if (wide) {
-        int seg_bits = 1;
-        while ((1LL << seg_bits) < P) ++seg_bits;
+    if (wide64) {
         PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
                                                      b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
-                                                     b->vals_b.as<unsigned>(), b->total_n, morton_skip_bits(b->max_n),
-                                                     30 + seg_bits));
+                                                     b->vals_b.as<unsigned>(), b->total_n, 0, mbits + seg_bits));
+    } else if (wide) {
+        PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
+                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n, 0,
+                                           mbits + seg_bits));
     } else {
         PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
                                            b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n,
-                                           morton_skip_bits(b->total_n), 30));
+                                           30 - mbits, 30));
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
