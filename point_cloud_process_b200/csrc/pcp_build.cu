@@ -489,7 +489,8 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         while ((1LL << lg) < b->max_n) ++lg;
         mbits = std::max(8, std::min(mbits, lg - 1));
     }
-    const bool wide64 = wide && seg_bits + mbits > 32;
+    static const bool force64 = getenv("PCP_BUILD_KEYS") && strcmp(getenv("PCP_BUILD_KEYS"), "64") == 0;   // tests
+    const bool wide64 = wide && (seg_bits + mbits > 32 || force64);
     const size_t key_bytes = wide64 ? 8 : 4;
     PCP_TRY(b->keys_a.ensure(key_bytes * (size_t)b->total_n));
     PCP_TRY(b->keys_b.ensure(key_bytes * (size_t)b->total_n));

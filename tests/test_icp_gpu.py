@@ -133,3 +133,26 @@ def test_homo2tq_golden(pcp, icp_golden):
     g = icp_golden
     got = np.asarray([pcp.native.homo2tq(M) for M in g["quat/homo"]])
     assert np.array_equal(got, g["quat/tq"])
+
+
+@pytest.mark.timeout(600)
+def test_icp_batch_key_width_same_results():
+    """The batched build packs (segment id, significant Morton bits) into 32-bit sort keys when they fit;
+    PCP_BUILD_KEYS=64 forces the 64-bit layout.  Same order, so bit-identical poses and iteration counts."""
+    import os, subprocess, sys, tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import point_cloud_process_b200 as pcp;"
+            "from oracle import icp_oracle;"
+            "prs = [icp_oracle.make_pair(2000 + i, n=1500 + 331 * i, box=(30.0, 30.0, 5.0)) for i in range(9)];"
+            "out = pcp.icp_batch([p[1] for p in prs], [p[0] for p in prs], max_iteration=30, R_diff_thres=1e-6, t_diff_thres=1e-6);"
+            "np.savez(sys.argv[1], T=out['T_total'], L=out['T_last'], it=out['iterations'], st=out['status'])") % root
+    outs = []
+    with tempfile.TemporaryDirectory() as tmp:
+        for i, extra in enumerate(({}, {"PCP_BUILD_KEYS": "64"})):
+            path = os.path.join(tmp, "v%d.npz" % i)
+            r = subprocess.run([sys.executable, "-c", code, path], env=dict(os.environ, **extra), capture_output=True,
+                               text=True, timeout=300, cwd=root)
+            assert r.returncode == 0, r.stderr[-2000:]
+            outs.append(dict(np.load(path)))
+    for key in outs[0]:
+        assert np.array_equal(outs[0][key], outs[1][key]), key

@@ -291,3 +291,51 @@ def test_work_counters_all_search_kernels(pcp, kitti):
     for a, b in zip(ref_small[0] + ref_small[1], got_small[0] + got_small[1]):
         assert np.array_equal(a, b)
     assert c_big[0] > 0 and c_small[0] > 0 and c_self[0] > 0
+
+
+def _run_variants(code, variants, timeout=600):
+    """Run `code` (writes an .npz to sys.argv[1]) once per environment variant; returns the loaded arrays."""
+    import os, subprocess, sys, tempfile
+    outs = []
+    with tempfile.TemporaryDirectory() as tmp:
+        for i, extra in enumerate(variants):
+            path = os.path.join(tmp, "v%d.npz" % i)
+            env = dict(os.environ, **extra)
+            r = subprocess.run([sys.executable, "-c", code, path], env=env, capture_output=True, text=True, timeout=timeout)
+            assert r.returncode == 0, r.stderr[-2000:]
+            outs.append(dict(np.load(path)))
+    return outs
+
+
+ROOT = __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__)))
+
+
+@pytest.mark.timeout(900)
+def test_knn_tail_handover_same_results():
+    """400 000 uniform points (12 500 groups: the unbudgeted large-grid path): the tiled kernel with the tail
+    hand-over (default), without it (PCP_TILE_TAIL=0) and the warp-per-query kernel give identical arrays for
+    EVERY query -- the stragglers that move to the overflow kernel, seeded with their gates, included."""
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import point_cloud_process_b200 as pcp;"
+            "db = (np.random.default_rng(77).random((400000, 3)) * 20).astype(np.float32);"
+            "ix = pcp.SearchIndex(db); i1, d1, c1 = ix.knn_self(8); i2, d2, c2 = ix.knn(db[::3].copy(), 16);"
+            "np.savez(sys.argv[1], i1=i1, d1=d1, c1=c1, i2=i2, d2=d2, c2=c2)") % ROOT
+    outs = _run_variants(code, [{}, {"PCP_TILE_TAIL": "0"}, {"PCP_TILE_TAIL": "0.5"}, {"PCP_KNN_KERNEL": "warp"}])
+    for o in outs[1:]:
+        for key in outs[0]:
+            assert np.array_equal(outs[0][key], o[key]), key
+
+
+@pytest.mark.timeout(900)
+def test_radius_large_query_set_paths_agree():
+    """300 000 queries (>= 262 144: tiled COUNT with hand-over + tiled staged FILL by default) against the
+    warp-per-query FILL, the tiled kernels without hand-over, and the all-warp path: same sorted CSR."""
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import point_cloud_process_b200 as pcp;"
+            "rng = np.random.default_rng(78); db = (rng.random((300000, 3)) * 15).astype(np.float32);"
+            "db[:40000] = db[:40000] * 0.1 + 3;"                      # a dense clump: long rows, many flushes
+            "off, idx, dist = pcp.SearchIndex(db).radius(db, 0.4, sorted=True);"
+            "np.savez(sys.argv[1], off=off, idx=idx, dist=dist)") % ROOT
+    outs = _run_variants(code, [{}, {"PCP_RADIUS_FILL": "warp"}, {"PCP_TILE_TAIL": "0"}, {"PCP_RADIUS_KERNEL": "warp"}])
+    assert outs[0]["off"][-1] > 300000
+    for o in outs[1:]:
+        for key in outs[0]:
+            assert np.array_equal(outs[0][key], o[key]), key
