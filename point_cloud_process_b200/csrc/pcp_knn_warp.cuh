@@ -56,9 +56,9 @@ struct QueryState {
     unsigned n_test, n_scan, n_ins, n_open;
 };
 
-__device__ __forceinline__ void scan_bucket(QueryState &st, const IndexView &ix, long long leaf, int lane, int k) {
+// p: this lane's point of the bucket (lane j = point j), loaded by the caller
+__device__ __forceinline__ void scan_bucket(QueryState &st, const float4 p, int lane, int k) {
     ++st.n_scan;
-    const float4 p = __ldg(ix.pts + leaf * kLeaf + lane);
     const float d2 = ref_d2(st.qx, st.qy, st.qz, p.x, p.y, p.z);
     if (st.first) {
         // pad points (NaN coordinates) sort to the end as empty keys
@@ -104,7 +104,7 @@ __device__ __forceinline__ void search(const IndexView &ix, QueryState &st, int 
     st.n_test = st.n_scan = st.n_ins = st.n_open = 0;
     const int top = ix.n_levels - 1;
     if (top == 0) {
-        scan_bucket(st, ix, 0, lane, k);
+        scan_bucket(st, __ldg(ix.pts + lane), lane, k);
     } else if (top > 0) {
         // children of `node` (a level-`lv` node) live on level lv-1
         auto open_node = [&](int lv, unsigned node) {
@@ -124,32 +124,59 @@ __device__ __forceinline__ void search(const IndexView &ix, QueryState &st, int 
             cds[lv][lane] = cbits;
             __syncwarp();
         };
+        // nearest pending child of the open node on `level` (ties: nearest box centre), or -1; `bound` = its
+        // lower bound.  Does not mark it visited.
+        auto select = [&](int level, unsigned &bound) -> int {
+            const unsigned mine = lbs[level][lane];
+            bound = __reduce_min_sync(kFullMask, mine);
+            if (bound == kDone) return -1;
+            unsigned tie = __ballot_sync(kFullMask, mine == bound);
+            if (tie & (tie - 1)) {   // several children at the same bound (typically 0: the query is inside them)
+                const unsigned cd = (mine == bound) ? cds[level][lane] : kDone;
+                const unsigned cbest = __reduce_min_sync(kFullMask, cd);
+                tie = __ballot_sync(kFullMask, cd == cbest);
+            }
+            return __ffs(tie) - 1;
+        };
+        auto mark = [&](int level, int sel) {
+            if (lane == sel) lbs[level][lane] = kDone;
+            __syncwarp();
+        };
         int level = top;
         open_node(top, 0u);
         while (true) {
-            const unsigned mine = lbs[level][lane];
-            const unsigned best = __reduce_min_sync(kFullMask, mine);
-            // exact prune: every point below a child is at least `best` away (in d2 arithmetic)
-            if (best == kDone || !(__uint_as_float(best) <= st.gate)) {
+            unsigned bound;
+            int sel = select(level, bound);
+            // exact prune: every point below a child is at least `bound` away (in d2 arithmetic)
+            if (sel < 0 || !(__uint_as_float(bound) <= st.gate)) {
                 if (level == top) break;
                 ++level;
                 continue;
             }
-            unsigned tie = __ballot_sync(kFullMask, mine == best);
-            if (tie & (tie - 1)) {   // several children at the same bound (typically 0: the query is inside them)
-                const unsigned cd = (mine == best) ? cds[level][lane] : kDone;
-                const unsigned cbest = __reduce_min_sync(kFullMask, cd);
-                tie = __ballot_sync(kFullMask, cd == cbest);
-            }
-            const int sel = __ffs(tie) - 1;
-            if (lane == sel) lbs[level][lane] = kDone;
-            const unsigned child = nodes[level] * kFan + sel;
+            mark(level, sel);
             ++st.n_test;
-            if (level == 1) {
-                scan_bucket(st, ix, child, lane, k);
-            } else {
+            if (level > 1) {
+                const unsigned child = nodes[level] * kFan + sel;
                 --level;
                 open_node(level, child);
+                continue;
+            }
+            // level 1: buckets.  The visiting order depends only on the bounds, so the NEXT bucket's points are
+            // requested before the current one is ranked (a query is one dependent chain of L2 round trips
+            // otherwise); if the tightened gate then excludes it, so it does every bucket after it.
+            const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
+            float4 cur = __ldg(base + sel * kLeaf);
+            while (true) {
+                unsigned nb;
+                const int nxt = select(1, nb);
+                const bool more = nxt >= 0 && __uint_as_float(nb) <= st.gate;
+                float4 pf = cur;
+                if (more) pf = __ldg(base + nxt * kLeaf);
+                scan_bucket(st, cur, lane, k);
+                if (!more || !(__uint_as_float(nb) <= st.gate)) break;
+                mark(1, nxt);
+                ++st.n_test;
+                cur = pf;
             }
         }
     }
