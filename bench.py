@@ -372,6 +372,32 @@ def main():
                 "frac": hbm_bytes / tile_s / 1e9 / peaks.get("hbm_gbs", 6533.8)},
     }
 
+    # ---- SURVEY 8(d) companions: work efficiency eta = C_min / C on a query sample, and single-shot latency
+    if rank == 0:
+        try:
+            from scipy.spatial import cKDTree
+            ctx.synchronize()
+            d_k = dst[:, k - 1].cpu().numpy().astype(np.float64)          # true k-th distances (exact search)
+            sel = np.random.default_rng(5).choice(n, min(n, 4000), replace=False)
+            tree = cKDTree(pts.astype(np.float64))
+            # C_min: points inside the L-infinity cube of half-side rho_q (what ANY cell/box scheme must look at)
+            c_min = sum(len(tree.query_ball_point(pts[i].astype(np.float64), d_k[i], p=np.inf)) for i in sel)
+            roofline["work_efficiency"] = {"eta": (c_min / len(sel)) / (evals_all / n), "c_min_per_query": c_min / len(sel),
+                                           "c_per_query": evals_all / n, "sample_queries": int(len(sel)),
+                                           "note": "C_min = points with |p - q|_inf <= true k-th distance (host, scipy)"}
+        except Exception as e:                                             # a reporting extra, never fatal
+            roofline["work_efficiency"] = {"error": repr(e)[:200]}
+    shots = []
+    for _ in range(20):
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        step()
+        ctx.synchronize()
+        shots.append(time.perf_counter() - t0)
+    latency = {"single_shot_ms": 1e3 * statistics.median(shots), "min_ms": 1e3 * min(shots),
+               "note": "one build + kNN step issued on an idle stream and waited for (host clock, launches included); "
+                       "no CUDA graph: the steady-state figure is 'ms_per_step' over back-to-back stream launches"}
+
     # ---- end to end through the public API with pinned host buffers (H2D + D2H inside)
     h_pts = torch.from_numpy(pts).pin_memory()
     h_np = h_pts.numpy()
@@ -417,6 +443,7 @@ def main():
 
     line = {
         "metric": "kNN queries/s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "latency": latency,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "KITTI scan bundled with the reference (tests/golden copy)" if args.workload.startswith("kitti") else "synthetic",
         "config": {"workload": args.workload, "desc": w["desc"], "step": "index build + kNN of every point",
