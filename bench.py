@@ -351,6 +351,11 @@ def main():
         t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
+        per_rank = [None] * world                     # diagnostic: device time and host issue rate of every rank
+        dist.all_gather_object(per_rank, {"ms_per_step": total_ms_local / K, "step_median_ms": statistics.median(step_ms),
+                                          "wall_ms_per_step": 1e3 * t_wall / K})
+    else:
+        per_rank = None
     value = world * n * K / (total_ms * 1e-3)
 
     # ---- work counters (untimed pass): distance evaluations C of the kNN kernel
@@ -452,7 +457,7 @@ def main():
 
     line = {
         "metric": "kNN queries/s", "value": value, "unit": "queries/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
-        "latency": latency,
+        "latency": latency, "per_rank": per_rank,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "KITTI scan bundled with the reference (tests/golden copy)" if args.workload.startswith("kitti") else "synthetic",
         "config": {"workload": args.workload, "desc": w["desc"], "step": "index build + kNN of every point",
