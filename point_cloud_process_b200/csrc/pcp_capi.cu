@@ -104,7 +104,8 @@ int upload(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t byte
 // call synchronises before it returns).  A page-locked source is copied on the side stream, so that the copy
 // overlaps whatever is still queued on the main stream (typically the index build of a pcp_index_rebuild that
 // returned as soon as its own upload was done); the main stream then waits for the copy.
-int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes, bool *on_side = nullptr) {
+int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t bytes, bool *on_side = nullptr,
+                bool main_waits = true) {
     if (on_side) *on_side = false;
     PCP_TRY(dst.ensure(bytes));
     if (bytes == 0) return PCP_OK;
@@ -114,7 +115,7 @@ int upload_side(pcp_ctx *ctx, int pin_slot, DevBuf &dst, const void *src, size_t
     if (!pinned) return upload(ctx, pin_slot, dst, src, bytes);
     PCP_CUDA(cudaMemcpyAsync(dst.p, src, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
     PCP_CUDA(cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
-    PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+    if (main_waits) PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));   // else: the caller orders on ev_copy
     if (on_side) *on_side = true;
     return PCP_OK;
 }
@@ -560,14 +561,25 @@ int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_pairs, c
         return fail(PCP_ERR_INVALID, "pcp_icp_batch: NaN threshold");
     DeviceGuard g(ctx->device);
     const float *d_src = src_xyz, *d_tgt = tgt_xyz;
+    cudaEvent_t src_ready = nullptr;
     if (mem == PCP_HOST) {
-        PCP_TRY(upload(ctx, 0, ctx->scratch[5], src_xyz, sizeof(float) * (size_t)ns * (size_t)stride));
+        // Targets first, on the main stream: their bucket build starts as soon as they are on the device.  The
+        // sources follow on the side stream (page-locked input), behind the target copy and behind whatever the
+        // main stream still runs on the scratch buffer, and the main stream only waits for them before the
+        // source build -- the target build runs beside the second half of the transfer.
         PCP_TRY(upload(ctx, 1, ctx->scratch[6], tgt_xyz, sizeof(float) * (size_t)nt * (size_t)stride));
+        PCP_CUDA(cudaEventRecord(ctx->ev_search_end, ctx->stream));
+        PCP_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_search_end, 0));
+        bool src_side = false;
+        PCP_TRY(upload_side(ctx, 0, ctx->scratch[5], src_xyz, sizeof(float) * (size_t)ns * (size_t)stride, &src_side, false));
+        if (src_side) src_ready = ctx->ev_copy;
         d_src = ctx->scratch[5].as<float>();
         d_tgt = ctx->scratch[6].as<float>();
     }
-    return icp_batch_device(ctx, prm, n_pairs, d_src, src_offsets, d_tgt, tgt_offsets, stride, T_init, T_last, T_total,
-                            iterations, status, diff_log);
+    const int rc = icp_batch_device(ctx, prm, n_pairs, d_src, src_offsets, d_tgt, tgt_offsets, stride, T_init, T_last,
+                                    T_total, iterations, status, diff_log, src_ready);
+    if (rc != PCP_OK && src_ready) cudaStreamSynchronize(ctx->copy_stream);   // the caller's buffer is free on return
+    return rc;
 }
 
 int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, int mem, double *R, double *t, double *cost) {

@@ -715,7 +715,8 @@ int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_
 
 int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const float *d_src, const int64_t *h_src_off,
                      const float *d_tgt, const int64_t *h_tgt_off, int64_t stride, const double *h_T_init,
-                     double *h_T_last, double *h_T_total, int32_t *h_iters, int32_t *h_status, double *h_log) {
+                     double *h_T_last, double *h_T_total, int32_t *h_iters, int32_t *h_status, double *h_log,
+                     cudaEvent_t src_ready) {
     if (P == 0) return PCP_OK;
     if (P > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_icp_batch: too many pairs");
     cudaStream_t st = ctx->stream;
@@ -725,6 +726,7 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
     BatchIndex &tb = ctx->icp_targets;
     tb.ctx = ctx;
     PCP_TRY(batch_build_device(&tb, d_tgt, stride, P, h_tgt_off));
+    if (src_ready) PCP_CUDA(cudaStreamWaitEvent(st, src_ready, 0));   // sources still in flight on the side stream
 
     int64_t max_ns = 0;
     for (int64_t p = 0; p < P; ++p) {

@@ -181,7 +181,7 @@ int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
 int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, const float *d_src,
                      const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,
                      const double *h_T_init, double *h_T_last, double *h_T_total, int32_t *h_iters,
-                     int32_t *h_status, double *h_log);
+                     int32_t *h_status, double *h_log, cudaEvent_t src_ready = nullptr);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,
                       double *h_cost);
