@@ -194,6 +194,31 @@ PCP_API int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_
 PCP_API int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, int mem, double *R, double *t,
                    double *cost);
 
+/* ---- ICP front end: voxel-grid down-sampling and normals -----------------------
+ * pcp_voxel_filter replaces voxel_filter(point_cloud, leaf_size, type)   Pca_and_Voxel_filter/voxel_filter.py:10-66
+ * (the hash-grid precedent for the voxel_down_sample call of Registration/main.py:35), float64 arithmetic on the
+ * float32 rows (the reference is handed Open3D's float64 points), reference quirks kept:
+ *   D = (max - min) // leaf_size per axis (:22-24); h = hx + hy*Dx + hz*Dx*Dy (:29-33, colliding cells merge);
+ *   stable sort by h (:36); one point per run of equal h in ascending h; the LAST run is not emitted (:40-50).
+ * PCP_VOXEL_CENTROID: np.mean of the run in input order, numpy's pairwise summation order -- bit-equal (:48).
+ * PCP_VOXEL_RANDOM:   one point of the run, chosen by a counter hash of (seed, run) -- the reference draws from
+ *                     Python's global random state (:60), so only the run structure is comparable.
+ * Two-phase: pcp_voxel_filter computes into a context-owned device buffer and reports n_out rows;
+ * pcp_voxel_filter_read copies those n_out x 3 float64 rows out (host or device per `mem`). */
+enum pcp_voxel_mode { PCP_VOXEL_CENTROID = 0, PCP_VOXEL_RANDOM = 1 };
+PCP_API int pcp_voxel_filter(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_floats, double leaf_size,
+                             int mode, uint64_t seed, int mem, int64_t *n_out);
+PCP_API int pcp_voxel_filter_read(pcp_ctx *ctx, int mem, double *out_xyz);
+
+/* pcp_normals replaces the per-point loop of Pca_and_Voxel_filter/pca_normal.py:85-90:
+ *   search_knn_vector_3d(p, k) (self included) -> PCA(pc_array[idx, :]) (pca_normal.py:10-36: mean, np.cov with
+ *   1/(k-1), eigh, eigenvalues descending) -> normal = eigenvector of the smallest eigenvalue (v[:, 2]).
+ * The neighbours are the library's exact float32 kNN of the indexed cloud (pcp_knn_self).  normals: n x 3
+ * float64, unit length, sign fixed so that the component of largest magnitude is positive (numpy leaves the
+ * sign to LAPACK); eigenvalues (may be NULL): n x 3 float64, descending.  2 <= k <= PCP_MAX_K (the reference
+ * uses 5).  For an index built with PCP_DEVICE the cloud passed to the build must still be alive. */
+PCP_API int pcp_normals(pcp_index *index, int k, int mem, double *normals, double *eigenvalues);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

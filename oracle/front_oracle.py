@@ -1,0 +1,67 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement of the ICP front end used as the checker by
+tests/, never imported by the product path.
+
+  voxel_filter   restates Pca_and_Voxel_filter/voxel_filter.py:10-66 (type="centroid")
+  pca / normals  restate  Pca_and_Voxel_filter/pca_normal.py:10-36 and the loop at :85-90
+
+Pinned: tests/golden/front_golden.npz holds outputs of the reference's OWN voxel_filter() and PCA() (imported
+from /root/reference with stand-ins for the absent open3d / pyntcloud / matplotlib modules, which those two
+functions never touch) -- tests/golden/make_golden_front.py; tests/test_oracle_golden.py checks this file
+against them.
+"""
+import numpy as np
+
+
+def voxel_filter(points, leaf_size):
+    """voxel_filter.py:10-66, centroid mode, vectorised: same float64 arithmetic, same stable order, np.mean per
+    run (so numpy's own summation order), last run dropped."""
+    pc = np.asarray(points, dtype=np.float64)                       # :19 (Open3D points are float64)
+    mx = np.max(pc, axis=0)                                         # :20
+    mn = np.min(pc, axis=0)                                         # :21
+    Dx = (mx[0] - mn[0]) // leaf_size                               # :22
+    Dy = (mx[1] - mn[1]) // leaf_size                               # :23
+    hx = np.floor((pc[:, 0] - mn[0]) / leaf_size)                   # :29
+    hy = np.floor((pc[:, 1] - mn[1]) / leaf_size)                   # :30
+    hz = np.floor((pc[:, 2] - mn[2]) / leaf_size)                   # :31
+    h = hx + hy * Dx + hz * Dx * Dy                                 # :32
+    order = np.argsort(h, kind="stable")                            # :36 (sorted() is stable)
+    hs = h[order]
+    heads = np.flatnonzero(np.r_[True, hs[1:] != hs[:-1]])
+    ends = np.r_[heads[1:], len(hs)]
+    out = []
+    for s, e in zip(heads[:-1], ends[:-1]):                         # the last run is never appended (:40-50)
+        grp = np.ascontiguousarray(pc[order[s:e]].T)                # np.hstack of (3,1) columns -> (3, g)
+        out.append(np.mean(grp, axis=1))                            # :48
+    return np.array(out, dtype=np.float64)                          # :65
+
+
+def voxel_runs(points, leaf_size):
+    """Sizes of the runs of equal hash, ascending hash, last run included."""
+    pc = np.asarray(points, dtype=np.float64)
+    mx, mn = np.max(pc, axis=0), np.min(pc, axis=0)
+    Dx, Dy = (mx[0] - mn[0]) // leaf_size, (mx[1] - mn[1]) // leaf_size
+    h = (np.floor((pc[:, 0] - mn[0]) / leaf_size) + np.floor((pc[:, 1] - mn[1]) / leaf_size) * Dx
+         + np.floor((pc[:, 2] - mn[2]) / leaf_size) * Dx * Dy)
+    return np.unique(h, return_counts=True)[1]
+
+
+def pca(data):
+    """PCA(data, correlation=False, sort=True) of pca_normal.py:10-36."""
+    pc_array = np.transpose(np.asarray(data, dtype=np.float64))     # :21
+    pc_mean = np.mean(pc_array, axis=1, keepdims=True)              # :23
+    pc_norm = pc_array - pc_mean                                    # :24
+    H = np.cov(pc_norm)                                             # :26
+    w, v = np.linalg.eigh(H)                                        # :28
+    order = w.argsort()[::-1]                                       # :31-33
+    return w[order], v[:, order]
+
+
+def normals(points, nn_idx):
+    """Loop of pca_normal.py:85-90 over given neighbour lists (N, k): normal = v[:, 2]; also the eigenvalues."""
+    pts = np.asarray(points, dtype=np.float64)
+    nrm = np.empty((len(nn_idx), 3))
+    ev = np.empty((len(nn_idx), 3))
+    for i, idx in enumerate(nn_idx):
+        w, v = pca(pts[idx, :])
+        nrm[i], ev[i] = v[:, 2], w
+    return nrm, ev

@@ -147,6 +147,17 @@ class Index {
         rethrow();
         return py::make_tuple(idx, dist, cnt);
     }
+    // normals by k-NN PCA (pca_normal.py:85-90): (normals (N,3) f64, eigenvalues (N,3) f64 descending)
+    py::tuple normals(int k) {
+        const int64_t n = size();
+        auto nrm = result_array<double>({(py::ssize_t)n, (py::ssize_t)3});
+        auto ev = result_array<double>({(py::ssize_t)n, (py::ssize_t)3});
+        check(pcp_normals(ix_, k, PCP_HOST, nrm.mutable_data(), ev.mutable_data()), "pcp_normals");
+        return py::make_tuple(nrm, ev);
+    }
+    void normals_device(int k, uintptr_t nrm, uintptr_t ev) {
+        check(pcp_normals(ix_, k, PCP_DEVICE, reinterpret_cast<double *>(nrm), reinterpret_cast<double *>(ev)), "pcp_normals");
+    }
     // device in / device out (raw pointers), asynchronous on the context stream
     void knn_device(uintptr_t q, int64_t nq, int64_t stride, int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
         check(pcp_knn(ix_, reinterpret_cast<const float *>(q), nq, stride, k, PCP_DEVICE,
@@ -282,6 +293,33 @@ py::tuple procrustes(std::shared_ptr<Context> ctx, const f64_array &A, const f64
     return py::make_tuple(R, t, cost);
 }
 
+// voxel_filter(point_cloud, leaf_size, type) of Pca_and_Voxel_filter/voxel_filter.py:10-66 -> (M, 3) float64
+py::array_t<double> voxel_filter(std::shared_ptr<Context> ctx, const py::object &points, double leaf_size,
+                                 const std::string &type, uint64_t seed) {
+    Cloud c(points, "point_cloud");
+    int mode;
+    if (type == "centroid") mode = PCP_VOXEL_CENTROID;
+    else if (type == "random") mode = PCP_VOXEL_RANDOM;
+    else throw py::value_error("voxel_filter: type must be 'centroid' or 'random'");
+    int64_t m = 0;
+    check(pcp_voxel_filter(ctx->get(), c.data(), c.n, c.stride, leaf_size, mode, seed, PCP_HOST, &m), "pcp_voxel_filter");
+    auto out = result_array<double>({(py::ssize_t)m, (py::ssize_t)3});
+    check(pcp_voxel_filter_read(ctx->get(), PCP_HOST, out.mutable_data()), "pcp_voxel_filter_read");
+    return out;
+}
+
+// device-resident cloud: returns the number of output rows (the rows stay in the context until read)
+int64_t voxel_filter_device(std::shared_ptr<Context> ctx, uintptr_t dptr, int64_t n, int64_t stride, double leaf_size,
+                            int mode, uint64_t seed) {
+    int64_t m = 0;
+    check(pcp_voxel_filter(ctx->get(), reinterpret_cast<const float *>(dptr), n, stride, leaf_size, mode, seed,
+                           PCP_DEVICE, &m), "pcp_voxel_filter");
+    return m;
+}
+void voxel_filter_read_device(std::shared_ptr<Context> ctx, uintptr_t out) {
+    check(pcp_voxel_filter_read(ctx->get(), PCP_DEVICE, reinterpret_cast<double *>(out)), "pcp_voxel_filter_read");
+}
+
 py::array_t<double> homo2tq(const f64_array &homo) {
     if (homo.size() != 16) throw py::value_error("homo2tq: expected a 4x4 matrix");
     py::array_t<double> tq(7);
@@ -323,6 +361,8 @@ PYBIND11_MODULE(_pcp, m) {
         .def("stats", &Index::stats)
         .def("knn", &Index::knn, py::arg("queries"), py::arg("k"))
         .def("knn_self", &Index::knn_self, py::arg("k"))
+        .def("normals", &Index::normals, py::arg("k") = 5)
+        .def("normals_device", &Index::normals_device)
         .def("knn_device", &Index::knn_device)
         .def("knn_self_device", &Index::knn_self_device)
         .def("radius", &Index::radius, py::arg("queries"), py::arg("radius"), py::arg("sorted") = false)
@@ -335,6 +375,10 @@ PYBIND11_MODULE(_pcp, m) {
           py::arg("want_log") = false);
     m.def("icp_batch_device", &icp_batch_device);
     m.def("homo2tq", &homo2tq, py::arg("homo"));
+    m.def("voxel_filter_device", &voxel_filter_device);
+    m.def("voxel_filter_read_device", &voxel_filter_read_device);
+    m.def("voxel_filter", &voxel_filter, py::arg("ctx"), py::arg("point_cloud"), py::arg("leaf_size"),
+          py::arg("type") = "centroid", py::arg("seed") = 0);
     m.def("procrustes", &procrustes, py::arg("ctx"), py::arg("A"), py::arg("B"));
 
 }

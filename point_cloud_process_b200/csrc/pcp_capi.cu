@@ -267,6 +267,9 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     ctx->cub_tmp.release();
     ctx->counters.release();
     ctx->radius_perm.release();
+    ctx->voxel_out.release();
+    ctx->voxel_meta.release();
+    ctx->normals_nn.release();
     ctx->icp_targets.release();
     ctx->icp_sources.release();
     for (auto &b : ctx->scratch) b.release();
@@ -596,6 +599,67 @@ int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, in
     }
     return procrustes_device(ctx, d_A, d_B, n, R, t, cost);
 }
+
+// ---------------------------------------------------------------------------------------------- ICP front end
+
+int pcp_voxel_filter(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride, double leaf_size, int mode,
+                     uint64_t seed, int mem, int64_t *n_out) {
+    if (!ctx || !n_out) return fail(PCP_ERR_INVALID, "pcp_voxel_filter: ctx/n_out is NULL");
+    *n_out = 0;
+    PCP_TRY(check_cloud("pcp_voxel_filter", xyz, n, stride, mem));
+    if (n == 0) return fail(PCP_ERR_INVALID, "pcp_voxel_filter: empty cloud (the reference raises on np.max of an empty array, voxel_filter.py:20)");
+    if (n > 0x7fffffffLL) return fail(PCP_ERR_UNSUPPORTED, "pcp_voxel_filter: more than 2^31-1 points");
+    if (!(leaf_size > 0.0) || !std::isfinite(leaf_size)) return fail(PCP_ERR_INVALID, "pcp_voxel_filter: leaf_size must be finite and > 0");
+    if (mode != PCP_VOXEL_CENTROID && mode != PCP_VOXEL_RANDOM) return fail(PCP_ERR_INVALID, "pcp_voxel_filter: mode must be PCP_VOXEL_CENTROID or PCP_VOXEL_RANDOM");
+    DeviceGuard g(ctx->device);
+    const float *d_xyz = xyz;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 0, ctx->scratch[6], xyz, sizeof(float) * (size_t)n * (size_t)stride));
+        d_xyz = ctx->scratch[6].as<float>();
+    }
+    return voxel_filter_device(ctx, d_xyz, n, stride, leaf_size, mode, seed, n_out);
+}
+
+int pcp_voxel_filter_read(pcp_ctx *ctx, int mem, double *out_xyz) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_voxel_filter_read: ctx is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_voxel_filter_read: mem must be PCP_HOST or PCP_DEVICE");
+    if (ctx->voxel_n_out < 0) return fail(PCP_ERR_INVALID, "pcp_voxel_filter_read: no pcp_voxel_filter result on this context");
+    if (ctx->voxel_n_out == 0) return PCP_OK;
+    if (!out_xyz) return fail(PCP_ERR_INVALID, "pcp_voxel_filter_read: out_xyz is NULL");
+    DeviceGuard g(ctx->device);
+    const size_t bytes = sizeof(double) * 3 * (size_t)ctx->voxel_n_out;
+    PCP_CUDA(cudaMemcpyAsync(out_xyz, ctx->voxel_out.p, bytes, mem == PCP_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, ctx->stream));
+    if (mem == PCP_HOST) PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+int pcp_normals(pcp_index *ix, int k, int mem, double *normals, double *eigenvalues) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_normals: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_normals: mem must be PCP_HOST or PCP_DEVICE");
+    PCP_TRY(check_k(k));
+    if (k < 2) return fail(PCP_ERR_INVALID, "pcp_normals: k must be >= 2 (np.cov of one sample is undefined)");
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    if (!normals) return fail(PCP_ERR_INVALID, "pcp_normals: normals is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    double *d_nrm = normals, *d_ev = eigenvalues;
+    const size_t row = sizeof(double) * 3 * (size_t)n;
+    if (mem == PCP_HOST) {
+        PCP_TRY(ctx->scratch[7].ensure(row * (eigenvalues ? 2 : 1)));
+        d_nrm = ctx->scratch[7].as<double>();
+        d_ev = eigenvalues ? d_nrm + 3 * (size_t)n : nullptr;
+    }
+    PCP_TRY(normals_device(ix, k, d_nrm, d_ev));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, normals, d_nrm, row));
+        if (eigenvalues) PCP_TRY(download(ctx, eigenvalues, d_ev, row));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- pose helpers
 
 // rotmat2quaternion / copysign / homo2tq of main.py:158-180 (host arithmetic, float64)
 int pcp_homo2tq(const double *m, double *tq) {

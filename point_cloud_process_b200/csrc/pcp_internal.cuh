@@ -120,6 +120,10 @@ struct pcp_ctx {
     // follows it (the two-phase API passes the same queries twice): valid while the tag matches
     pcp::DevBuf radius_perm;
     struct { const void *q = nullptr; int64_t nq = 0, stride = 0; const void *ix = nullptr; uint64_t serial = 0; } radius_perm_tag;
+    // ICP front end (pcp_front.cu): result of the last pcp_voxel_filter (read by pcp_voxel_filter_read), its run
+    // count / bounding-box accumulators, and the neighbour lists of pcp_normals
+    pcp::DevBuf voxel_out, voxel_meta, normals_nn;
+    int64_t voxel_n_out = -1;
     bool count_work = false;
     // optional timing of the dominant kernel (pcp_ctx_enable_kernel_timing): event pairs around every
     // knn_tile_kernel launch, summed by pcp_ctx_read_kernel_timing
@@ -182,6 +186,11 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, c
                      const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,
                      const double *h_T_init, double *h_T_last, double *h_T_total, int32_t *h_iters,
                      int32_t *h_status, double *h_log, cudaEvent_t src_ready = nullptr);
+
+// ICP front end (pcp_front.cu)
+int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double leaf, int mode,
+                        unsigned long long seed, int64_t *n_out);
+int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,
                       double *h_cost);

@@ -30,6 +30,11 @@ def icp_golden():
     return np.load(os.path.join(GOLDEN, "icp_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def front_golden():
+    return np.load(os.path.join(GOLDEN, "front_golden.npz"))
+
+
 def golden_cases(g):
     return sorted({k.split("/")[0] for k in g.files})
 

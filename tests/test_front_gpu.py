@@ -1,0 +1,154 @@
+"""GPU: ICP front end through pybind11 -> C ABI -> CUDA against the reference-generated golden
+vectors (tests/golden/front_golden.npz) and the CPU restatement (oracle/front_oracle.py).
+
+Bars: voxel filter centroids BIT-EXACT float64 (integer-valued hash, stable sort, numpy's summation order);
+normals: eigenvalues within 1e-9 relative to the largest one, normal direction within 1e-6 rad up to sign when
+the two smallest eigenvalues are separated (numpy's np.cov goes through BLAS, whose summation order is not
+defined, and eigenvector signs are LAPACK's)."""
+import numpy as np
+import pytest
+
+from oracle import front_oracle, knn_oracle
+
+pytestmark = pytest.mark.gpu
+
+VF_CASES = ("uniform", "dense", "kitti_sub", "flat", "one_voxel")
+
+
+@pytest.fixture(scope="module")
+def pcp():
+    import point_cloud_process_b200 as m
+    return m
+
+
+@pytest.mark.parametrize("name", VF_CASES)
+def test_voxel_filter_golden_bit_exact(pcp, front_golden, name):
+    from point_cloud_process_b200.voxel_filter import voxel_filter
+    g = front_golden
+    out = voxel_filter(g[f"vf_{name}_pts"], float(g[f"vf_{name}_leaf"]), "centroid")
+    assert out.dtype == np.float64 and out.shape == g[f"vf_{name}_out"].shape
+    assert np.array_equal(out, g[f"vf_{name}_out"])
+
+
+@pytest.mark.parametrize("n,box,leaf", [(200_000, (60, 60, 5), 0.5), (100_000, (2, 2, 2), 1.0), (1000, (1, 1, 1), 1e-3),
+                                        (50_000, (3000, 3000, 3000), 0.01)])
+def test_voxel_filter_vs_restatement(pcp, n, box, leaf):
+    """Seeded clouds: many small voxels, few huge runs (> 128 points: pairwise recursion), one point per voxel,
+    and a hash beyond 2^32 (64-bit key path)."""
+    from point_cloud_process_b200.voxel_filter import voxel_filter
+    rng = np.random.default_rng(n)
+    pts = (rng.random((n, 3)) * np.float32(box)).astype(np.float32)
+    out = voxel_filter(pts, leaf, "centroid")
+    ref = front_oracle.voxel_filter(pts, leaf).reshape(-1, 3)
+    assert out.shape == ref.shape
+    assert np.array_equal(out, ref)
+
+
+def test_voxel_filter_kitti_and_strided_rows(pcp, kitti):
+    from point_cloud_process_b200.voxel_filter import voxel_filter
+    ref = front_oracle.voxel_filter(kitti, 0.5).reshape(-1, 3)
+    assert np.array_equal(voxel_filter(kitti, 0.5, "centroid"), ref)
+    rows6 = np.concatenate([kitti, np.ones_like(kitti)], axis=1)          # Oxford xyz + normal rows (main.py:14)
+    assert np.array_equal(pcp.native.voxel_filter(pcp.default_context(), rows6, 0.5, "centroid", 0), ref)
+
+
+def test_voxel_filter_full_size_properties(pcp):
+    """C3 size (1 M points): one row per distinct hash but the last, and the count-weighted sum of the centroids
+    equals the sum over the emitted voxels' points (a checksum of checksums)."""
+    from point_cloud_process_b200.voxel_filter import voxel_filter
+    rng = np.random.default_rng(1234)
+    pts = (rng.random((1_000_000, 3)) * np.float32(25.4)).astype(np.float32)
+    leaf = 0.4
+    out = voxel_filter(pts, leaf, "centroid")
+    runs = front_oracle.voxel_runs(pts, leaf)
+    assert len(out) == len(runs) - 1
+    pc = pts.astype(np.float64)
+    mn, mx = pc.min(0), pc.max(0)
+    Dx, Dy = (mx[0] - mn[0]) // leaf, (mx[1] - mn[1]) // leaf
+    hfun = lambda p: (np.floor((p[:, 0] - mn[0]) / leaf) + np.floor((p[:, 1] - mn[1]) / leaf) * Dx
+                      + np.floor((p[:, 2] - mn[2]) / leaf) * Dx * Dy)
+    h = hfun(pc)
+    keep = h != h.max()
+    total = (out * runs[:-1, None]).sum(0)
+    assert np.allclose(total, pc[keep].sum(0), rtol=1e-12)
+
+
+def test_voxel_filter_random_mode_and_errors(pcp):
+    from point_cloud_process_b200.voxel_filter import voxel_filter
+    rng = np.random.default_rng(7)
+    pts = (rng.random((20_000, 3)) * np.float32([10, 10, 2])).astype(np.float32)
+    cen = voxel_filter(pts, 0.5, "centroid")
+    a = voxel_filter(pts, 0.5, "random", seed=1)
+    b = voxel_filter(pts, 0.5, "random", seed=1)
+    c = voxel_filter(pts, 0.5, "random", seed=2)
+    assert a.shape == cen.shape and np.array_equal(a, b) and not np.array_equal(a, c)
+    members = {tuple(r) for r in pts.astype(np.float64)}
+    assert all(tuple(r) in members for r in a)               # every pick is a point of the cloud ...
+    pc = pts.astype(np.float64)
+    mn, mx = pc.min(0), pc.max(0)
+    Dx, Dy = (mx[0] - mn[0]) // 0.5, (mx[1] - mn[1]) // 0.5
+    hfun = lambda p: (np.floor((p[:, 0] - mn[0]) / 0.5) + np.floor((p[:, 1] - mn[1]) / 0.5) * Dx
+                      + np.floor((p[:, 2] - mn[2]) / 0.5) * Dx * Dy)
+    assert np.array_equal(hfun(a), np.unique(hfun(pc))[:-1])  # ... of the right run, in ascending hash order
+    with pytest.raises(ValueError):
+        voxel_filter(np.zeros((0, 3), np.float32), 0.5, "centroid")
+    with pytest.raises(ValueError):
+        voxel_filter(pts, 0.0, "centroid")
+    with pytest.raises(ValueError):
+        voxel_filter(pts, 0.5, "median")
+
+
+def _check_normals(nrm, ev, ref_n, ref_w):
+    scale = ref_w[:, :1]
+    assert np.all(np.abs(ev - ref_w) <= 1e-9 * scale + 1e-300)
+    assert np.allclose(np.linalg.norm(nrm, axis=1), 1.0, atol=1e-12)
+    lead = nrm[np.arange(len(nrm)), np.abs(nrm).argmax(1)]
+    assert np.all(lead > 0)                                   # the documented sign convention
+    gap = (ref_w[:, 1] - ref_w[:, 2]) / ref_w[:, 0]
+    ok = gap > 1e-6
+    assert ok.mean() > 0.95
+    cosang = np.abs(np.sum(nrm * ref_n, axis=1))[ok]
+    # angle error ~ eps / gap
+    assert np.all(1.0 - cosang <= 1e-12 + 1e-18 / gap[ok] ** 2)
+
+
+@pytest.mark.parametrize("k", (5, 8, 16))
+def test_normals_vs_restatement(pcp, kitti, k):
+    """pca_normal.py:85-90 on a 30k-point part of the scan; the neighbour lists are the library's exact kNN
+    (checked against the kd-tree restatement on a sample here, exhaustively in test_knn_gpu.py)."""
+    from point_cloud_process_b200.pca_normal import estimate_normals
+    pts = kitti[:30_000]
+    ix = pcp.SearchIndex(pts)
+    idx, dist, cnt = ix.knn_self(k)
+    o_dist, o_idx, _ = knn_oracle.bruteforce_knn(pts, pts[:2000], k, threads=8)
+    assert np.array_equal(idx[:2000], o_idx.astype(np.int32))
+    nrm, ev = estimate_normals(pts, k=k, index=ix, return_eigenvalues=True)
+    sel = np.random.default_rng(k).choice(len(pts), 4000, replace=False)
+    ref_n, ref_w = front_oracle.normals(pts, idx[sel])
+    _check_normals(nrm[sel], ev[sel], ref_n, ref_w)
+
+
+@pytest.mark.parametrize("k", (5, 12, 30))
+def test_normals_golden_pca(pcp, front_golden, k):
+    """A cloud of exactly k points: every neighbourhood is the whole cloud, so every row must reproduce the
+    reference's PCA(data) (pca_normal.py:10-36) of that cloud."""
+    from point_cloud_process_b200.pca_normal import estimate_normals
+    g = front_golden
+    data = g[f"pca_{k}_data"]
+    nrm, ev = estimate_normals(data, k=k, return_eigenvalues=True)
+    w, v = g[f"pca_{k}_w"], g[f"pca_{k}_v"]
+    assert np.all(np.abs(ev - w[None]) <= 1e-9 * w[0])
+    assert np.all(1.0 - np.abs(nrm @ v[:, 2]) <= 1e-10)
+
+
+def test_normals_plane_and_errors(pcp):
+    rng = np.random.default_rng(3)
+    xy = rng.random((5000, 2)).astype(np.float32) * 10
+    n_true = np.array([0.3, -0.2, 0.933]); n_true /= np.linalg.norm(n_true)
+    z = -(xy @ n_true[:2]) / n_true[2]
+    pts = np.c_[xy, z].astype(np.float32)
+    from point_cloud_process_b200.pca_normal import estimate_normals
+    nrm = estimate_normals(pts, k=10)
+    assert np.all(np.abs(nrm @ n_true) > 1 - 1e-6)
+    with pytest.raises(ValueError):
+        estimate_normals(pts, k=1)

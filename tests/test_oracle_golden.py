@@ -138,3 +138,32 @@ def test_mode_a_iteration_histogram():
         _, info = icp_oracle.icp_point2point(src, tgt, np.eye(4), return_info=True)
         its.append(info["iterations"])
     assert set(its) <= {1, 2, 3}
+
+
+# ---- ICP front end: tests/golden/front_golden.npz <- the reference's own voxel_filter() / PCA()
+
+VF_CASES = ("uniform", "dense", "kitti_sub", "flat", "one_voxel")
+
+
+@pytest.mark.parametrize("name", VF_CASES)
+def test_voxel_filter_restatement_matches_reference(front_golden, name):
+    from oracle import front_oracle
+    g = front_golden
+    out = front_oracle.voxel_filter(g[f"vf_{name}_pts"], float(g[f"vf_{name}_leaf"])).reshape(-1, 3)
+    assert np.array_equal(out, g[f"vf_{name}_out"])        # bit-exact float64
+    runs = front_oracle.voxel_runs(g[f"vf_{name}_pts"], float(g[f"vf_{name}_leaf"]))
+    assert len(out) == len(runs) - 1                       # the reference drops the last voxel (voxel_filter.py:40-50)
+
+
+def test_voxel_filter_golden_covers_long_runs(front_golden):
+    from oracle import front_oracle
+    runs = front_oracle.voxel_runs(front_golden["vf_dense_pts"], float(front_golden["vf_dense_leaf"]))
+    assert runs.max() > 128      # numpy's pairwise recursion (blocks of 128) is exercised
+
+
+@pytest.mark.parametrize("k", (5, 12, 30))
+def test_pca_restatement_matches_reference(front_golden, k):
+    from oracle import front_oracle
+    g = front_golden
+    w, v = front_oracle.pca(g[f"pca_{k}_data"])
+    assert np.array_equal(w, g[f"pca_{k}_w"]) and np.array_equal(v, g[f"pca_{k}_v"])
