@@ -28,7 +28,8 @@ def declared_symbols():
 def test_header_declares_the_documented_surface():
     syms = declared_symbols()
     for s in ("pcp_ctx_create", "pcp_index_build", "pcp_knn", "pcp_knn_self", "pcp_radius_count", "pcp_radius_fill",
-              "pcp_icp_batch", "pcp_procrustes", "pcp_homo2tq", "pcp_last_error"):
+              "pcp_icp_batch", "pcp_procrustes", "pcp_homo2tq", "pcp_last_error", "pcp_voxel_filter",
+              "pcp_voxel_filter_read", "pcp_normals"):
         assert s in syms
 
 
@@ -147,3 +148,37 @@ def test_reg_result_writer_format(tmp_path):
     assert text.splitlines()[0] == "# idx1,idx2,t_x,t_y,t_z,q_w,q_x,q_y,q_z"
     assert text.splitlines()[1] == "643,456,1.500000,-2.250000,0.125000,0.543700,0.100000,-0.200000,0.800000"
     assert icp.read_pair_list(p) == [(643, 456), (0, 456)]
+
+
+def test_evaluate_rt_matches_reference(tmp_path):
+    """the evaluator mirror against outputs of the reference's own evaluate_rt.py on the two
+    reg_result.txt files it ships (tests/golden/eval_golden.npz <- tests/golden/make_golden_eval.py); the files
+    are re-written through this package's writer (main.py:220-222 format) first."""
+    from point_cloud_process_b200 import evaluate_rt as ev
+    from point_cloud_process_b200.icp import write_reg_result
+    g = np.load(os.path.join(ROOT, "tests", "golden", "eval_golden.npz"))
+    a, b = str(tmp_path / "a.txt"), str(tmp_path / "b.txt")
+    write_reg_result(g["rows_a"], a)
+    write_reg_result(g["rows_b"], b)
+    assert open(a).readline().rstrip("\n") == str(g["header_a"])          # numpy's "# " prefix, as shipped
+    for (x, y), key in (((a, b), "eval_ab"), ((b, a), "eval_ba"), ((a, a), "eval_aa")):
+        got = np.array(ev.evaluate_rt(x, y))
+        assert np.allclose(got, g[key], rtol=1e-12, atol=1e-15), (key, got, g[key])
+    ra, rb = ev.read_reg_results(a), ev.read_reg_results(b)
+    assert len(ra) == 343 and ra[1][0] == "643"
+    for i in range(1, 40):
+        _, _, ta, qa = ev.reg_result_row_to_array(ra[i])
+        _, _, tb, qb = ev.reg_result_row_to_array(rb[i])
+        d = ev.get_P_diff(ev.get_P_from_Rt(qa.as_matrix(), ta), ev.get_P_from_Rt(qb.as_matrix(), tb))
+        assert np.allclose(d, g["p_diff_first39"][i - 1], rtol=1e-12, atol=1e-15)
+    with pytest.raises(AssertionError):
+        open(b, "a").write("1,2,0,0,0,1,0,0,0\n")
+        ev.evaluate_rt(a, b)
+
+
+def test_front_end_modules_mirror_reference_names():
+    from point_cloud_process_b200 import evaluate_rt, pca_normal, voxel_filter
+    assert callable(voxel_filter.voxel_filter) and callable(pca_normal.estimate_normals)
+    for name in ("get_P_from_Rt", "is_registration_successful", "get_P_diff", "read_oxford_bin", "read_reg_results",
+                 "reg_result_row_to_array", "evaluate_rt"):
+        assert hasattr(evaluate_rt, name)
