@@ -219,6 +219,14 @@ PCP_API int pcp_voxel_filter_read(pcp_ctx *ctx, int mem, double *out_xyz);
  * uses 5).  For an index built with PCP_DEVICE the cloud passed to the build must still be alive. */
 PCP_API int pcp_normals(pcp_index *index, int k, int mem, double *normals, double *eigenvalues);
 
+/* pcp_pca replaces PCA(data, correlation=False, sort=True) of pca_normal.py:10-36 on a whole cloud: mean, centred
+ * covariance with 1/(n-1) (np.cov), symmetric eigen-decomposition (np.linalg.eigh), all float64 on the device.
+ * eigenvalues: 3 doubles DESCENDING (the sort=True order, pca_normal.py:30-33); eigenvectors: 9 doubles, row-major
+ * 3x3 whose COLUMN j belongs to eigenvalues[j], sign: component of largest magnitude positive.  Outputs are host
+ * memory.  n >= 2. */
+PCP_API int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_floats, int mem, double *eigenvalues,
+                    double *eigenvectors);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

@@ -308,6 +308,19 @@ py::array_t<double> voxel_filter(std::shared_ptr<Context> ctx, const py::object 
     return out;
 }
 
+// PCA(data) of pca_normal.py:10-36 -> (eigenvalues (3,) descending, eigenvectors (3,3) columns)
+py::tuple pca(std::shared_ptr<Context> ctx, const py::object &points) {
+    Cloud c(points, "data");
+    py::array_t<double> w(3), v({(py::ssize_t)3, (py::ssize_t)3});
+    check(pcp_pca(ctx->get(), c.data(), c.n, c.stride, PCP_HOST, w.mutable_data(), v.mutable_data()), "pcp_pca");
+    return py::make_tuple(w, v);
+}
+py::tuple pca_device(std::shared_ptr<Context> ctx, uintptr_t dptr, int64_t n, int64_t stride) {
+    py::array_t<double> w(3), v({(py::ssize_t)3, (py::ssize_t)3});
+    check(pcp_pca(ctx->get(), reinterpret_cast<const float *>(dptr), n, stride, PCP_DEVICE, w.mutable_data(), v.mutable_data()), "pcp_pca");
+    return py::make_tuple(w, v);
+}
+
 // device-resident cloud: returns the number of output rows (the rows stay in the context until read)
 int64_t voxel_filter_device(std::shared_ptr<Context> ctx, uintptr_t dptr, int64_t n, int64_t stride, double leaf_size,
                             int mode, uint64_t seed) {
@@ -375,6 +388,8 @@ PYBIND11_MODULE(_pcp, m) {
           py::arg("want_log") = false);
     m.def("icp_batch_device", &icp_batch_device);
     m.def("homo2tq", &homo2tq, py::arg("homo"));
+    m.def("pca", &pca, py::arg("ctx"), py::arg("data"));
+    m.def("pca_device", &pca_device);
     m.def("voxel_filter_device", &voxel_filter_device);
     m.def("voxel_filter_read_device", &voxel_filter_read_device);
     m.def("voxel_filter", &voxel_filter, py::arg("ctx"), py::arg("point_cloud"), py::arg("leaf_size"),

@@ -659,6 +659,19 @@ int pcp_normals(pcp_index *ix, int k, int mem, double *normals, double *eigenval
     return PCP_OK;
 }
 
+int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride, int mem, double *eigenvalues, double *eigenvectors) {
+    if (!ctx || !eigenvalues || !eigenvectors) return fail(PCP_ERR_INVALID, "pcp_pca: ctx/eigenvalues/eigenvectors is NULL");
+    PCP_TRY(check_cloud("pcp_pca", xyz, n, stride, mem));
+    if (n < 2) return fail(PCP_ERR_INVALID, "pcp_pca: at least 2 points are needed (np.cov divides by n - 1)");
+    DeviceGuard g(ctx->device);
+    const float *d_xyz = xyz;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 0, ctx->scratch[6], xyz, sizeof(float) * (size_t)n * (size_t)stride));
+        d_xyz = ctx->scratch[6].as<float>();
+    }
+    return pca_device(ctx, d_xyz, n, stride, eigenvalues, eigenvectors);
+}
+
 // ---------------------------------------------------------------------------------------------- pose helpers
 
 // rotmat2quaternion / copysign / homo2tq of main.py:158-180 (host arithmetic, float64)

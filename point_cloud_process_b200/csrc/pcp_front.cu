@@ -494,4 +494,135 @@ int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals) {
     return PCP_OK;
 }
 
+// ================================================================================================ whole-cloud PCA
+// PCA(data, correlation=False, sort=True) of pca_normal.py:10-36 on a whole cloud: mean, centred covariance with
+// 1/(n-1), symmetric eigen-decomposition -- two deterministic reduction passes in float64 (per-thread partial sums
+// over a grid-stride loop, warp shuffle, shared memory, fixed-order final sum in one CTA), 12 B/point each.
+
+namespace {
+
+constexpr int kPcaThreads = 256;
+
+template <int NV>
+__device__ __forceinline__ void block_sum_store(double (&v)[NV], double *__restrict__ partial) {
+    __shared__ double sh[kPcaThreads / 32][NV];
+#pragma unroll
+    for (int a = 0; a < NV; ++a)
+#pragma unroll
+        for (int m = 16; m > 0; m >>= 1) v[a] += __shfl_xor_sync(0xffffffffu, v[a], m);
+    if ((threadIdx.x & 31) == 0)
+#pragma unroll
+        for (int a = 0; a < NV; ++a) sh[threadIdx.x >> 5][a] = v[a];
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        double t = 0.0;
+        for (int w = 0; w < kPcaThreads / 32; ++w) t += sh[w][threadIdx.x];
+        partial[blockIdx.x * NV + threadIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(kPcaThreads) pca_sum_kernel(const float *__restrict__ xyz, long long n, long long stride,
+                                                              double *__restrict__ partial) {
+    double v[3] = {0.0, 0.0, 0.0};
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float *p = xyz + i * stride;
+        v[0] += (double)p[0];
+        v[1] += (double)p[1];
+        v[2] += (double)p[2];
+    }
+    block_sum_store<3>(v, partial);
+}
+
+// fixed-order sum of the per-CTA partials by one CTA: thread t takes CTAs t, t+256, ...; shared-memory tree
+template <int NV>
+__device__ __forceinline__ void final_sum(const double *__restrict__ partial, int blocks, double (&tot)[NV]) {
+    __shared__ double sh[kPcaThreads][NV];
+    double v[NV];
+#pragma unroll
+    for (int a = 0; a < NV; ++a) v[a] = 0.0;
+    for (int b = threadIdx.x; b < blocks; b += kPcaThreads)
+#pragma unroll
+        for (int a = 0; a < NV; ++a) v[a] += partial[b * NV + a];
+#pragma unroll
+    for (int a = 0; a < NV; ++a) sh[threadIdx.x][a] = v[a];
+    __syncthreads();
+    for (int h = kPcaThreads / 2; h > 0; h >>= 1) {
+        if (threadIdx.x < h)
+#pragma unroll
+            for (int a = 0; a < NV; ++a) sh[threadIdx.x][a] += sh[threadIdx.x + h][a];
+        __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < NV; ++a) tot[a] = sh[0][a];
+}
+
+__global__ void __launch_bounds__(kPcaThreads) pca_mean_kernel(const double *__restrict__ partial, int blocks, long long n,
+                                                               double *__restrict__ mean) {
+    double tot[3];
+    final_sum<3>(partial, blocks, tot);
+    if (threadIdx.x < 3) mean[threadIdx.x] = tot[threadIdx.x] / (double)n;
+}
+
+__global__ void __launch_bounds__(kPcaThreads) pca_cov_kernel(const float *__restrict__ xyz, long long n, long long stride,
+                                                              const double *__restrict__ mean, double *__restrict__ partial) {
+    const double mx = mean[0], my = mean[1], mz = mean[2];
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float *p = xyz + i * stride;
+        const double x = (double)p[0] - mx, y = (double)p[1] - my, z = (double)p[2] - mz;
+        v[0] += x * x; v[1] += x * y; v[2] += x * z;
+        v[3] += y * y; v[4] += y * z; v[5] += z * z;
+    }
+    block_sum_store<6>(v, partial);
+}
+
+// out[0..2] eigenvalues descending, out[3..11] eigenvectors as columns (row-major 3x3) in the same order, each
+// with its component of largest magnitude positive
+__global__ void __launch_bounds__(kPcaThreads) pca_solve_kernel(const double *__restrict__ partial, int blocks, long long n,
+                                                                double *__restrict__ out) {
+    double c[6];
+    final_sum<6>(partial, blocks, c);
+    if (threadIdx.x != 0) return;
+    for (int a = 0; a < 6; ++a) c[a] *= 1.0 / (double)(n - 1);   // np.cov: c *= np.true_divide(1, n - 1)
+    double w[3], V[9];
+    sym_eig3(c[0], c[1], c[2], c[3], c[4], c[5], w, V);
+    int o[3] = {0, 1, 2}, t;
+    if (w[o[0]] < w[o[1]]) { t = o[0]; o[0] = o[1]; o[1] = t; }
+    if (w[o[1]] < w[o[2]]) { t = o[1]; o[1] = o[2]; o[2] = t; }
+    if (w[o[0]] < w[o[1]]) { t = o[0]; o[0] = o[1]; o[1] = t; }
+    for (int j = 0; j < 3; ++j) {
+        out[j] = w[o[j]];
+        double x = V[0 * 3 + o[j]], y = V[1 * 3 + o[j]], z = V[2 * 3 + o[j]];
+        const double ax = fabs(x), ay = fabs(y), az = fabs(z);
+        const double lead = ax >= ay && ax >= az ? x : (ay >= az ? y : z);
+        const double sgn = lead < 0.0 ? -1.0 : 1.0;
+        out[3 + 0 * 3 + j] = sgn * x;
+        out[3 + 1 * 3 + j] = sgn * y;
+        out[3 + 2 * 3 + j] = sgn * z;
+    }
+}
+
+}  // namespace
+
+int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double *h_w, double *h_V) {
+    cudaStream_t st = ctx->stream;
+    int blocks = (int)((n + kPcaThreads - 1) / kPcaThreads);
+    if (blocks > ctx->sm_count * 8) blocks = ctx->sm_count * 8;
+    PCP_TRY(ctx->scratch[0].ensure(sizeof(double) * ((size_t)blocks * 6 + 16)));
+    double *partial = ctx->scratch[0].as<double>();
+    double *mean = partial + (size_t)blocks * 6, *out = mean + 3;
+    pca_sum_kernel<<<blocks, kPcaThreads, 0, st>>>(d_xyz, n, stride, partial);
+    pca_mean_kernel<<<1, kPcaThreads, 0, st>>>(partial, blocks, n, mean);
+    pca_cov_kernel<<<blocks, kPcaThreads, 0, st>>>(d_xyz, n, stride, mean, partial);
+    pca_solve_kernel<<<1, kPcaThreads, 0, st>>>(partial, blocks, n, out);
+    PCP_CUDA(cudaGetLastError());
+    ctx->launches += 4;
+    double h[12];
+    PCP_CUDA(cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaStreamSynchronize(st));
+    for (int i = 0; i < 3; ++i) h_w[i] = h[i];
+    for (int i = 0; i < 9; ++i) h_V[i] = h[3 + i];
+    return PCP_OK;
+}
+
 }  // namespace pcp

@@ -191,6 +191,7 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, c
 int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double leaf, int mode,
                         unsigned long long seed, int64_t *n_out);
 int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals);
+int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double *h_w, double *h_V);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,
                       double *h_cost);

@@ -9,7 +9,19 @@ of largest magnitude is positive.
 """
 import numpy as np
 
-from .api import SearchIndex
+from . import native
+from .api import SearchIndex, default_context
+
+
+def PCA(data, correlation=False, sort=True, device=0, ctx=None):
+    """PCA(data, correlation=False, sort=True) of pca_normal.py:10-36 on the GPU (pcp_pca): data (N, 3) ->
+    (eigenvalues (3,), eigenvectors (3, 3) as columns).  `correlation` is accepted and unused, as in the
+    reference (:10,26); sort=False gives np.linalg.eigh's ascending order (:28)."""
+    pts = np.asarray(getattr(data, "points", data))
+    if pts.ndim != 2 or pts.shape[1] < 3:
+        raise ValueError(f"data: expected (N, 3) rows, got shape {pts.shape}")
+    w, v = native.pca(ctx or default_context(device), np.ascontiguousarray(pts[:, :3], dtype=np.float32))
+    return (w, v) if sort else (w[::-1].copy(), v[:, ::-1].copy())
 
 
 def estimate_normals(points, k=5, device=0, ctx=None, index=None, return_eigenvalues=False):

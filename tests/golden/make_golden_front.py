@@ -50,6 +50,11 @@ def main():
         out[f"pca_{k}_data"] = data
         out[f"pca_{k}_w"] = w
         out[f"pca_{k}_v"] = v
+    # whole-cloud PCA (pca_normal.py:69): the voxel-filter clouds again
+    for name in ("uniform", "kitti_sub", "flat"):
+        w, v = ref_pca.PCA(cases[name][0].astype(np.float64))
+        out[f"pca_cloud_{name}_w"] = w
+        out[f"pca_cloud_{name}_v"] = v
     np.savez_compressed(os.path.join(HERE, "front_golden.npz"), **out)
     print({k: v.shape for k, v in out.items()})
 

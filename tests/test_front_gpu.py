@@ -152,3 +152,37 @@ def test_normals_plane_and_errors(pcp):
     assert np.all(np.abs(nrm @ n_true) > 1 - 1e-6)
     with pytest.raises(ValueError):
         estimate_normals(pts, k=1)
+
+
+@pytest.mark.parametrize("name", ("uniform", "kitti_sub", "flat"))
+def test_whole_cloud_pca_golden(pcp, front_golden, name):
+    """PCA(data) of pca_normal.py:10-36 on a whole cloud against the reference's own output: eigenvalues within
+    1e-12 of the largest one (np.cov sums through BLAS, order undefined), eigenvectors up to sign."""
+    from point_cloud_process_b200.pca_normal import PCA
+    g = front_golden
+    pts = g[f"vf_{name}_pts"]
+    w, v = PCA(pts)
+    rw, rv = g[f"pca_cloud_{name}_w"], g[f"pca_cloud_{name}_v"]
+    assert np.all(np.abs(w - rw) <= 1e-12 * rw[0])
+    assert np.all(np.diff(w) <= 0)
+    for j in range(3):
+        gap = min(abs(rw[j] - rw[i]) for i in range(3) if i != j) / rw[0]
+        if gap > 1e-6:
+            assert 1.0 - abs(v[:, j] @ rv[:, j]) <= 1e-12 / gap
+    w2, v2 = PCA(pts, sort=False)
+    assert np.array_equal(w2, w[::-1]) and np.array_equal(v2, v[:, ::-1])
+    with pytest.raises(ValueError):
+        PCA(pts[:1])
+
+
+def test_whole_cloud_pca_large_is_deterministic(pcp):
+    from point_cloud_process_b200.pca_normal import PCA
+    rng = np.random.default_rng(11)
+    pts = (rng.normal(size=(2_000_000, 3)) * np.float32([5, 2, 0.5]) + np.float32([100, -50, 3])).astype(np.float32)
+    w, v = PCA(pts)
+    w2, v2 = PCA(pts)
+    assert np.array_equal(w, w2) and np.array_equal(v, v2)       # fixed-order reductions
+    H = np.cov(pts.astype(np.float64).T)
+    rw = np.linalg.eigvalsh(H)[::-1]
+    assert np.allclose(w, rw, rtol=1e-10)
+    assert np.allclose(np.abs(np.diag(v)), 1.0, atol=1e-2)        # axes of the anisotropic Gaussian

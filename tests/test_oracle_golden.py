@@ -167,3 +167,11 @@ def test_pca_restatement_matches_reference(front_golden, k):
     g = front_golden
     w, v = front_oracle.pca(g[f"pca_{k}_data"])
     assert np.array_equal(w, g[f"pca_{k}_w"]) and np.array_equal(v, g[f"pca_{k}_v"])
+
+
+@pytest.mark.parametrize("name", ("uniform", "kitti_sub", "flat"))
+def test_whole_cloud_pca_restatement_matches_reference(front_golden, name):
+    from oracle import front_oracle
+    g = front_golden
+    w, v = front_oracle.pca(g[f"vf_{name}_pts"])
+    assert np.array_equal(w, g[f"pca_cloud_{name}_w"]) and np.array_equal(v, g[f"pca_cloud_{name}_v"])

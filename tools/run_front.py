@@ -59,6 +59,10 @@ def main():
             r["cpu_restatement_ms_1core"] = cpu * 1e3
             r["bit_exact_vs_restatement"] = bool(np.array_equal(out.cpu().numpy(), ref.reshape(-1, 3)))
         res.append(r)
+        ms = wall(ctx, lambda: native.pca_device(ctx, d.data_ptr(), n, 3))
+        res.append({"op": "whole-cloud PCA (pcp_pca)", "cloud": name, "points": n, "ms": ms, "algorithmic_bytes": 24 * n,
+                    "achieved_gbs": 24 * n / (ms * 1e-3) / 1e9, "hbm_frac": 24 * n / (ms * 1e-3) / 1e9 / peak,
+                    "timer": "host perf_counter around the call (4 launches + the 96-byte result read back)"})
         del d
     for name, pts, k in (("KITTI 000000.bin", kitti, 5), ("uniform 1M in [0,25.4)^3", uni, 5), ("uniform 1M in [0,25.4)^3", uni, 16)):
         n = len(pts)
