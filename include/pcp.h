@@ -227,6 +227,19 @@ PCP_API int pcp_normals(pcp_index *index, int k, int mem, double *normals, doubl
 PCP_API int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_floats, int mem, double *eigenvalues,
                     double *eigenvectors);
 
+/* ---- ISS keypoints on the radius search --------------------------------------------
+ * pcp_iss_keypoints replaces the detection loop of Keypoint_detection_ISS/ISS.py:40-73 over the indexed cloud:
+ * weights 1/|ball(p_j, radius)| (:49), weighted scatter matrix of the radius neighbourhood (:43-51, float64),
+ * eigenvalues descending, candidate iff l2/l1 < lambda21 and l3/l2 < lambda32 (:52-57), non-maximum suppression
+ * with non_max_radius in descending l3 (ties: ascending index), stopping once MORE than iss_count keypoints are
+ * kept (:59-73; so at most iss_count + 1 indices are written -- size `keypoints` accordingly).
+ * Neighbourhoods are the library's radius search (float32 distance <= radius, result_set.py:80); the reference
+ * uses scipy's cKDTree in float64, which can differ only for pairs within one float32 ulp of the radius.
+ * keypoints / n_keypoints: host memory; lambda3 (host, may be NULL): n doubles, l3 of every candidate, NaN elsewhere.
+ * For an index built with PCP_DEVICE the cloud passed to the build must still be alive. */
+PCP_API int pcp_iss_keypoints(pcp_index *index, float radius, double lambda21, double lambda32, float non_max_radius,
+                              int iss_count, int32_t *keypoints, int32_t *n_keypoints, double *lambda3);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

@@ -65,3 +65,44 @@ def normals(points, nn_idx):
         w, v = pca(pts[idx, :])
         nrm[i], ev[i] = v[:, 2], w
     return nrm, ev
+
+
+def iss_keypoints(points, radius=0.5, lambda21=0.5, lambda32=0.5, non_max_radius=0.5, iss_count=20):
+    """The detection loop of Keypoint_detection_ISS/ISS.py:36-73 as a function (the reference keeps it under
+    __main__): -> (iss_idx list, cand_idx list, {index: lambda3}).  Pinned by tests/golden/iss_golden.npz, which
+    holds the variables of the reference script itself after it was executed on the same clouds
+    (tests/golden/make_golden_iss.py)."""
+    from scipy import spatial
+    pts = np.asarray(points, dtype=np.float64)[:, :3]
+    tree = spatial.cKDTree(pts)                                           # :36
+    balls = tree.query_ball_point(pts, radius)
+    counts = np.array([len(b) for b in balls], dtype=np.float64)
+    cand_idx, lambda3 = [], {}
+    for i in range(len(pts)):                                             # :41
+        nb = np.asarray(balls[i])
+        w = 1.0 / counts[nb]                                              # :49
+        d = pts[nb] - pts[i]
+        nume = np.zeros((3, 3))
+        for wj, dj in zip(w, d):                                          # :48-51 (same accumulation order)
+            nume += wj * np.outer(dj, dj)
+        denom = 0
+        for wj in w:
+            denom += wj
+        with np.errstate(invalid="ignore", divide="ignore"):
+            value, _ = np.linalg.eig(nume / denom)                        # :52
+            s = np.sort(value)[::-1]                                      # :53
+            if s[1] / s[0] < lambda21 and s[2] / s[1] < lambda32:         # :55
+                cand_idx.append(i)
+                lambda3[i] = s[2]
+    all_l3 = dict(lambda3)
+    order = dict(sorted(lambda3.items(), key=lambda x: x[1], reverse=True))   # :59
+    iss_idx = []
+    for idx in order:                                                     # :61-73
+        if idx not in lambda3:
+            continue
+        iss_idx.append(idx)
+        for j in tree.query_ball_point(pts[idx], non_max_radius):
+            lambda3.pop(j, None)
+        if len(iss_idx) > iss_count:
+            break
+    return iss_idx, cand_idx, all_l3

@@ -155,6 +155,18 @@ class Index {
         check(pcp_normals(ix_, k, PCP_HOST, nrm.mutable_data(), ev.mutable_data()), "pcp_normals");
         return py::make_tuple(nrm, ev);
     }
+    // ISS.py:40-73 -> (keypoint indices in selection order, lambda3 (N,) with NaN for non-candidates)
+    py::tuple iss_keypoints(float radius, double lambda21, double lambda32, float non_max_radius, int iss_count) {
+        if (iss_count < 0) throw py::value_error("iss_count must be >= 0");
+        std::vector<int32_t> kp((size_t)iss_count + 1);
+        int32_t nk = 0;
+        auto l3 = result_array<double>({(py::ssize_t)size()});
+        check(pcp_iss_keypoints(ix_, radius, lambda21, lambda32, non_max_radius, iss_count, kp.data(), &nk, l3.mutable_data()),
+              "pcp_iss_keypoints");
+        py::array_t<int32_t> out(nk);
+        std::copy(kp.begin(), kp.begin() + nk, out.mutable_data());
+        return py::make_tuple(out, l3);
+    }
     void normals_device(int k, uintptr_t nrm, uintptr_t ev) {
         check(pcp_normals(ix_, k, PCP_DEVICE, reinterpret_cast<double *>(nrm), reinterpret_cast<double *>(ev)), "pcp_normals");
     }
@@ -376,6 +388,8 @@ PYBIND11_MODULE(_pcp, m) {
         .def("knn_self", &Index::knn_self, py::arg("k"))
         .def("normals", &Index::normals, py::arg("k") = 5)
         .def("normals_device", &Index::normals_device)
+        .def("iss_keypoints", &Index::iss_keypoints, py::arg("radius") = 0.5f, py::arg("lambda21") = 0.5,
+             py::arg("lambda32") = 0.5, py::arg("non_max_radius") = 0.5f, py::arg("iss_count") = 20)
         .def("knn_device", &Index::knn_device)
         .def("knn_self_device", &Index::knn_self_device)
         .def("radius", &Index::radius, py::arg("queries"), py::arg("radius"), py::arg("sorted") = false)

@@ -270,6 +270,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     ctx->voxel_out.release();
     ctx->voxel_meta.release();
     ctx->normals_nn.release();
+    for (auto &b : ctx->iss_buf) b.release();
     ctx->icp_targets.release();
     ctx->icp_sources.release();
     for (auto &b : ctx->scratch) b.release();
@@ -670,6 +671,30 @@ int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride, int mem, 
         d_xyz = ctx->scratch[6].as<float>();
     }
     return pca_device(ctx, d_xyz, n, stride, eigenvalues, eigenvectors);
+}
+
+int pcp_iss_keypoints(pcp_index *ix, float radius, double lambda21, double lambda32, float non_max_radius, int iss_count,
+                      int32_t *keypoints, int32_t *n_keypoints, double *lambda3) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: index is NULL");
+    if (!keypoints || !n_keypoints) return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: keypoints/n_keypoints is NULL");
+    if (!(radius > 0.f) || !(non_max_radius >= 0.f) || std::isnan(lambda21) || std::isnan(lambda32) || iss_count < 0)
+        return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: radius must be > 0, non_max_radius >= 0, iss_count >= 0");
+    *n_keypoints = 0;
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    double *d_l3 = nullptr;
+    if (lambda3) {
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(double) * (size_t)n));
+        d_l3 = ctx->scratch[7].as<double>();
+    }
+    PCP_TRY(iss_device(ix, radius, lambda21, lambda32, non_max_radius, iss_count, keypoints, n_keypoints, d_l3));
+    if (lambda3) {
+        PCP_TRY(download(ctx, lambda3, d_l3, sizeof(double) * (size_t)n));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
 }
 
 // ---------------------------------------------------------------------------------------------- pose helpers

@@ -18,6 +18,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #include "pcp_internal.cuh"
 
@@ -622,6 +623,172 @@ int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, doub
     PCP_CUDA(cudaStreamSynchronize(st));
     for (int i = 0; i < 3; ++i) h_w[i] = h[i];
     for (int i = 0; i < 9; ++i) h_V[i] = h[3 + i];
+    return PCP_OK;
+}
+
+// ================================================================================================ ISS keypoints
+// The detection loop of Keypoint_detection_ISS/ISS.py:40-73 on top of the radius search:
+//   c_j  = |ball(p_j, radius)|                                              ISS.py:49   (pcp_radius_count)
+//   M_i  = sum_j (1/c_j) (p_j - p_i)(p_j - p_i)^T / sum_j (1/c_j), j in ball(p_i)   :43-51 (CSR of pcp_radius_fill,
+//          one warp per point, float64)
+//   candidates: l2/l1 < lambda21 and l3/l2 < lambda32 (eigenvalues descending; NaN ratios fail as in numpy)  :52-57
+//   non-maximum suppression in descending l3 (ties: ascending index -- sorted(..., reverse=True) is stable) :59-73,
+//   stopping once MORE than iss_count keypoints are kept (:72) -- as rounds of a parallel rule that reaches the
+//   same fixed point as the sequential loop: a candidate is kept once every earlier-ranked neighbour is suppressed,
+//   suppressed once an earlier-ranked neighbour is kept.
+
+namespace {
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+    return v;
+}
+
+__global__ void __launch_bounds__(256) iss_saliency_kernel(const float *__restrict__ xyz, long long stride, long long n,
+                                                           const long long *__restrict__ off,
+                                                           const int32_t *__restrict__ nbr, double lambda21,
+                                                           double lambda32, double *__restrict__ lambda3,
+                                                           unsigned long long *__restrict__ keys,
+                                                           unsigned *__restrict__ vals) {
+    const long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const float *pi = xyz + i * stride;
+    const double px = pi[0], py = pi[1], pz = pi[2];
+    double a[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (long long e = off[i] + lane; e < off[i + 1]; e += 32) {
+        const long long j = nbr[e];
+        const double w = 1.0 / (double)(off[j + 1] - off[j]);          // ISS.py:49
+        const float *pj = xyz + j * stride;
+        const double dx = (double)pj[0] - px, dy = (double)pj[1] - py, dz = (double)pj[2] - pz;
+        a[0] += w * dx * dx; a[1] += w * dx * dy; a[2] += w * dx * dz;
+        a[3] += w * dy * dy; a[4] += w * dy * dz; a[5] += w * dz * dz;
+        a[6] += w;
+    }
+#pragma unroll
+    for (int u = 0; u < 7; ++u) a[u] = warp_sum_d(a[u]);
+    if (lane != 0) return;
+    double w[3], V[9];
+    sym_eig3(a[0] / a[6], a[1] / a[6], a[2] / a[6], a[3] / a[6], a[4] / a[6], a[5] / a[6], w, V);
+    const double l1 = fmax(w[0], fmax(w[1], w[2])), l3 = fmin(w[0], fmin(w[1], w[2]));
+    const double l2 = fmax(fmin(w[0], w[1]), fmin(fmax(w[0], w[1]), w[2]));          // median of the three
+    const bool cand = (l2 / l1 < lambda21) && (l3 / l2 < lambda32);    // NaN (isolated point: 0/0) compares false
+    lambda3[i] = cand ? l3 : nan("");
+    // sort key: candidates first in DESCENDING l3 (order-preserving image of the double, inverted), others last
+    unsigned long long b = (unsigned long long)__double_as_longlong(l3);
+    b = (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+    keys[i] = cand ? ~b : 0xffffffffffffffffull;
+    vals[i] = (unsigned)i;
+}
+
+// state: 0 = not a candidate, 1 = undecided, 2 = kept, 3 = suppressed.  rank[i] = position in the sorted order.
+__global__ void __launch_bounds__(256) iss_rank_kernel(const unsigned long long *__restrict__ keys_sorted,
+                                                       const unsigned *__restrict__ vals_sorted, long long n,
+                                                       unsigned *__restrict__ rank, unsigned char *__restrict__ state,
+                                                       unsigned *__restrict__ meta) {
+    const long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const bool cand = keys_sorted[s] != 0xffffffffffffffffull;
+    const unsigned i = vals_sorted[s];
+    rank[i] = (unsigned)s;
+    state[i] = cand ? 1 : 0;
+    if (cand && (s + 1 == n || keys_sorted[s + 1] == 0xffffffffffffffffull)) meta[0] = (unsigned)(s + 1);   // candidates
+}
+
+// one warp per sorted candidate position; meta[1] counts the undecided left after this round
+__global__ void __launch_bounds__(256) iss_nms_round_kernel(const unsigned *__restrict__ vals_sorted, unsigned n_cand,
+                                                            const long long *__restrict__ off,
+                                                            const int32_t *__restrict__ nbr,
+                                                            const unsigned *__restrict__ rank,
+                                                            volatile unsigned char *__restrict__ state,
+                                                            unsigned *__restrict__ meta) {
+    const unsigned s = (unsigned)((blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (s >= n_cand) return;
+    const unsigned i = vals_sorted[s];
+    if (state[i] != 1) return;
+    bool kept_before = false, open_before = false;
+    for (long long e = off[i] + lane; e < off[i + 1]; e += 32) {
+        const unsigned j = (unsigned)nbr[e];
+        if (j == i || rank[j] >= s) continue;
+        const unsigned char st = state[j];
+        kept_before |= st == 2;
+        open_before |= st == 1;
+    }
+    kept_before = __any_sync(0xffffffffu, kept_before);
+    open_before = __any_sync(0xffffffffu, open_before);
+    if (lane != 0) return;
+    if (kept_before) state[i] = 3;
+    else if (!open_before) state[i] = 2;
+    else atomicAdd(meta + 1, 1u);
+}
+
+}  // namespace
+
+int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, float nms_radius, int iss_count,
+               int32_t *h_keypoints, int32_t *h_n_keypoints, double *d_lambda3_out) {
+    pcp_ctx *ctx = ix->ctx;
+    cudaStream_t st = ctx->stream;
+    const int64_t n = ix->n;
+    const float *d_xyz = ix->built_from;
+    const int64_t stride = ix->built_stride;
+    DevBuf &b_off = ctx->iss_buf[0], &b_idx = ctx->iss_buf[1], &b_dist = ctx->iss_buf[2], &b_misc = ctx->iss_buf[3];
+    auto csr = [&](float r, long long *M) -> int {
+        PCP_TRY(b_off.ensure(sizeof(int64_t) * (size_t)(n + 1)));
+        PCP_TRY(radius_count_device(ix, d_xyz, n, stride, r, b_off.as<int64_t>()));
+        PCP_CUDA(cudaMemcpyAsync(M, b_off.as<int64_t>() + n, sizeof(long long), cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaStreamSynchronize(st));
+        PCP_TRY(b_idx.ensure(sizeof(int32_t) * (size_t)*M));
+        PCP_TRY(b_dist.ensure(sizeof(float) * (size_t)*M));
+        return radius_fill_device(ix, d_xyz, n, stride, r, b_off.as<int64_t>(), b_idx.as<int32_t>(), b_dist.as<float>(), 0);
+    };
+    long long M = 0;
+    PCP_TRY(csr(radius, &M));
+    // misc: lambda3 (n f64) | keys a/b (n u64 each) | vals a/b (n u32 each) | rank (n u32) | meta (4 u32) | state (n u8)
+    PCP_TRY(b_misc.ensure((size_t)n * (8 + 16 + 8 + 4 + 1) + 64));
+    double *lambda3 = b_misc.as<double>();
+    unsigned long long *k_a = reinterpret_cast<unsigned long long *>(lambda3 + n), *k_b = k_a + n;
+    unsigned *v_a = reinterpret_cast<unsigned *>(k_b + n), *v_b = v_a + n, *rank = v_b + n, *meta = rank + n;
+    unsigned char *state = reinterpret_cast<unsigned char *>(meta + 4);
+    const unsigned warp_blocks = (unsigned)((n * 32 + 255) / 256), blocks = (unsigned)((n + 255) / 256);
+    iss_saliency_kernel<<<warp_blocks, 256, 0, st>>>(d_xyz, stride, n, b_off.as<long long>(), b_idx.as<int32_t>(), lambda21,
+                                                    lambda32, lambda3, k_a, v_a);
+    size_t tmp = 0;
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, k_a, k_b, v_a, v_b, n, 0, 64, st));
+    PCP_TRY(ctx->cub_tmp.ensure(tmp));
+    PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, k_a, k_b, v_a, v_b, n, 0, 64, st));
+    PCP_CUDA(cudaMemsetAsync(meta, 0, 16, st));
+    iss_rank_kernel<<<blocks, 256, 0, st>>>(k_b, v_b, n, rank, state, meta);
+    ctx->launches += 2 + 10;
+    if (d_lambda3_out)
+        PCP_CUDA(cudaMemcpyAsync(d_lambda3_out, lambda3, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+    if (nms_radius != radius) PCP_TRY(csr(nms_radius, &M));          // ISS.py:67 searches with non_max_radius
+    unsigned h_meta[2] = {0, 0};
+    PCP_CUDA(cudaMemcpyAsync(h_meta, meta, sizeof(h_meta), cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaStreamSynchronize(st));
+    const unsigned n_cand = h_meta[0];
+    *h_n_keypoints = 0;
+    if (n_cand == 0) return PCP_OK;
+    const unsigned cand_blocks = (unsigned)(((long long)n_cand * 32 + 255) / 256);
+    for (int round = 0; round < 100000; ++round) {
+        PCP_CUDA(cudaMemsetAsync(meta + 1, 0, 4, st));
+        iss_nms_round_kernel<<<cand_blocks, 256, 0, st>>>(v_b, n_cand, b_off.as<long long>(), b_idx.as<int32_t>(), rank, state, meta);
+        ctx->launches += 1;
+        PCP_CUDA(cudaMemcpyAsync(h_meta, meta, sizeof(h_meta), cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaStreamSynchronize(st));
+        if (h_meta[1] == 0) break;
+    }
+    // kept candidates in rank order; the loop of ISS.py:61-73 stops once more than iss_count are kept
+    std::vector<unsigned> order(n_cand);
+    std::vector<unsigned char> h_state((size_t)n);
+    PCP_CUDA(cudaMemcpyAsync(order.data(), v_b, sizeof(unsigned) * n_cand, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaMemcpyAsync(h_state.data(), state, (size_t)n, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA(cudaStreamSynchronize(st));
+    int kept = 0;
+    for (unsigned s = 0; s < n_cand && kept <= iss_count; ++s)
+        if (h_state[order[s]] == 2) h_keypoints[kept++] = (int32_t)order[s];
+    *h_n_keypoints = kept;
     return PCP_OK;
 }
 

@@ -123,6 +123,7 @@ struct pcp_ctx {
     // ICP front end (pcp_front.cu): result of the last pcp_voxel_filter (read by pcp_voxel_filter_read), its run
     // count / bounding-box accumulators, and the neighbour lists of pcp_normals
     pcp::DevBuf voxel_out, voxel_meta, normals_nn;
+    pcp::DevBuf iss_buf[4];        // pcp_iss_keypoints: CSR of the radius search (offsets, indices, distances) and its work arrays
     int64_t voxel_n_out = -1;
     bool count_work = false;
     // optional timing of the dominant kernel (pcp_ctx_enable_kernel_timing): event pairs around every
@@ -191,6 +192,8 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, c
 int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double leaf, int mode,
                         unsigned long long seed, int64_t *n_out);
 int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals);
+int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, float nms_radius, int iss_count,
+               int32_t *h_keypoints, int32_t *h_n_keypoints, double *d_lambda3_out);
 int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double *h_w, double *h_V);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,

@@ -35,6 +35,11 @@ def front_golden():
     return np.load(os.path.join(GOLDEN, "front_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def iss_golden():
+    return np.load(os.path.join(GOLDEN, "iss_golden.npz"))
+
+
 def golden_cases(g):
     return sorted({k.split("/")[0] for k in g.files})
 

@@ -186,3 +186,57 @@ def test_whole_cloud_pca_large_is_deterministic(pcp):
     rw = np.linalg.eigvalsh(H)[::-1]
     assert np.allclose(w, rw, rtol=1e-10)
     assert np.allclose(np.abs(np.diag(v)), 1.0, atol=1e-2)        # axes of the anisotropic Gaussian
+
+
+# ---- ISS keypoints
+
+def _iss_margins(pts, r, l21=None, l32=None):
+    """Precondition of an exact comparison: the float32 neighbourhoods the library searches (result_set.py:80
+    semantics, restated by the kd-tree oracle) are the float64 neighbourhoods of scipy's cKDTree (ISS.py:36,43) --
+    they can differ only for a pair within a float32 ulp of the radius."""
+    from scipy import spatial
+    off, _, _ = knn_oracle.KdTree(pts, 32).radius(pts, np.float32(r))
+    p64 = pts.astype(np.float64)
+    c64 = [len(b) for b in spatial.cKDTree(p64).query_ball_point(p64, float(r))]
+    return np.array_equal(np.diff(off), c64)
+
+
+@pytest.mark.parametrize("name", ("box1500", "box3000"))
+def test_iss_golden_reference_script(pcp, iss_golden, name):
+    from point_cloud_process_b200.iss import iss_keypoints
+    g = iss_golden
+    pts = g[f"{name}_pts"]
+    r, l21, l32, rn, cnt = g[f"{name}_params"]
+    assert _iss_margins(pts, r, l21, l32)
+    kp, l3 = iss_keypoints(pts, r, l21, l32, rn, int(cnt), return_lambda3=True)
+    assert np.flatnonzero(~np.isnan(l3)).tolist() == g[f"{name}_cand_idx"].tolist()
+    assert kp == g[f"{name}_iss_idx"].tolist()
+
+
+@pytest.mark.parametrize("seed,n,r,rn,cnt", [(1, 6000, 0.25, 0.25, 20), (2, 6000, 0.2, 0.35, 5), (3, 20000, 0.12, 0.12, 40)])
+def test_iss_vs_restatement(pcp, seed, n, r, rn, cnt):
+    """Denser seeded clouds: many candidates, the iss_count early stop (ISS.py:72), non_max_radius != radius."""
+    import importlib.util, os
+    from conftest import GOLDEN
+    from point_cloud_process_b200.iss import iss_keypoints
+    spec = importlib.util.spec_from_file_location("make_golden_iss", os.path.join(GOLDEN, "make_golden_iss.py"))
+    mg = importlib.util.module_from_spec(spec); spec.loader.exec_module(mg)
+    pts = mg.cloud(seed, n)
+    assert _iss_margins(pts, r, 0.5, 0.5) and _iss_margins(pts, rn, 0.5, 0.5)
+    ref_kp, ref_cand, ref_l3 = front_oracle.iss_keypoints(pts, r, 0.6, 0.6, rn, cnt)
+    kp, l3 = iss_keypoints(pts, r, 0.6, 0.6, rn, cnt, return_lambda3=True)
+    cand = np.flatnonzero(~np.isnan(l3))
+    assert len(ref_cand) > 50
+    assert cand.tolist() == ref_cand
+    rl3 = np.array([ref_l3[i] for i in ref_cand])
+    assert np.allclose(l3[cand], rl3, rtol=1e-9, atol=1e-18)
+    assert kp == ref_kp
+    assert len(kp) <= cnt + 1
+
+
+def test_iss_degenerate(pcp):
+    from point_cloud_process_b200.iss import iss_keypoints
+    pts = (np.arange(30, dtype=np.float32)[:, None] * np.float32([10, 0, 0]))      # isolated points: 0/0 ratios
+    assert iss_keypoints(pts, 0.5, 0.5, 0.5, 0.5, 20) == []
+    with pytest.raises(ValueError):
+        iss_keypoints(pts, -1.0)

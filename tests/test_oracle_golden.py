@@ -175,3 +175,14 @@ def test_whole_cloud_pca_restatement_matches_reference(front_golden, name):
     g = front_golden
     w, v = front_oracle.pca(g[f"vf_{name}_pts"])
     assert np.array_equal(w, g[f"pca_cloud_{name}_w"]) and np.array_equal(v, g[f"pca_cloud_{name}_v"])
+
+
+@pytest.mark.parametrize("name", ("box1500", "box3000"))
+def test_iss_restatement_matches_reference_script(iss_golden, name):
+    """tests/golden/iss_golden.npz <- Keypoint_detection_ISS/ISS.py executed unmodified (make_golden_iss.py)."""
+    from oracle import front_oracle
+    g = iss_golden
+    r, l21, l32, rn, cnt = g[f"{name}_params"]
+    iss_idx, cand_idx, _ = front_oracle.iss_keypoints(g[f"{name}_pts"], r, l21, l32, rn, int(cnt))
+    assert cand_idx == g[f"{name}_cand_idx"].tolist()
+    assert iss_idx == g[f"{name}_iss_idx"].tolist()
