@@ -79,6 +79,20 @@ def main():
                     "pca_kernel_bytes": int(n * (4 * k + 12 * k + 48)), "pca_kernel_gbs": n * (16 * k + 48) / max(1e-9, (ms - ms_knn) * 1e-3) / 1e9,
                     "cpu_restatement_points_per_s_1core": 2000 / cpu, "cpu_sample": "PCA of 2000 sampled neighbourhoods (numpy), kNN not included"})
         del ix, d
+    for name, pts, r in (("KITTI 000000.bin", kitti, 0.5), ("KITTI 000000.bin", kitti, 1.0), ("uniform 1M in [0,25.4)^3", uni, 0.5)):
+        n = len(pts)
+        d = torch.from_numpy(pts).cuda()
+        ix = native.Index(ctx, d.data_ptr(), n, 3)
+        kp, l3 = ix.iss_keypoints(r, 0.5, 0.5, r, 20)
+        ms = wall(ctx, lambda: ix.iss_keypoints(r, 0.5, 0.5, r, 20), reps=5, warm=1)
+        off = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+        ix.radius_count_device(d.data_ptr(), n, 3, r, off.data_ptr()); ctx.synchronize()
+        m = int(off[-1].item())
+        res.append({"op": "ISS keypoints (radius count + fill + saliency + NMS)", "cloud": name, "points": n, "radius": r,
+                    "pairs": m, "candidates": int(np.count_nonzero(~np.isnan(l3))), "keypoints": len(kp), "ms": ms,
+                    "points_per_s": n / (ms * 1e-3), "pairs_per_s": m / (ms * 1e-3),
+                    "timer": "host perf_counter around the whole call incl. the lambda3 read back (n x 8 B)"})
+        del ix, d
     print(json.dumps(res, indent=1))
 
 
