@@ -240,6 +240,18 @@ PCP_API int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_fl
 PCP_API int pcp_iss_keypoints(pcp_index *index, float radius, double lambda21, double lambda32, float non_max_radius,
                               int iss_count, int32_t *keypoints, int32_t *n_keypoints, double *lambda3);
 
+/* pcp_dbscan replaces DBSCAN(radius, Min_Pts).fit(data) + predict() of Cluster_dbscan/dbscan.py:4-38 over the
+ * indexed cloud: labels[i] = cluster number (0, 1, ... in the order the reference opens them: seeds are popped
+ * from the END of its `unvisited` list, :18) or -1 for noise -- the SAME labels as the sequential loop, including
+ * its order-dependent rules: a popped point with fewer than Min_Pts neighbours (self included) stays noise for
+ * good (:20-22), a point with >= Min_Pts opens a cluster (:24), a claimed point expands it only with MORE than
+ * Min_Pts neighbours (:31-32).  Computed on the radius CSR as connected components of the expanding points plus a
+ * rank-ordered fixed point for the rest.  Neighbourhoods: float32 dist <= radius
+ * (result_set.py:80); scipy's KDTree in the reference is float64 (differs only within one float32 ulp of the
+ * radius).  labels: n x int32 (host or device per `mem`); n_clusters (host, may be NULL).  For an index built
+ * with PCP_DEVICE the cloud passed to the build must still be alive. */
+PCP_API int pcp_dbscan(pcp_index *index, float radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

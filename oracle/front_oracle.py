@@ -106,3 +106,37 @@ def iss_keypoints(points, radius=0.5, lambda21=0.5, lambda32=0.5, non_max_radius
         if len(iss_idx) > iss_count:
             break
     return iss_idx, cand_idx, all_l3
+
+
+def dbscan_labels(data, radius=0.5, min_pts=10):
+    """DBSCAN.fit + predict of Cluster_dbscan/dbscan.py:10-38 with the same visiting order, using sets where the
+    reference scans Python lists (`cur_ind in unvisited`, `unvisited.remove`, :29,:35) -- identical labels, without
+    the O(N^2) list work.  Pinned by tests/golden/dbscan_golden.npz (the reference class itself,
+    tests/golden/make_golden_dbscan.py)."""
+    from scipy.spatial import KDTree
+    data = np.asarray(data, dtype=np.float64)
+    n = data.shape[0]
+    labels = -1 * np.ones(n)                                       # :12
+    visited = np.zeros(n, dtype=bool)
+    tree = KDTree(data, leafsize=32)                               # :16
+    balls = tree.query_ball_point(data, radius)
+    label = -1
+    for ind in range(n - 1, -1, -1):                               # unvisited.pop() takes the highest index left (:18)
+        if visited[ind]:
+            continue
+        visited[ind] = True
+        nb = balls[ind]
+        if len(nb) < min_pts:                                      # :20
+            labels[ind] = -1
+            continue
+        label += 1                                                 # :24
+        labels[ind] = label
+        stack = list(nb)                                           # :26
+        while stack:
+            cur = stack.pop()                                      # :28
+            if not visited[cur]:                                   # :29
+                labels[cur] = label
+                if len(balls[cur]) > min_pts:                      # :32 (strict)
+                    stack.extend(balls[cur])
+                visited[cur] = True                                # :35
+    return labels.astype(np.int32)

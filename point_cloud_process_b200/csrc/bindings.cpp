@@ -167,6 +167,18 @@ class Index {
         std::copy(kp.begin(), kp.begin() + nk, out.mutable_data());
         return py::make_tuple(out, l3);
     }
+    // DBSCAN.fit + predict of Cluster_dbscan/dbscan.py:10-38 -> (labels (N,) int32, number of clusters)
+    py::tuple dbscan(float radius, int min_pts) {
+        auto lab = result_array<int32_t>({(py::ssize_t)size()});
+        int32_t nc = 0;
+        check(pcp_dbscan(ix_, radius, min_pts, PCP_HOST, lab.mutable_data(), &nc), "pcp_dbscan");
+        return py::make_tuple(lab, nc);
+    }
+    int dbscan_device(float radius, int min_pts, uintptr_t labels) {
+        int32_t nc = 0;
+        check(pcp_dbscan(ix_, radius, min_pts, PCP_DEVICE, reinterpret_cast<int32_t *>(labels), &nc), "pcp_dbscan");
+        return nc;
+    }
     void normals_device(int k, uintptr_t nrm, uintptr_t ev) {
         check(pcp_normals(ix_, k, PCP_DEVICE, reinterpret_cast<double *>(nrm), reinterpret_cast<double *>(ev)), "pcp_normals");
     }
@@ -388,6 +400,8 @@ PYBIND11_MODULE(_pcp, m) {
         .def("knn_self", &Index::knn_self, py::arg("k"))
         .def("normals", &Index::normals, py::arg("k") = 5)
         .def("normals_device", &Index::normals_device)
+        .def("dbscan", &Index::dbscan, py::arg("radius") = 0.5f, py::arg("min_pts") = 10)
+        .def("dbscan_device", &Index::dbscan_device)
         .def("iss_keypoints", &Index::iss_keypoints, py::arg("radius") = 0.5f, py::arg("lambda21") = 0.5,
              py::arg("lambda32") = 0.5, py::arg("non_max_radius") = 0.5f, py::arg("iss_count") = 20)
         .def("knn_device", &Index::knn_device)

@@ -697,6 +697,31 @@ int pcp_iss_keypoints(pcp_index *ix, float radius, double lambda21, double lambd
     return PCP_OK;
 }
 
+int pcp_dbscan(pcp_index *ix, float radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_dbscan: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_dbscan: mem must be PCP_HOST or PCP_DEVICE");
+    if (!(radius >= 0.f)) return fail(PCP_ERR_INVALID, "pcp_dbscan: radius must be >= 0");
+    int32_t dummy = 0;
+    if (!n_clusters) n_clusters = &dummy;
+    *n_clusters = 0;
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    if (!labels) return fail(PCP_ERR_INVALID, "pcp_dbscan: labels is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    int32_t *d_lab = labels;
+    if (mem == PCP_HOST) {
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(int32_t) * (size_t)n));
+        d_lab = ctx->scratch[7].as<int32_t>();
+    }
+    PCP_TRY(dbscan_device(ix, radius, min_pts, d_lab, n_clusters));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, labels, d_lab, sizeof(int32_t) * (size_t)n));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------- pose helpers
 
 // rotmat2quaternion / copysign / homo2tq of main.py:158-180 (host arithmetic, float64)

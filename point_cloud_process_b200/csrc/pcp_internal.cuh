@@ -194,6 +194,8 @@ int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t str
 int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals);
 int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, float nms_radius, int iss_count,
                int32_t *h_keypoints, int32_t *h_n_keypoints, double *d_lambda3_out);
+// DBSCAN on the radius CSR (pcp_dbscan.cu)
+int dbscan_device(pcp_index *ix, float radius, int min_pts, int32_t *d_labels, int32_t *h_n_clusters);
 int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double *h_w, double *h_V);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,

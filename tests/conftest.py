@@ -40,6 +40,11 @@ def iss_golden():
     return np.load(os.path.join(GOLDEN, "iss_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def dbscan_golden():
+    return np.load(os.path.join(GOLDEN, "dbscan_golden.npz"))
+
+
 def golden_cases(g):
     return sorted({k.split("/")[0] for k in g.files})
 

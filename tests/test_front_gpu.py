@@ -240,3 +240,58 @@ def test_iss_degenerate(pcp):
     assert iss_keypoints(pts, 0.5, 0.5, 0.5, 0.5, 20) == []
     with pytest.raises(ValueError):
         iss_keypoints(pts, -1.0)
+
+
+# ---- DBSCAN
+
+DB_CASES = ("a", "b", "c", "d", "flat")
+
+
+@pytest.mark.parametrize("name", DB_CASES)
+def test_dbscan_golden_reference_class(pcp, dbscan_golden, name):
+    """Labels IDENTICAL to the reference's sequential loop (numbering, permanent noise, strict expansion)."""
+    from point_cloud_process_b200.dbscan import DBSCAN
+    g = dbscan_golden
+    pts = g[f"{name}_pts"]
+    r, mp = g[f"{name}_params"]
+    assert _iss_margins(pts, r)          # float32 neighbourhoods == the float64 ones scipy's KDTree finds
+    d = DBSCAN(radius=r, Min_Pts=int(mp))
+    d.fit(pts)
+    lab = d.predict()
+    assert lab.dtype == np.int32 and np.array_equal(lab, g[f"{name}_labels"])
+    assert d.n_clusters_ == g[f"{name}_labels"].max() + 1
+
+
+@pytest.mark.parametrize("seed,n,r,mp", [(21, 30_000, 0.08, 5), (22, 60_000, 0.05, 3), (23, 20_000, 0.1, 12)])
+def test_dbscan_vs_restatement(pcp, seed, n, r, mp):
+    import importlib.util, os
+    from conftest import GOLDEN
+    from point_cloud_process_b200.dbscan import DBSCAN
+    spec = importlib.util.spec_from_file_location("make_golden_dbscan", os.path.join(GOLDEN, "make_golden_dbscan.py"))
+    mg = importlib.util.module_from_spec(spec); spec.loader.exec_module(mg)
+    pts = mg.cloud(seed, n)
+    assert _iss_margins(pts, r)
+    ref = front_oracle.dbscan_labels(pts, r, mp)
+    d = DBSCAN(radius=r, Min_Pts=mp)
+    d.fit(pts)
+    assert ref.max() >= 3 and (ref < 0).any()
+    assert np.array_equal(d.predict(), ref)
+
+
+def test_dbscan_kitti_properties(pcp, kitti):
+    """Full scan (r = 0.5, 22 M pairs): size-independent properties -- every point with > Min_Pts neighbours shares
+    its label with all such neighbours, labels are 0..S-1 with every cluster non-empty, noise has < Min_Pts
+    neighbours or only later-opened clusters around it (checked through the restatement on a 20 k subset above)."""
+    ix = pcp.SearchIndex(kitti)
+    lab, S = ix._ix.dbscan(0.5, 10)
+    off, idx, _ = ix.radius(kitti, 0.5)
+    cnt = np.diff(off)
+    assert lab.min() >= -1 and lab.max() == S - 1 and len(np.unique(lab[lab >= 0])) == S
+    exp = cnt > 10
+    src = np.repeat(np.arange(len(kitti)), cnt)
+    both = exp[src] & exp[idx]
+    assert np.array_equal(lab[src[both]], lab[idx[both]])
+    assert np.all(lab[exp] >= 0)
+    # cluster numbers follow the seeds' descending index: the first cluster contains the last seedable point
+    seedable = np.flatnonzero(cnt >= 10)
+    assert lab[seedable[-1]] == 0

@@ -29,7 +29,7 @@ def test_header_declares_the_documented_surface():
     syms = declared_symbols()
     for s in ("pcp_ctx_create", "pcp_index_build", "pcp_knn", "pcp_knn_self", "pcp_radius_count", "pcp_radius_fill",
               "pcp_icp_batch", "pcp_procrustes", "pcp_homo2tq", "pcp_last_error", "pcp_voxel_filter",
-              "pcp_voxel_filter_read", "pcp_normals", "pcp_pca", "pcp_iss_keypoints"):
+              "pcp_voxel_filter_read", "pcp_normals", "pcp_pca", "pcp_iss_keypoints", "pcp_dbscan"):
         assert s in syms
 
 

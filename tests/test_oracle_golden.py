@@ -186,3 +186,15 @@ def test_iss_restatement_matches_reference_script(iss_golden, name):
     iss_idx, cand_idx, _ = front_oracle.iss_keypoints(g[f"{name}_pts"], r, l21, l32, rn, int(cnt))
     assert cand_idx == g[f"{name}_cand_idx"].tolist()
     assert iss_idx == g[f"{name}_iss_idx"].tolist()
+
+
+DB_CASES = ("a", "b", "c", "d", "flat")
+
+
+@pytest.mark.parametrize("name", DB_CASES)
+def test_dbscan_restatement_matches_reference_class(dbscan_golden, name):
+    """tests/golden/dbscan_golden.npz <- Cluster_dbscan/dbscan.py's DBSCAN imported unmodified."""
+    from oracle import front_oracle
+    g = dbscan_golden
+    r, mp = g[f"{name}_params"]
+    assert np.array_equal(front_oracle.dbscan_labels(g[f"{name}_pts"], r, int(mp)), g[f"{name}_labels"])

@@ -93,6 +93,20 @@ def main():
                     "points_per_s": n / (ms * 1e-3), "pairs_per_s": m / (ms * 1e-3),
                     "timer": "host perf_counter around the whole call incl. the lambda3 read back (n x 8 B)"})
         del ix, d
+    for name, pts, r, mp in (("KITTI 000000.bin", kitti, 0.5, 10), ("KITTI 000000.bin", kitti, 1.0, 10), ("uniform 1M in [0,25.4)^3", uni, 0.5, 30)):
+        n = len(pts)
+        d = torch.from_numpy(pts).cuda()
+        ix = native.Index(ctx, d.data_ptr(), n, 3)
+        lab = torch.empty(n, dtype=torch.int32, device="cuda")
+        l0 = ctx.launch_count()
+        nc = ix.dbscan_device(r, mp, lab.data_ptr())
+        launches = ctx.launch_count() - l0
+        ms = wall(ctx, lambda: ix.dbscan_device(r, mp, lab.data_ptr()), reps=5, warm=1)
+        res.append({"op": "DBSCAN (radius count + fill + components + seed order + labels)", "cloud": name, "points": n,
+                    "radius": r, "min_pts": mp, "clusters": int(nc), "noise": int((lab < 0).sum().item()), "ms": ms,
+                    "launches": int(launches), "points_per_s": n / (ms * 1e-3),
+                    "timer": "host perf_counter around the whole call, labels left on the device"})
+        del ix, d
     print(json.dumps(res, indent=1))
 
 
