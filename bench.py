@@ -278,6 +278,9 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        # NCCL_DEBUG=VERSION (the box default) prints "NCCL version ..." on STDOUT, in front of the one JSON line
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     import point_cloud_process_b200 as pcp
