@@ -48,6 +48,21 @@ def test_version_and_argument_errors_without_gpu(lib):
     tq = (ctypes.c_double * 7)()
     eye = (ctypes.c_double * 16)(*np.eye(4).ravel())
     assert lib.pcp_homo2tq(eye, tq) == 0 and list(tq) == [0, 0, 0, 1, 0, 0, 0]
+    # the widened entry points (voxel filter, normals, PCA, ISS, DBSCAN) reject NULL handles the same way
+    lib.pcp_voxel_filter.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_double,
+                                     ctypes.c_int, ctypes.c_uint64, ctypes.c_int, ctypes.c_void_p]
+    assert lib.pcp_voxel_filter(None, None, 0, 3, 0.5, 0, 0, 0, None) == -1
+    assert lib.pcp_voxel_filter_read(None, 0, None) == -1
+    assert lib.pcp_normals(None, 5, 0, None, None) == -1
+    lib.pcp_pca.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int,
+                            ctypes.c_void_p, ctypes.c_void_p]
+    assert lib.pcp_pca(None, None, 0, 3, 0, None, None) == -1
+    lib.pcp_iss_keypoints.argtypes = [ctypes.c_void_p, ctypes.c_float, ctypes.c_double, ctypes.c_double, ctypes.c_float,
+                                      ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    assert lib.pcp_iss_keypoints(None, 0.5, 0.5, 0.5, 0.5, 20, None, None, None) == -1
+    lib.pcp_dbscan.argtypes = [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    assert lib.pcp_dbscan(None, 0.5, 10, 0, None, None) == -1
+    assert b"pcp_dbscan" in lib.pcp_last_error()
     prm = (ctypes.c_byte * 64)()
     assert lib.pcp_icp_default_params(prm) == 0
     assert np.frombuffer(prm, np.int32, 1)[0] == 100              # main.py:98
@@ -65,6 +80,13 @@ def test_no_cpu_fallback_without_device(lib):
         pcp.SearchIndex(np.zeros((10, 3), np.float32))
     with pytest.raises(RuntimeError):
         pcp.icp_batch([np.zeros((10, 3), np.float32)], [np.zeros((10, 3), np.float32)])
+    from point_cloud_process_b200 import dbscan, iss, pca_normal, voxel_filter
+    pts = np.random.default_rng(0).random((50, 3)).astype(np.float32)
+    for call in (lambda: voxel_filter.voxel_filter(pts, 0.1, "centroid"), lambda: pca_normal.PCA(pts),
+                 lambda: pca_normal.estimate_normals(pts), lambda: iss.iss_keypoints(pts),
+                 lambda: dbscan.DBSCAN(0.2, 3).fit(pts)):
+        with pytest.raises(RuntimeError):
+            call()
 
 
 def test_product_never_imports_the_oracle():
@@ -177,8 +199,11 @@ def test_evaluate_rt_matches_reference(tmp_path):
 
 
 def test_front_end_modules_mirror_reference_names():
-    from point_cloud_process_b200 import evaluate_rt, pca_normal, voxel_filter
-    assert callable(voxel_filter.voxel_filter) and callable(pca_normal.estimate_normals)
+    from point_cloud_process_b200 import dbscan, evaluate_rt, iss, pca_normal, voxel_filter
+    assert callable(voxel_filter.voxel_filter) and callable(pca_normal.estimate_normals) and callable(pca_normal.PCA)
+    assert callable(iss.iss_keypoints) and callable(iss.readModelNet40)
+    d = dbscan.DBSCAN(radius=0.3, Min_Pts=7)                    # dbscan.py:5-8
+    assert (d.radius, d.Min_Pts, d.labels_) == (0.3, 7, None) and d.predict() is None
     for name in ("get_P_from_Rt", "is_registration_successful", "get_P_diff", "read_oxford_bin", "read_reg_results",
                  "reg_result_row_to_array", "evaluate_rt"):
         assert hasattr(evaluate_rt, name)
