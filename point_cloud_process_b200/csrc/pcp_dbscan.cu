@@ -47,7 +47,10 @@ __global__ void __launch_bounds__(256) db_classify_kernel(const long long *__res
     vmax[i] = -1;
 }
 
-// max-index propagation over expander-expander edges; one warp per expander
+// max-index propagation over expander-expander edges; one warp per expander.  (Measured alternatives, both dropped:
+// a single-pass lock-free union-find with path halving -- 58 ms on the KITTI scan, whose ground plane is ONE component
+// of ~10^5 points, so 22 M edges contend for a handful of roots -- against 1.1 ms for these rounds; and reading the
+// "changed" flag only every 2, 4, 8 rounds -- each extra round rescans the whole CSR, 1.57 -> 1.89 ms at r = 1.0.)
 __global__ void __launch_bounds__(256) db_hook_kernel(const long long *__restrict__ off, const int32_t *__restrict__ nbr,
                                                       long long n, const unsigned char *__restrict__ kind,
                                                       int *__restrict__ comp, unsigned *__restrict__ changed) {

@@ -771,10 +771,12 @@ int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, fl
     *h_n_keypoints = 0;
     if (n_cand == 0) return PCP_OK;
     const unsigned cand_blocks = (unsigned)(((long long)n_cand * 32 + 255) / 256);
-    for (int round = 0; round < 100000; ++round) {
-        PCP_CUDA(cudaMemsetAsync(meta + 1, 0, 4, st));
-        iss_nms_round_kernel<<<cand_blocks, 256, 0, st>>>(v_b, n_cand, b_off.as<long long>(), b_idx.as<int32_t>(), rank, state, meta);
-        ctx->launches += 1;
+    for (int batch = 1;; batch = batch < 8 ? batch * 2 : 8) {   // counter read back after 1, 2, 4, 8, 8, ... rounds
+        for (int r = 0; r < batch; ++r) {
+            PCP_CUDA(cudaMemsetAsync(meta + 1, 0, 4, st));
+            iss_nms_round_kernel<<<cand_blocks, 256, 0, st>>>(v_b, n_cand, b_off.as<long long>(), b_idx.as<int32_t>(), rank, state, meta);
+            ctx->launches += 1;
+        }
         PCP_CUDA(cudaMemcpyAsync(h_meta, meta, sizeof(h_meta), cudaMemcpyDeviceToHost, st));
         PCP_CUDA(cudaStreamSynchronize(st));
         if (h_meta[1] == 0) break;
