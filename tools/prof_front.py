@@ -17,5 +17,13 @@ ix = native.Index(ctx, uni.data_ptr(), 1_000_000, 3)
 nrm = torch.empty((1_000_000, 3), dtype=torch.float64, device="cuda"); ev = torch.empty_like(nrm)
 for _ in range(2):
     ix.normals_device(5, nrm.data_ptr(), ev.data_ptr())
+if os.environ.get("PCP_PROF_CONSUMERS", "1") == "1":      # ISS keypoints + DBSCAN on the KITTI scan (r = 1.0: 80 M pairs)
+    import bench
+    kitti = torch.from_numpy(np.fromfile(bench.KITTI, np.float32).reshape(-1, 3)).cuda()
+    kx = native.Index(ctx, kitti.data_ptr(), kitti.shape[0], 3)
+    lab = torch.empty(kitti.shape[0], dtype=torch.int32, device="cuda")
+    for _ in range(2):
+        kx.iss_keypoints(1.0, 0.5, 0.5, 1.0, 20)
+        kx.dbscan_device(1.0, 10, lab.data_ptr())
 ctx.synchronize()
 print("done")
