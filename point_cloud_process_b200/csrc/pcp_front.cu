@@ -645,7 +645,17 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
-__global__ void __launch_bounds__(256) iss_saliency_kernel(const float *__restrict__ xyz, long long stride, long long n,
+// x, y, z and the neighbour count (exact in float below 2^24) of every point in ONE aligned 16-byte record: the
+// saliency pass then pays one scattered sector per pair instead of a 12-byte row plus two CSR offsets
+__global__ void __launch_bounds__(256) iss_pack_kernel(const float *__restrict__ xyz, long long stride, long long n,
+                                                       const long long *__restrict__ off, float4 *__restrict__ packed) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *p = xyz + i * stride;
+    packed[i] = make_float4(p[0], p[1], p[2], (float)(off[i + 1] - off[i]));
+}
+
+__global__ void __launch_bounds__(256) iss_saliency_kernel(const float4 *__restrict__ packed, long long n,
                                                            const long long *__restrict__ off,
                                                            const int32_t *__restrict__ nbr, double lambda21,
                                                            double lambda32, double *__restrict__ lambda3,
@@ -654,14 +664,13 @@ __global__ void __launch_bounds__(256) iss_saliency_kernel(const float *__restri
     const long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (i >= n) return;
-    const float *pi = xyz + i * stride;
-    const double px = pi[0], py = pi[1], pz = pi[2];
+    const float4 pi = packed[i];
+    const double px = pi.x, py = pi.y, pz = pi.z;
     double a[7] = {0, 0, 0, 0, 0, 0, 0};
     for (long long e = off[i] + lane; e < off[i + 1]; e += 32) {
-        const long long j = nbr[e];
-        const double w = 1.0 / (double)(off[j + 1] - off[j]);          // ISS.py:49
-        const float *pj = xyz + j * stride;
-        const double dx = (double)pj[0] - px, dy = (double)pj[1] - py, dz = (double)pj[2] - pz;
+        const float4 pj = packed[nbr[e]];
+        const double w = 1.0 / (double)pj.w;                           // ISS.py:49
+        const double dx = (double)pj.x - px, dy = (double)pj.y - py, dz = (double)pj.z - pz;
         a[0] += w * dx * dx; a[1] += w * dx * dy; a[2] += w * dx * dz;
         a[3] += w * dy * dy; a[4] += w * dy * dz; a[5] += w * dz * dz;
         a[6] += w;
@@ -745,14 +754,17 @@ int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, fl
     };
     long long M = 0;
     PCP_TRY(csr(radius, &M));
-    // misc: lambda3 (n f64) | keys a/b (n u64 each) | vals a/b (n u32 each) | rank (n u32) | meta (4 u32) | state (n u8)
-    PCP_TRY(b_misc.ensure((size_t)n * (8 + 16 + 8 + 4 + 1) + 64));
-    double *lambda3 = b_misc.as<double>();
+    // misc: packed (n float4) | lambda3 (n f64) | keys a/b (n u64 each) | vals a/b (n u32 each) | rank (n u32) | meta (4 u32) | state (n u8)
+    if (n >= (1 << 24)) return fail(PCP_ERR_UNSUPPORTED, "pcp_iss_keypoints: more than 2^24 points");   // counts ride in a float
+    PCP_TRY(b_misc.ensure((size_t)n * (16 + 8 + 16 + 8 + 4 + 1) + 64));
+    float4 *packed = b_misc.as<float4>();
+    double *lambda3 = reinterpret_cast<double *>(packed + n);
     unsigned long long *k_a = reinterpret_cast<unsigned long long *>(lambda3 + n), *k_b = k_a + n;
     unsigned *v_a = reinterpret_cast<unsigned *>(k_b + n), *v_b = v_a + n, *rank = v_b + n, *meta = rank + n;
     unsigned char *state = reinterpret_cast<unsigned char *>(meta + 4);
     const unsigned warp_blocks = (unsigned)((n * 32 + 255) / 256), blocks = (unsigned)((n + 255) / 256);
-    iss_saliency_kernel<<<warp_blocks, 256, 0, st>>>(d_xyz, stride, n, b_off.as<long long>(), b_idx.as<int32_t>(), lambda21,
+    iss_pack_kernel<<<blocks, 256, 0, st>>>(d_xyz, stride, n, b_off.as<long long>(), packed);
+    iss_saliency_kernel<<<warp_blocks, 256, 0, st>>>(packed, n, b_off.as<long long>(), b_idx.as<int32_t>(), lambda21,
                                                     lambda32, lambda3, k_a, v_a);
     size_t tmp = 0;
     PCP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, k_a, k_b, v_a, v_b, n, 0, 64, st));
@@ -760,7 +772,7 @@ int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, fl
     PCP_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, k_a, k_b, v_a, v_b, n, 0, 64, st));
     PCP_CUDA(cudaMemsetAsync(meta, 0, 16, st));
     iss_rank_kernel<<<blocks, 256, 0, st>>>(k_b, v_b, n, rank, state, meta);
-    ctx->launches += 2 + 10;
+    ctx->launches += 3 + 10;
     if (d_lambda3_out)
         PCP_CUDA(cudaMemcpyAsync(d_lambda3_out, lambda3, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     if (nms_radius != radius) PCP_TRY(csr(nms_radius, &M));          // ISS.py:67 searches with non_max_radius
