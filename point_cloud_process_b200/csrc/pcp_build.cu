@@ -263,6 +263,15 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
     idx = s_idx[id];
     const_cast<float4 *>(v.pts)[pos] = make_float4(x, y, z, __uint_as_float(idx));
     const bool real = idx != 0xffffffffu;
+    {
+        // pair layout (IndexView::pts2): the even lane of a pair writes (x0, x1, y0, y1), the odd one (z0, z1, w0, w1)
+        const bool odd = (t & 1u) != 0u;
+        const float px = real ? x : __uint_as_float(0x7f800000u), py = real ? y : 0.f, pz = real ? z : 0.f;
+        const float pw = __uint_as_float(idx);
+        const float a = __shfl_xor_sync(kFullMask, odd ? px : pz, 1);
+        const float b = __shfl_xor_sync(kFullMask, odd ? py : pw, 1);
+        const_cast<float4 *>(v.pts2)[pos] = odd ? make_float4(a, pz, b, pw) : make_float4(px, a, py, b);
+    }
     const unsigned ox = float_to_ordered(x), oy = float_to_ordered(y), oz = float_to_ordered(z);
     const unsigned lx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), hx = __reduce_max_sync(kFullMask, real ? ox : 0u);
     const unsigned ly = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), hy = __reduce_max_sync(kFullMask, real ? oy : 0u);
@@ -402,7 +411,7 @@ inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(
 
 void BatchIndex::release() {
     if (ev_bbox) { cudaEventDestroy(ev_bbox); ev_bbox = nullptr; }
-    for (DevBuf *d : {&pts, &box_lo, &box_hi, &half, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
+    for (DevBuf *d : {&pts, &pts2, &box_lo, &box_hi, &half, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
     h_views.clear();
     P = 0;
 }
@@ -454,6 +463,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     }
 
     PCP_TRY(b->pts.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_leaf) * kLeaf));
+    PCP_TRY(b->pts2.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_leaf) * kLeaf));
     PCP_TRY(b->box_lo.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
     PCP_TRY(b->box_hi.ensure(sizeof(float4) * (size_t)std::max<int64_t>(1, b->total_nodes)));
     PCP_TRY(b->half.ensure(sizeof(float4) * 4 * (size_t)std::max<int64_t>(1, b->total_leaf)));
@@ -468,6 +478,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         IndexView &v = b->h_views[(size_t)p];
         const uintptr_t pt_off = reinterpret_cast<uintptr_t>(v.pts), node_off = reinterpret_cast<uintptr_t>(v.box_lo);
         v.pts = b->pts.as<float4>() + pt_off;
+        v.pts2 = b->pts2.as<float4>() + pt_off;
         v.box_lo = b->box_lo.as<float4>() + node_off;
         v.box_hi = b->box_hi.as<float4>() + node_off;
         v.half = b->half.as<float4>() + pt_off / kLeaf * 4;

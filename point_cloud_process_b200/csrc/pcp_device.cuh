@@ -19,6 +19,88 @@ __device__ __forceinline__ float ref_d2(float qx, float qy, float qz, float px, 
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
+// ---- packed FP32 (sm_100a FADD2 / FMUL2): two lanes of IEEE float32 per 64-bit register pair, every element
+// rounded once per operation exactly like the scalar __f*_rn intrinsics.  A packed multiply is never fed into
+// a packed add here (ptxas would contract that pair into FFMA2): products are unpacked and summed with scalar
+// __fadd_rn, so a pair of distances costs 3 FADD2 + 3 FMUL2 + 4 FADD issue slots instead of 16.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ float max3f(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float min3f(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+// ref_d2 of one query against a PAIR of points (x0, x1), (y0, y1), (z0, z1): bit-equal to two scalar ref_d2
+__device__ __forceinline__ void ref_d2_pair(f32x2 qx, f32x2 qy, f32x2 qz, f32x2 px, f32x2 py, f32x2 pz, float &d0, float &d1) {
+    const f32x2 dx = sub2(qx, px), dy = sub2(qy, py), dz = sub2(qz, pz);
+    float x0, x1, y0, y1, z0, z1;
+    upk2(mul2(dx, dx), x0, x1);
+    upk2(mul2(dy, dy), y0, y1);
+    upk2(mul2(dz, dz), z0, z1);
+    d0 = __fadd_rn(__fadd_rn(x0, y0), z0);
+    d1 = __fadd_rn(__fadd_rn(x1, y1), z1);
+}
+
+// ---- shared memory through explicit 32-bit shared-space addresses.  The hot kernels keep ONE opaque base address
+// in a register (smem_opaque): the compiler can neither re-derive it from %tid / kernel parameters inside the loops
+// (which it otherwise does, a dozen instructions per loop trip) nor fall back to generic addressing.
+__device__ __forceinline__ unsigned smem_opaque(const void *p) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p), r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ float4 lds_f4(unsigned a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ float2 lds_f2(unsigned a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ float lds_f1(unsigned a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned lds_u1(unsigned a) {
+    unsigned v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_f4(unsigned a, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts_f2(unsigned a, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void sts_u1(unsigned a, unsigned v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
 // Lower bound, in the same arithmetic, of ref_d2(q, p) over every p inside the box [lo, hi]:
 // per axis the clamped difference is <= |fl(q - p)| because rounding is monotone, and squaring and
 // the two additions are monotone too, so lb <= ref_d2(q, p) holds EXACTLY in float arithmetic --

@@ -65,6 +65,10 @@ namespace pcp {
 //   level_off[l] first node of level l in box_*; level_cnt[l] nodes on level l
 struct IndexView {
     const float4 *pts;
+    // the same buckets in PAIR layout for the packed-FP32 (f32x2) kernels: bucket b = float4[32] at pts2 + 32 b,
+    // float4 2m = (x[2m], x[2m+1], y[2m], y[2m+1]), float4 2m+1 = (z[2m], z[2m+1], w[2m], w[2m+1]);
+    // pad lanes x = +inf, y = z = 0, w = -1 (every distance against them is +inf, above every finite gate)
+    const float4 *pts2;
     const float4 *box_lo;
     const float4 *box_hi;
     const float4 *half;     // float4[n_leaf*4]: per bucket {lo, hi} of points 0..15 and {lo, hi} of points 16..31 (empty: +inf/-inf)
@@ -88,7 +92,7 @@ struct BatchIndex {
     int64_t level_max_cnt[kMaxLevels] = {0};
     std::vector<IndexView> h_views;
     cudaEvent_t ev_bbox = nullptr;   // optional: recorded on the build stream once the segment bounding boxes are final
-    DevBuf pts, box_lo, box_hi, half, bbox, views, keys_a, keys_b, vals_a, vals_b;
+    DevBuf pts, pts2, box_lo, box_hi, half, bbox, views, keys_a, keys_b, vals_a, vals_b;
     const IndexView *d_views() const { return views.as<IndexView>(); }
     void release();
 };

@@ -67,11 +67,13 @@ knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long
     if (ctr && lane == 0) {
         atomicAdd(ctr + 0, (unsigned long long)st.n_scan * kLeaf);
         if (LIST) atomicAdd(ctr + 7, (unsigned long long)st.n_scan * kLeaf);   // share of [0] spent on overflow groups
-        atomicAdd(ctr + 1, (unsigned long long)st.n_open * kFan);
-        atomicAdd(ctr + 2, (unsigned long long)st.n_open);
-        atomicAdd(ctr + 3, (unsigned long long)st.n_ins);
-        atomicAdd(ctr + 4, 1ull);
-        atomicAdd(ctr + 5, (unsigned long long)st.n_scan);
+        if (!LIST) {   // (overflow queries of the tiled kernel: [1..5] keep describing the tiled kernel alone)
+            atomicAdd(ctr + 1, (unsigned long long)st.n_open * kFan);
+            atomicAdd(ctr + 2, (unsigned long long)st.n_open);
+            atomicAdd(ctr + 3, (unsigned long long)st.n_ins);
+            atomicAdd(ctr + 4, 1ull);
+            atomicAdd(ctr + 5, (unsigned long long)st.n_scan);
+        }
     }
     // lane i < k writes slot i: one coalesced row per query
     const unsigned id = key_index(st.key);

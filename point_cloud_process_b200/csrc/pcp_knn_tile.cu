@@ -2,23 +2,30 @@
 // Replaces kdtree_knn_search (kdtree.py:141-172), octree_knn_search (octree.py:262-306) and
 // KNNResultSet.add_point (result_set.py:35-53) for batched query sets.
 //
-// The group walks the 32-ary AABB hierarchy ONCE for all its queries, nearest-first, pruning with
-// the exact box-to-box lower bound against the loosest k-th distance gate in the group.  Every
-// surviving bucket (32 points, 512 B) is staged in shared memory with one coalesced float4 load per
-// lane and read back as 32 broadcast LDS.128: each lane evaluates its own query against all 32
-// points (8 unfused FP32 ops per pair, the reference's operation order).  A candidate inside the
-// lane's gate is APPENDED to the lane's column of a shared-memory candidate buffer with one
-// predicated store -- no sorted insertion, no divergence in the scan loop (12 instructions per
-// distance evaluation, 8 of them FP32 pipe work: the kernel the FP32 roofline is quoted on).
-// When a column could overflow on the next scan the whole warp COMPACTS: each lane selects the
-// k-th smallest squared distance of its column with a register min/max network (2 FMNMX per slot),
-// tightens its gate to it and drops the candidates beyond it.  The first scan (gate = +inf) fills the
-// columns with 32 candidates and so bootstraps the gates.  After the walk one last compaction leaves
-// k (+ distance ties) candidates per lane, which are ranked by the packed (float32 sqrt, index) key
-// -- KNNResultSet order made canonical (distance, then index).
+// The group walks the 32-ary AABB hierarchy ONCE for all its queries, nearest-first, pruning with the
+// exact box-to-box lower bound against the loosest k-th distance gate in the group.  Every surviving
+// bucket (32 points, 512 B in PAIR layout, IndexView::pts2) is staged in shared memory with one coalesced
+// float4 load per lane and read back as broadcast LDS.128; each lane evaluates its own query against TWO
+// points per step in packed FP32 (3 FADD2 + 3 FMUL2 + 4 FADD for two distances, every element rounded once
+// per operation in the reference's order -- bit-equal to the scalar expression, 5 issue slots per evaluation
+// instead of 8).  A candidate inside the lane's gate is APPENDED to the lane's column of a shared-memory
+// candidate buffer with one predicated store -- no sorted insertion, no divergence in the scan loop.
 //
-// Query groups: for pcp_knn_self the buckets themselves (Morton-sorted cloud); for arbitrary query
-// sets the queries are first sorted by their Morton code in the index's frame (sort_queries).
+// Gates.  The FIRST bucket a group scans (its own bucket for pcp_knn_self, the bucket nearest to the group
+// otherwise) never touches the columns: its 32 distances stay in registers and a sorting network (batches of
+// 8 sorted with 19 compare-exchanges, merged into the running list with a half-cleaner + bitonic merge) yields
+// the k smallest, so every lane owns a tight gate before the walk proper starts and only the k (+ ties) survivors
+// are appended.  Later, when a column could overflow, the whole warp COMPACTS: the candidates appended since
+// the last compaction are merged into the register list with the same batch network, the gate tightens to the
+// k-th smallest squared distance, and candidates beyond it are dropped in place.  After the walk the k (+ ties)
+// survivors are ranked by the packed (float32 sqrt, index) key -- KNNResultSet order made canonical.
+//
+// Level-1 traversal state (one lower bound per child bucket) lives in a register per lane: the nearest unvisited
+// child is ONE redux.min over (bound bits | lane); the per-lane "does any lane still need this half bucket" test
+// evaluates both 16-point halves at once in packed FP32 against boxes staged pair-wise in shared memory.
+//
+// Query groups: for pcp_knn_self the buckets themselves; for arbitrary query sets the queries are first sorted by
+// Morton code in the index's frame and regrouped by the kd rule (sort_queries).
 #include <algorithm>
 #include <cfloat>
 #include <cstdio>
@@ -29,6 +36,10 @@
 #include "pcp_internal.cuh"
 
 namespace pcp {
+
+int knn_tile_device_v1(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
+                       int32_t *d_idx, float *d_dist, int32_t *d_count);
+int knn_tile_self_device_v1(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count);
 
 namespace {
 
@@ -45,28 +56,20 @@ constexpr unsigned kTestsPerSlot = 12;
 constexpr double kTailShare = 0.05;
 constexpr long long kHintGroups = 1 << 16;     // overflow groups whose gates are passed on (8 MB of scratch)
 
-// Candidate-buffer geometry per result capacity K: CAP entries per lane (a half-chunk of 4 evaluations appends
-// at most 4, a compaction leaves k + ties), WARPS groups per CTA.  The per-warp shared-memory state is
-//   CAP * 256 B candidate columns + 512 B staged bucket + 1536 B half-bucket boxes + 128 B per tree level + 32 B,
-// sized so that K <= 8 runs 28 warps per SM (7 CTAs; 72 registers) and K = 16 runs 20 (5 CTAs; 96 registers):
-// the kernel is latency-bound, and at 28 warps/SM the 3 896 groups of a KITTI scan are all resident at once.
-constexpr int kChunk = 8;                      // points loaded per step; the overflow check runs every kChunk / 2
+// Candidate-buffer geometry per result capacity K: CAP entries per lane (4 evaluations append at most 4 between two
+// overflow checks, a compaction leaves k + ties), WARPS groups per CTA.  Per-warp shared memory:
+//   CAP * 256 B candidate columns + 512 B staged bucket + 1536 B half-bucket boxes + 32 B + 128 B per level >= 2.
 template <int K> struct TileCfg { static constexpr int kCap = 21, kWarps = 4, kCtas = 7; };
 template <> struct TileCfg<16> { static constexpr int kCap = 34, kWarps = 4, kCtas = 5; };
 template <> struct TileCfg<32> { static constexpr int kCap = 68, kWarps = 2, kCtas = 8; };
-constexpr int kBoxFloats = 64 * 6;             // 64 half boxes x (lo.xyz, hi.xyz)
-__host__ __device__ constexpr size_t tile_warp_bytes(int cap, int levels) {
-    return (size_t)cap * 256 + 512 + kBoxFloats * 4 + (size_t)levels * 128 + 32;
+constexpr int kBoxBytes = 32 * 48;             // per child bucket: 3 float4 = the two half boxes, pair-interleaved
+__host__ __device__ constexpr size_t tile_warp_bytes(int cap, int upper_levels) {
+    return (size_t)cap * 256 + 512 + kBoxBytes + 32 + (size_t)upper_levels * 128;
 }
-// lower bound against a box stored as 6 floats (same arithmetic as box_lb2)
-__device__ __forceinline__ float box6_lb2(float qx, float qy, float qz, const float *b) {
-    const float2 l01 = *reinterpret_cast<const float2 *>(b), l2h0 = *reinterpret_cast<const float2 *>(b + 2),
-                 h12 = *reinterpret_cast<const float2 *>(b + 4);
-    float dx = fmaxf(fmaxf(__fsub_rn(l01.x, qx), __fsub_rn(qx, l2h0.y)), 0.f);
-    float dy = fmaxf(fmaxf(__fsub_rn(l01.y, qy), __fsub_rn(qy, h12.x)), 0.f);
-    float dz = fmaxf(fmaxf(__fsub_rn(l2h0.x, qz), __fsub_rn(qz, h12.y)), 0.f);
-    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-}
+// Euclidean distances above KNNResultSet's initial worst_dist are never accepted (result_set.py:19,37): the
+// initial gate is the squared image of 1e10, finite, so the +inf distances of pad lanes never pass it either.
+constexpr float kWorstDist0 = 1e10f;
+
 // free-running device timer in 32 ns units (wraps after 137 s; compared with wrap-safe differences)
 __device__ __forceinline__ unsigned timer32() {
     unsigned long long t;
@@ -77,6 +80,47 @@ __device__ __forceinline__ unsigned timer32() {
 // the slot then holds the distance's float bits >> 9, i.e. a value below kMinNormalBits that never prunes.
 constexpr unsigned kMinNormalBits = 0x00800000u;
 
+#define PCP_CE(a, b)                   \
+    do {                               \
+        const float _t = fminf(a, b);  \
+        b = fmaxf(a, b);               \
+        a = _t;                        \
+    } while (0)
+
+// optimal sorting networks: 5 compare-exchanges for 4 values, 19 for 8 (ascending)
+__device__ __forceinline__ void sort_net(float (&s)[4]) {
+    PCP_CE(s[0], s[1]); PCP_CE(s[2], s[3]); PCP_CE(s[0], s[2]); PCP_CE(s[1], s[3]); PCP_CE(s[1], s[2]);
+}
+__device__ __forceinline__ void sort_net(float (&s)[8]) {
+    PCP_CE(s[0], s[1]); PCP_CE(s[2], s[3]); PCP_CE(s[4], s[5]); PCP_CE(s[6], s[7]);
+    PCP_CE(s[0], s[2]); PCP_CE(s[1], s[3]); PCP_CE(s[4], s[6]); PCP_CE(s[5], s[7]);
+    PCP_CE(s[1], s[2]); PCP_CE(s[5], s[6]); PCP_CE(s[0], s[4]); PCP_CE(s[3], s[7]);
+    PCP_CE(s[1], s[5]); PCP_CE(s[2], s[6]);
+    PCP_CE(s[1], s[4]); PCP_CE(s[3], s[6]);
+    PCP_CE(s[2], s[4]); PCP_CE(s[3], s[5]);
+    PCP_CE(s[3], s[4]);
+}
+// Merge an ascending batch s[B] into the ascending list l[K], keeping the K smallest: the upper min(B, K) slots of
+// l against the batch reversed (lower half of a bitonic split: the result is a bitonic sequence holding the K
+// smallest), then a bitonic merge of K.
+template <int K, int B>
+__device__ __forceinline__ void merge_batch(float (&l)[K], const float (&s)[B]) {
+    constexpr int U = B < K ? B : K;
+#pragma unroll
+    for (int i = 0; i < U; ++i) l[K - U + i] = fminf(l[K - U + i], s[U - 1 - i]);
+#pragma unroll
+    for (int st = K / 2; st >= 1; st >>= 1) {
+#pragma unroll
+        for (int i = 0; i < K; ++i)
+            if ((i & st) == 0) PCP_CE(l[i], l[i + st]);
+    }
+}
+template <int B> __device__ __forceinline__ float batch_min(const float (&s)[B]);
+template <> __device__ __forceinline__ float batch_min<4>(const float (&s)[4]) { return fminf(min3f(s[0], s[1], s[2]), s[3]); }
+template <> __device__ __forceinline__ float batch_min<8>(const float (&s)[8]) {
+    return min3f(min3f(s[0], s[1], s[2]), min3f(s[3], s[4], s[5]), fminf(s[6], s[7]));
+}
+
 template <int K>
 struct TopK {
     unsigned long long key[K];
@@ -85,7 +129,6 @@ struct TopK {
 #pragma unroll
         for (int i = 0; i < K; ++i) key[i] = kEmptyKey;
     }
-    __device__ __forceinline__ unsigned long long worst() const { return key[K - 1]; }
     // sorted insertion of nk (a no-op when nk >= key[K-1])
     __device__ __forceinline__ void insert(unsigned long long nk) {
         bool g[K];
@@ -102,27 +145,30 @@ __global__ void __launch_bounds__(TileCfg<K>::kWarps * 32, TileCfg<K>::kCtas)
 knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm, long long nq,
                 long long stride, int k, int *__restrict__ out_idx, float *__restrict__ out_dist,
                 int *__restrict__ out_cnt, unsigned long long *__restrict__ ctr, unsigned *__restrict__ dbg,
-                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests, int trigger,
+                unsigned *__restrict__ overflow, unsigned max_scans, unsigned max_tests,
                 unsigned tail_slots, unsigned *__restrict__ sched, unsigned n_groups, float *__restrict__ hints,
-                unsigned hint_groups, unsigned warp_stride) {
-    constexpr int kTileWarps = TileCfg<K>::kWarps;
+                unsigned hint_groups, unsigned warp_bytes) {
     constexpr int kCap = TileCfg<K>::kCap;
-    // dynamic shared memory: [kTileWarps][kCap][32] candidate columns (d2 bits, index) first -- the filter's
-    // read-ahead past the last column lands in the arrays behind them --, then per warp: staged bucket,
-    // half-bucket boxes, open node per level, one row of child bounds per tree level
-    extern __shared__ uint2 s_cand[];
+    constexpr int kB = K >= 8 ? 8 : 4;                           // batch of the selection network
+    constexpr unsigned kTrigger = (unsigned)(kCap - 4) * 256u;   // a longer column could overflow during the next 4 evaluations
+    // dynamic shared memory, per warp (warp_bytes apart): candidate columns [kCap][32] of (d2 bits, index), staged
+    // bucket (pair layout), half-bucket boxes of the open level-1 node, open node per level, one row of child
+    // bounds per level >= 2.  The compaction filter's read-ahead past the last column lands in the arrays behind.
+    extern __shared__ __align__(16) unsigned char s_dyn[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // (warp_stride = tile_warp_bytes(0, levels), a kernel parameter: the per-warp arrays sit at constant offsets
-    // from one base that costs a single multiply-add to re-derive)
-    unsigned char *s_rest = reinterpret_cast<unsigned char *>(s_cand + kTileWarps * kCap * 32) + warp * warp_stride;
-    // sched (behind the overflow list): [0] next group to hand out, [1] groups finished (zeroed by the host);
-    // it and n_groups are kernel parameters so that the tail poll below holds no registers across the hot loops
-    // Persistent warps: groups are handed out dynamically, so the kernel ends within one group's work of the
-    // moment the queue runs dry instead of waiting for the unluckiest statically assigned warp.
-    // Tail hand-over (tail_slots != 0): once the queue is dry the kernel lasts as long as its slowest group
-    // while most warp slots idle (a group whose 32 queries straddle a jump of the Morton curve tests thousands of
-    // boxes and runs 10x the mean).  sched[1] counts finished groups; when fewer than tail_slots groups are still
-    // in flight the stragglers hand their queries to the warp-per-query kernel (32 warps per group instead of 1).
+    // (all accesses go through 32-bit shared-space addresses off one opaque per-lane base: pcp_device.cuh)
+    const unsigned col_addr = smem_opaque(s_dyn + (size_t)warp * warp_bytes + lane * 8);   // this lane's column: entry e at + e * 256
+    const unsigned wb = smem_opaque(s_dyn + (size_t)warp * warp_bytes);
+    constexpr unsigned kTileOff = kCap * 256, kBoxOff = kTileOff + 512, kNodeOff = kBoxOff + kBoxBytes, kLbsOff = kNodeOff + 32 - 2 * 128;
+#define TILE_A(e) (wb + kTileOff + (unsigned)(e) * 16u)
+#define BOX_A(c) (wb + kBoxOff + (unsigned)(c) * 48u)
+#define NODE_A(lv) (wb + kNodeOff + (unsigned)(lv) * 4u)
+#define LBS_A(lv, j) (wb + kLbsOff + (unsigned)(lv) * 128u + (unsigned)(j) * 4u)
+    const float inf = __uint_as_float(kInfBits);
+
+    // Persistent warps: groups are handed out dynamically (sched[0]); sched[1] counts finished groups.  Tail
+    // hand-over (tail_slots != 0): once the queue is dry and fewer than tail_slots groups are still in flight, the
+    // stragglers hand their queries to the warp-per-query kernel (32 warps per group instead of 1).
     for (;;) {
     unsigned group;
     {
@@ -139,13 +185,17 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         dbg[(size_t)group * 8 + 7] = 0u;
     }
 
-    // ---- this lane's query
+    // ---- this lane's query and the group's AABB
     float qx = 0.f, qy = 0.f, qz = 0.f;
     long long qid = -1;
+    float3 glo, ghi;
     if (SELF) {
         const float4 p = __ldg(ix.pts + (long long)group * kLeaf + lane);
-        qx = p.x; qy = p.y; qz = p.z;
         qid = (long long)(int)__float_as_uint(p.w);            // -1 on pad lanes
+        if (qid >= 0) { qx = p.x; qy = p.y; qz = p.z; }
+        const float4 lo = __ldg(ix.box_lo + group), hi = __ldg(ix.box_hi + group);   // the bucket's own box (level 0)
+        glo = make_float3(lo.x, lo.y, lo.z);
+        ghi = make_float3(hi.x, hi.y, hi.z);
     } else {
         const long long pos = (long long)group * 32 + lane;
         if (pos < nq) {
@@ -153,60 +203,42 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
             const float *q = queries + qid * stride;
             qx = __ldg(q); qy = __ldg(q + 1); qz = __ldg(q + 2);
         }
+        const bool a = qid >= 0;
+        glo.x = warp_min(a ? qx : FLT_MAX); glo.y = warp_min(a ? qy : FLT_MAX); glo.z = warp_min(a ? qz : FLT_MAX);
+        ghi.x = warp_max(a ? qx : -FLT_MAX); ghi.y = warp_max(a ? qy : -FLT_MAX); ghi.z = warp_max(a ? qz : -FLT_MAX);
     }
     const bool active = qid >= 0;
-    // group AABB over the active lanes
-    float3 glo, ghi;
-    glo.x = warp_min(active ? qx : FLT_MAX); glo.y = warp_min(active ? qy : FLT_MAX); glo.z = warp_min(active ? qz : FLT_MAX);
-    ghi.x = warp_max(active ? qx : -FLT_MAX); ghi.y = warp_max(active ? qy : -FLT_MAX); ghi.z = warp_max(active ? qz : -FLT_MAX);
     const float gcx = 0.5f * (glo.x + ghi.x), gcy = 0.5f * (glo.y + ghi.y), gcz = 0.5f * (glo.z + ghi.z);
+    const f32x2 QX = pk2(qx, qx), QY = pk2(qy, qy), QZ = pk2(qz, qz);
 
-    const float inf = __uint_as_float(kInfBits);
-    float gate = active ? inf : -1.f;                           // squared-distance gate of this lane (inactive: nothing passes)
-    unsigned group_gate = kInfBits;                             // bits of the loosest gate in the group
-    unsigned n_scan = 0, n_half = 0, n_open = 0, n_test = 0, n_round = 0;
-    bool aborted = false;
+    const float gate0 = d2_gate(kWorstDist0);
+    float gate = active ? gate0 : -1.f;                         // squared-distance gate of this lane (inactive: nothing passes)
+    unsigned group_gate = __float_as_uint(gate0);               // bits of the loosest gate in the group
+    unsigned n_scan = 0, n_half = 0, n_open = 0, n_test = 0, n_round = 0, gate_gen = 0;
+    bool aborted = false, booted = false;
     const unsigned n_active = __popc(__ballot_sync(kFullMask, active));
-
-    float4 *tile = reinterpret_cast<float4 *>(s_rest);
-    float *boxes = reinterpret_cast<float *>(s_rest + 512);   // half boxes below the open level-1 node: 6 floats at [(2*c + h) * 6]
-    uint2 *col = s_cand + warp * (kCap * 32) + lane;            // this lane's column: entry e at col[e * 32]
-    const unsigned col_addr = (unsigned)__cvta_generic_to_shared(col);
     unsigned waddr = col_addr;                                  // append position (shared-memory byte address; 256 B per entry)
 
-    // Running k smallest squared distances of this lane's column, ascending (k < K: the first K - k slots hold
-    // a sentinel below every distance, so that l[K-1] is always the k-th smallest).
+    // Running k smallest squared distances of this lane, ascending (k < K: the first K - k slots hold a sentinel
+    // below every distance, so that l[K-1] is always the k-th smallest).
     float l[K];
 #pragma unroll
     for (int i = 0; i < K; ++i) l[i] = i < K - k ? -1.f : inf;
     int n_old = 0;                                              // entries of the column already merged into l[]
 
-    // Merge the candidates appended since the last compaction into l[] (register min/max network), tighten the
-    // gates to the k-th smallest squared distance and drop the candidates beyond it.  Warp-uniform loops.
-    auto compact = [&]() {
-        const int cnt = (int)((waddr - col_addr) >> 8);
-        const int n_new = __reduce_max_sync(kFullMask, cnt - n_old);
-        const int nmax = __reduce_max_sync(kFullMask, cnt);
-        const uint2 *src_new = col + n_old * 32;
-#pragma unroll 2
-        for (int e = 0; e < n_new; ++e) {
-            float v = n_old + e < cnt ? __uint_as_float(src_new[e * 32].x) : inf;
-            // the lists tighten as the merge proceeds: a round in which no lane's candidate still beats its
-            // k-th distance changes nothing
-            if (!__any_sync(kFullMask, v < l[K - 1])) continue;
-            ++n_round;
-#pragma unroll
-            for (int i = 0; i < K; ++i) {
-                const float lo = fminf(v, l[i]);
-                v = fmaxf(v, l[i]);
-                l[i] = lo;
-            }
+    auto append = [&](float d2, float w) {
+        if (d2 <= gate) {
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(d2), "f"(w) : "memory");
+            waddr += 256;
         }
-        // candidates whose float32 sqrt can still tie the k-th distance stay (canonical (distance, index) order)
+    };
+    // In-place filter: gate <- k-th smallest squared distance (candidates whose float32 sqrt can still tie it
+    // stay: canonical order), candidates beyond it are dropped.  The write position never passes the read
+    // position, so loading 4 entries ahead of the stores they may alias is safe (and lets the loads overlap); the
+    // loads may run up to 3 entries past the longest column (they land in the arrays behind the columns), the
+    // `< end` test discards them.
+    auto filter = [&](int nmax) {
         if (l[K - 1] < inf) gate = fminf(gate, d2_gate(__fsqrt_rn(l[K - 1])));
-        // In-place filter.  The write position never passes the read position, so loading 4 entries ahead of the
-        // stores they may alias is safe (and lets the loads overlap); the loads may run up to 3 entries past the
-        // longest column (the buffer is padded for it), the `< end` test discards them.
         unsigned w = col_addr;
         const unsigned end = waddr;
 #pragma unroll 1
@@ -225,9 +257,36 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         waddr = w;
         n_old = (int)((w - col_addr) >> 8);
         group_gate = __reduce_max_sync(kFullMask, active ? __float_as_uint(gate) : 0u);
+        ++gate_gen;
     };
 
-    // Tail hand-over poll (every 4th scan / open): queue dry and fewer than tail_slots groups still in flight?
+    // Merge the candidates appended since the last compaction into l[] (batch network), tighten the gates and
+    // drop the candidates beyond them.  Warp-uniform loops.
+    auto compact = [&]() {
+        const int cnt = (int)((waddr - col_addr) >> 8);
+        const int n_new = __reduce_max_sync(kFullMask, cnt - n_old);
+        const int nmax = __reduce_max_sync(kFullMask, cnt);
+        unsigned src_new = col_addr + (unsigned)n_old * 256u;
+        int rem = cnt - n_old;                                  // this lane's candidates not merged yet
+#pragma unroll 1
+        for (int b = 0; b < n_new; b += kB, rem -= kB, src_new += kB * 256u) {
+            float s[kB];
+#pragma unroll
+            for (int i = 0; i < kB; ++i) {
+                s[i] = inf;
+                if (i < rem) s[i] = lds_f1(src_new + i * 256u); // (predicated: never reads past this lane's entries)
+            }
+            // the lists tighten as the merge proceeds: a batch in which no lane's candidate beats its k-th
+            // distance changes nothing
+            if (!__any_sync(kFullMask, batch_min<kB>(s) < l[K - 1])) continue;
+            ++n_round;
+            sort_net(s);
+            merge_batch<K, kB>(l, s);
+        }
+        filter(nmax);
+    };
+
+    // Tail hand-over poll: queue dry and fewer than tail_slots groups still in flight?
     auto poll_tail = [&]() {
         if (!tail_slots) return;
         uint2 w = make_uint2(0u, 0u);
@@ -236,44 +295,107 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         if (__shfl_sync(kFullMask, (w.x >= n_groups && n_groups - w.y < tail_slots) ? 1 : 0, 0)) aborted = true;
     };
 
-    // Exact per-lane lower bounds against the boxes of bucket c's two 16-point halves (shared-memory broadcast):
-    // bit h is set when ANY lane can still use half h.
+    // Exact per-lane lower bounds against the boxes of bucket c's two 16-point halves, both at once in packed
+    // FP32 (box_lb2's arithmetic, element by element): bit h is set when ANY lane can still use half h.
     auto bucket_needed = [&](int c) -> unsigned {
         ++n_test;
-        const bool a = box6_lb2(qx, qy, qz, boxes + c * 12) <= gate;
-        const bool b = box6_lb2(qx, qy, qz, boxes + c * 12 + 6) <= gate;
+        // b0 = (loA.x, loB.x, loA.y, loB.y), b1 = (loA.z, loB.z, hiA.x, hiB.x), b2 = (hiA.y, hiB.y, hiA.z, hiB.z)
+        const float4 b0 = lds_f4(BOX_A(c)), b1 = lds_f4(BOX_A(c) + 16u), b2 = lds_f4(BOX_A(c) + 32u);
+        float ax, bx, ay, by, az, bz, t0, t1, u0, u1;
+        upk2(sub2(pk2(b0.x, b0.y), QX), t0, t1);
+        upk2(sub2(QX, pk2(b1.z, b1.w)), u0, u1);
+        ax = max3f(t0, u0, 0.f); bx = max3f(t1, u1, 0.f);
+        upk2(sub2(pk2(b0.z, b0.w), QY), t0, t1);
+        upk2(sub2(QY, pk2(b2.x, b2.y)), u0, u1);
+        ay = max3f(t0, u0, 0.f); by = max3f(t1, u1, 0.f);
+        upk2(sub2(pk2(b1.x, b1.y), QZ), t0, t1);
+        upk2(sub2(QZ, pk2(b2.z, b2.w)), u0, u1);
+        az = max3f(t0, u0, 0.f); bz = max3f(t1, u1, 0.f);
+        const f32x2 X = pk2(ax, bx), Y = pk2(ay, by), Z = pk2(az, bz);
+        float x0, x1, y0, y1, z0, z1;
+        upk2(mul2(X, X), x0, x1);
+        upk2(mul2(Y, Y), y0, y1);
+        upk2(mul2(Z, Z), z0, z1);
+        const bool a = __fadd_rn(__fadd_rn(x0, y0), z0) <= gate;
+        const bool b = __fadd_rn(__fadd_rn(x1, y1), z1) <= gate;
         return (__any_sync(kFullMask, a) ? 1u : 0u) | (__any_sync(kFullMask, b) ? 2u : 0u);
     };
-    // Scan the needed halves of one bucket whose points `pv` (lane j = point j) are already in registers.
+
+    // First bucket of the group: its distances go through the batch network straight from registers (kB at a
+    // time: evaluate, sort, merge into l[], tighten the gate) and a batch's candidates are appended against the gate
+    // it has just produced -- about 2k entries reach the columns instead of 32, and every lane owns its k-th
+    // distance among 32 real points before the walk proper starts.
+    auto bootstrap = [&]() {
+#pragma unroll 1
+        for (int g = 0; g < 32; g += kB) {
+            float d[kB];
+#pragma unroll
+            for (int m = 0; m < kB / 2; ++m) {
+                const float4 a = lds_f4(TILE_A(g + 2 * m)), b = lds_f4(TILE_A(g + 2 * m + 1));
+                ref_d2_pair(QX, QY, QZ, pk2(a.x, a.y), pk2(a.z, a.w), pk2(b.x, b.y), d[2 * m], d[2 * m + 1]);
+            }
+            {
+                float s[kB];
+#pragma unroll
+                for (int i = 0; i < kB; ++i) s[i] = d[i];
+                sort_net(s);
+                merge_batch<K, kB>(l, s);
+            }
+            if (l[K - 1] < inf) gate = fminf(gate, d2_gate(__fsqrt_rn(l[K - 1])));
+#pragma unroll
+            for (int m = 0; m < kB / 2; ++m) {
+                const float2 w = lds_f2(TILE_A(g + 2 * m + 1) + 8u);
+                append(d[2 * m], w.x);
+                append(d[2 * m + 1], w.y);
+            }
+            // columns that could overflow during the next batch: drop what the tightened gates no longer admit; still
+            // too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
+            if (g + kB < 32 && __any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kB) * 256u)) {
+                filter(__reduce_max_sync(kFullMask, (int)((waddr - col_addr) >> 8)));
+                if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kB) * 256u)) { aborted = true; break; }
+            }
+        }
+        n_round += 32 / kB;
+        filter(__reduce_max_sync(kFullMask, (int)((waddr - col_addr) >> 8)));
+        if (__any_sync(kFullMask, waddr > col_addr + kTrigger)) aborted = true;
+    };
+
+    // Scan the needed halves of one bucket whose pair-layout row `pv` (one float4 per lane) is already in registers.
     auto scan_bucket = [&](const float4 pv, unsigned halves) {
         ++n_scan;
+        __syncwarp();
+        sts_f4(TILE_A(lane), pv);
+        __syncwarp();
+        if (!booted) {
+            booted = true;
+            n_half += 2;
+            bootstrap();
+            return;
+        }
         n_half += __popc(halves);
-        __syncwarp();
-        tile[lane] = pv;
-        __syncwarp();
-        // 8 points at a time: the broadcast loads are issued ahead of the (possibly aliasing) candidate stores; the
-        // columns are checked after every 4 evaluations, so only 4 entries of headroom are reserved
-        const int j_end = (halves & 2u) ? 32 : 16;             // (halves != 0: at least one of the two is scanned)
+        // 8 points (= 8 float4 of the pair layout) at a time: the broadcast loads are issued ahead of the (possibly
+        // aliasing) candidate stores; the columns are checked after every 4 evaluations
+        const int e_end = (halves & 2u) ? 32 : 16;             // (halves != 0: at least one of the two is scanned)
 #pragma unroll 1
-        for (int j0 = (halves & 1u) ? 0 : 16; j0 < j_end; j0 += kChunk) {
-            float4 p[kChunk];
+        for (int e0 = (halves & 1u) ? 0 : 16; e0 < e_end; e0 += 8) {
+            float4 p[8];
 #pragma unroll
-            for (int j = 0; j < kChunk; ++j) p[j] = tile[j0 + j];
+            for (int j = 0; j < 8; ++j) p[j] = lds_f4(TILE_A(e0 + j));
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
 #pragma unroll
-                for (int j = h * (kChunk / 2); j < (h + 1) * (kChunk / 2); ++j) {
-                    const float d2 = ref_d2(qx, qy, qz, p[j].x, p[j].y, p[j].z);
-                    if (d2 <= gate) {                            // NaN pads never pass
-                        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(d2), "f"(p[j].w) : "memory");
-                        waddr += 256;
-                    }
+                for (int m = 2 * h; m < 2 * h + 2; ++m) {
+                    float d0, d1;
+                    ref_d2_pair(QX, QY, QZ, pk2(p[2 * m].x, p[2 * m].y), pk2(p[2 * m].z, p[2 * m].w),
+                                pk2(p[2 * m + 1].x, p[2 * m + 1].y), d0, d1);
+                    append(d0, p[2 * m + 1].z);
+                    append(d1, p[2 * m + 1].w);
                 }
                 // a column that could overflow during the next 4 evaluations: compact all columns of the warp
-                if (__any_sync(kFullMask, waddr > col_addr + (unsigned)trigger * 256)) {
+                if (__any_sync(kFullMask, waddr > col_addr + kTrigger)) {
                     compact();
                     // still too long = a mass of exactly tied distances: leave the group to the warp-per-query kernel
-                    if (__any_sync(kFullMask, waddr > col_addr + (unsigned)(kCap - kChunk / 2) * 256)) aborted = true;
+                    if (__any_sync(kFullMask, waddr > col_addr + kTrigger)) aborted = true;
                 }
                 if (aborted) break;      // (before the second half appends past the end of the columns)
             }
@@ -281,91 +403,131 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         }
     };
 
+    // ---- upper levels (>= 2): child bounds of the open node per level in shared memory
     const int top_level = ix.n_levels - 1;      // >= 1 for every non-empty index (pcp_build.cu)
-    if (top_level > 0) {
-        unsigned *nodes = reinterpret_cast<unsigned *>(s_rest + 512 + kBoxFloats * 4) - 1;               // [lv - 1]
-        unsigned(*lbs)[32] = reinterpret_cast<unsigned(*)[32]>(s_rest + 512 + kBoxFloats * 4 + 32) - 1;   // row lv - 1
-        auto open_node = [&](int lv, unsigned node) {
-            ++n_open;
-            if (lv == 1 && (n_open & 3u) == 0u) poll_tail();
-            if (lane == 0) nodes[lv] = node;
+    auto open_upper = [&](int lv, unsigned node) {
+        ++n_open;
+        if (lane == 0) sts_u1(NODE_A(lv), node);
+        const long long c = (long long)node * kFan + lane;
+        unsigned bits = kDone;
+        if (c < ix.level_cnt[lv - 1]) {
+            const long long b = ix.level_off[lv - 1] + c;
+            const float4 lo = __ldg(ix.box_lo + b), hi = __ldg(ix.box_hi + b);
+            bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
+            if (bits == 0u) {   // overlaps the group box: order by centre distance (a hint, never used to prune)
+                const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
+                bits = __float_as_uint(cx * cx + cy * cy + cz * cz) >> 9;
+            }
+        }
+        sts_u1(LBS_A(lv, lane), bits);
+        __syncwarp();
+    };
+    // nearest unvisited child of the open node on `lv` that can still matter: -1 if none.  Marks it visited.
+    auto pick_upper = [&](int lv) -> int {
+        const unsigned mine = lds_u1(LBS_A(lv, lane));
+        const unsigned best = __reduce_min_sync(kFullMask, mine);
+        // exact prune: every point below a child is at least `best` away from every query of the group
+        // (slots below kMinNormalBits are ordering hints of overlapping children or denormal bounds: kept)
+        if (best == kDone || (best > group_gate && best >= kMinNormalBits)) return -1;
+        const int sel = __ffs(__ballot_sync(kFullMask, mine == best)) - 1;
+        if (lane == sel) sts_u1(LBS_A(lv, lane), kDone);
+        __syncwarp();
+        return sel;
+    };
+
+    // ---- one level-1 node: its 32 buckets.  Lane j keeps (lower bound of bucket j, low 5 bits = j) in a register.
+    auto process_l1 = [&](unsigned node) {
+        ++n_open;
+        if ((n_open & 3u) == 0u) poll_tail();
+        unsigned key = kDone;
+        {
             const long long c = (long long)node * kFan + lane;
-            unsigned bits = kDone;
-            if (c < ix.level_cnt[lv - 1]) {
-                float4 lo, hi;
-                if (lv == 1) {
-                    // buckets: the boxes of the two halves; the bucket's bound is the smaller of theirs
-                    const float4 *h = ix.half + c * 4;
-                    const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
-                    float2 *bw = reinterpret_cast<float2 *>(boxes + lane * 12);
-                    bw[0] = make_float2(alo.x, alo.y); bw[1] = make_float2(alo.z, ahi.x); bw[2] = make_float2(ahi.y, ahi.z);
-                    bw[3] = make_float2(blo.x, blo.y); bw[4] = make_float2(blo.z, bhi.x); bw[5] = make_float2(bhi.y, bhi.z);
-                    bits = min(__float_as_uint(boxbox_lb2(glo, ghi, alo, ahi)), __float_as_uint(boxbox_lb2(glo, ghi, blo, bhi)));
-                    lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
-                    hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
-                } else {
-                    const long long b = ix.level_off[lv - 1] + c;
-                    lo = __ldg(ix.box_lo + b); hi = __ldg(ix.box_hi + b);
-                    bits = __float_as_uint(boxbox_lb2(glo, ghi, lo, hi));
-                }
+            if (c < ix.level_cnt[0]) {
+                // the boxes of the bucket's two halves; the bucket's bound is the smaller of theirs
+                const float4 *h = ix.half + c * 4;
+                const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
+                sts_f4(BOX_A(lane), make_float4(alo.x, blo.x, alo.y, blo.y));
+                sts_f4(BOX_A(lane) + 16u, make_float4(alo.z, blo.z, ahi.x, bhi.x));
+                sts_f4(BOX_A(lane) + 32u, make_float4(ahi.y, bhi.y, ahi.z, bhi.z));
+                unsigned bits = min(__float_as_uint(boxbox_lb2(glo, ghi, alo, ahi)), __float_as_uint(boxbox_lb2(glo, ghi, blo, bhi)));
                 if (bits == 0u) {   // overlaps the group box: order by centre distance (a hint, never used to prune)
-                    const float cx = 0.5f * (lo.x + hi.x) - gcx, cy = 0.5f * (lo.y + hi.y) - gcy, cz = 0.5f * (lo.z + hi.z) - gcz;
+                    const float cx = 0.5f * (fminf(alo.x, blo.x) + fmaxf(ahi.x, bhi.x)) - gcx;
+                    const float cy = 0.5f * (fminf(alo.y, blo.y) + fmaxf(ahi.y, bhi.y)) - gcy;
+                    const float cz = 0.5f * (fminf(alo.z, blo.z) + fmaxf(ahi.z, bhi.z)) - gcz;
                     bits = __float_as_uint(cx * cx + cy * cy + cz * cz) >> 9;
                 }
+                // (clearing the low mantissa bits only lowers the bound: still exact to prune with)
+                key = (bits & ~31u) | (unsigned)lane;
             }
-            lbs[lv][lane] = bits;
-            __syncwarp();
+        }
+        __syncwarp();
+        // nearest unvisited bucket that some lane still needs: -1 if none
+        auto next_needed = [&](unsigned &halves) -> int {
+            for (;;) {
+                const unsigned best = __reduce_min_sync(kFullMask, key);
+                const unsigned bound = best & ~31u;
+                if (best == kDone || (bound > group_gate && bound >= kMinNormalBits)) return -1;
+                const int sel = (int)(best & 31u);
+                if (lane == sel) key = kDone;
+                if ((halves = bucket_needed(sel)) != 0u) return sel;
+            }
         };
-        // nearest unvisited child of the open node on `lv` that can still matter: -1 if none.  Marks it visited.
-        auto pick = [&](int lv) -> int {
-            const unsigned mine = lbs[lv][lane];
-            const unsigned best = __reduce_min_sync(kFullMask, mine);
-            // exact prune: every point below a child is at least `best` away from every query of the group
-            // (slots below kMinNormalBits are ordering hints of overlapping children or denormal bounds: kept)
-            if (best == kDone || (best > group_gate && best >= kMinNormalBits)) return -1;
-            const int sel = __ffs(__ballot_sync(kFullMask, mine == best)) - 1;
-            if (lane == sel) lbs[lv][lane] = kDone;
-            __syncwarp();
-            return sel;
-        };
+        // Software pipeline: the points of the NEXT needed bucket in visiting order are loaded while the current
+        // one is scanned (the order depends only on the box bounds; the gates only shrink, so a bucket rejected
+        // now stays rejected; one accepted before the gates tightened is tested again).
+        const float4 *base = ix.pts2 + (long long)node * kFan * kLeaf + lane;
+        unsigned halves = 0;
+        int sel = next_needed(halves);
+        if (sel < 0) return;
+        float4 cur = __ldg(base + sel * kLeaf);
+        for (;;) {
+            unsigned nxt_halves = 0;
+            int nxt = booted ? next_needed(nxt_halves) : -2;    // (before the bootstrap every bucket passes: decide after it)
+            float4 pf = cur;
+            if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
+            const unsigned gen = gate_gen;
+            scan_bucket(cur, halves);
+            if ((n_scan & 3u) == 0u) poll_tail();
+            if (aborted || n_scan > max_scans || n_test > max_tests) { aborted = true; return; }
+            if (nxt == -2 || (nxt >= 0 && gate_gen != gen)) {
+                // the gates tightened during the scan: test the prefetched bucket again, move on if it dropped out
+                if (nxt >= 0) nxt_halves = bucket_needed(nxt);
+                if (nxt < 0 || nxt_halves == 0u) {
+                    nxt = next_needed(nxt_halves);
+                    if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
+                }
+            }
+            if (nxt < 0) return;
+            sel = nxt;
+            halves = nxt_halves;
+            cur = pf;
+        }
+    };
+
+    {
         int level = top_level;
-        open_node(top_level, 0u);
-        while (!aborted) {
-            int sel = pick(level);
-            if (sel < 0) {
-                if (level == top_level) break;
-                ++level;
-                continue;
+        bool have_l1 = top_level == 1;
+        unsigned l1node = 0;
+        if (!have_l1) open_upper(top_level, 0u);
+        for (;;) {
+            if (!have_l1) {
+                const int sel = pick_upper(level);
+                if (sel < 0) {
+                    if (level == top_level) break;
+                    ++level;
+                    continue;
+                }
+                const unsigned child = lds_u1(NODE_A(level)) * kFan + sel;
+                if (level > 2) {
+                    --level;
+                    open_upper(level, child);
+                    continue;
+                }
+                l1node = child;
             }
-            if (level > 1) {
-                const unsigned child = nodes[level] * kFan + sel;
-                --level;
-                open_node(level, child);
-                continue;
-            }
-            // level 1: buckets.  Software pipeline: the points of the NEXT needed bucket in visiting order are
-            // loaded while the current one is scanned (the order depends only on the box bounds; the gates only
-            // shrink, so a bucket rejected now stays rejected).
-            const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
-            unsigned halves = 0;
-            while (sel >= 0 && !(halves = bucket_needed(sel))) sel = pick(1);
-            if (sel < 0) continue;
-            float4 cur = __ldg(base + sel * kLeaf);
-            while (true) {
-                int nxt = pick(1);
-                unsigned nxt_halves = 0;
-                while (nxt >= 0 && !(nxt_halves = bucket_needed(nxt))) nxt = pick(1);
-                float4 pf = cur;
-                if (nxt >= 0) pf = __ldg(base + nxt * kLeaf);
-                scan_bucket(cur, halves);
-                if ((n_scan & 3u) == 0u) poll_tail();
-                if (nxt < 0) break;
-                sel = nxt;
-                halves = nxt_halves;
-                cur = pf;
-                if (aborted || n_scan > max_scans || n_test > max_tests) break;
-            }
-            if (aborted || n_scan > max_scans || n_test > max_tests) { aborted = true; break; }
+            process_l1(l1node);
+            have_l1 = false;
+            if (aborted || top_level == 1) break;
         }
     }
     if (aborted) {
@@ -379,7 +541,7 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         }
         // the gates reached so far seed the searches of the warp-per-query kernel
         pos = __shfl_sync(kFullMask, pos, 0);
-        if (pos < hint_groups) hints[(size_t)pos * 32 + lane] = gate;
+        if (pos < hint_groups) hints[(size_t)pos * 32 + lane] = active ? gate : inf;
         if (ctr && lane == 0) {
             atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
             atomicAdd(ctr + 6, 1ull);
@@ -398,8 +560,8 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         const int nmax = __reduce_max_sync(kFullMask, cnt);
         for (int e = 0; e < nmax; ++e) {
             if (e < cnt) {
-                const uint2 ent = col[e * 32];
-                top.insert(pack_key(__fsqrt_rn(__uint_as_float(ent.x)), ent.y));
+                const float2 ent = lds_f2(col_addr + (unsigned)e * 256u);
+                top.insert(pack_key(__fsqrt_rn(ent.x), __float_as_uint(ent.y)));
             }
         }
     }
@@ -434,6 +596,10 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
     }
     __syncwarp();
     }   // next group
+#undef TILE_A
+#undef BOX_A
+#undef NODE_A
+#undef LBS_A
 }
 
 template <bool SELF>
@@ -456,7 +622,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
     const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
     static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS"),
-                      *e_trig = getenv("PCP_TILE_TRIGGER"), *e_tail = getenv("PCP_TILE_TAIL");   // developer overrides
+                      *e_tail = getenv("PCP_TILE_TAIL");   // developer overrides
     const double tail_share = e_tail ? atof(e_tail) : kTailShare;   // share of the warp slots; 0 = off
     const unsigned max_scans = e_scans ? (unsigned)atoi(e_scans) : small_grid ? kScansPerSlot * std::max(K, 4) : 0xffffffffu;
     const unsigned max_tests = e_tests ? (unsigned)atoi(e_tests) : small_grid ? kTestsPerSlot * std::max(K, 4) : 0xffffffffu;
@@ -469,10 +635,11 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
 #define PCP_TILE(KK)                                                                                                   \
     do {                                                                                                               \
         constexpr int W = TileCfg<KK>::kWarps, CAP = TileCfg<KK>::kCap;                                                \
-        const int n_lv = v.n_levels > 1 ? v.n_levels - 1 : 1;                                                          \
-        const size_t smem = (size_t)W * tile_warp_bytes(CAP, n_lv);                                                   \
+        const int n_up = v.n_levels > 2 ? v.n_levels - 2 : 0;                                                          \
+        const size_t wbytes = tile_warp_bytes(CAP, n_up);                                                              \
+        const size_t smem = (size_t)W * wbytes;                                                                        \
         static int occ_by_levels[kMaxLevels + 1] = {0};   /* resident CTAs per SM, per tree depth */                   \
-        int &ctas_per_sm = occ_by_levels[n_lv];                                                                        \
+        int &ctas_per_sm = occ_by_levels[n_up];                                                                        \
         if (!ctas_per_sm) {                                                                                            \
             static size_t attr_smem = 0;                                                                               \
             if (smem > attr_smem) {                                                                                    \
@@ -484,17 +651,14 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
             if (const char *e = getenv("PCP_TILE_CTAS")) ctas_per_sm = std::max(1, std::min(ctas_per_sm, atoi(e)));     \
             if (getenv("PCP_VERBOSE")) fprintf(stderr, "knn_tile_kernel<%d>: %zu B smem, %d CTAs/SM\n", KK, smem, ctas_per_sm); \
         }                                                                                                              \
-        /* compaction trigger: a column longer than this could overflow during the next chunk of evaluations */       \
-        const int trig = e_trig ? std::min(atoi(e_trig), CAP - kChunk / 2) : CAP - kChunk / 2;                         \
         /* persistent grid: every resident warp slot, or fewer when there are not that many groups */                  \
         const unsigned grid = (unsigned)std::min<long long>((n_groups + W - 1) / W, (long long)ctx->sm_count * ctas_per_sm); \
         const unsigned tail_slots = (unsigned)(tail_share * (double)grid * W);                                        \
         knn_tile_kernel<KK, SELF><<<grid, W * 32, smem, ctx->stream>>>(v, d_q, d_perm, nq, stride, k, d_idx, d_dist,   \
                                                                        d_count, ctr, dbg, overflow, max_scans,         \
-                                                                       max_tests, trig, tail_slots,                    \
+                                                                       max_tests, tail_slots,                          \
                                                                        overflow + sched_at, (unsigned)n_groups, hints, \
-                                                                       hint_groups,                                    \
-                                                                       (unsigned)tile_warp_bytes(0, n_lv));            \
+                                                                       hint_groups, (unsigned)wbytes);                 \
     } while (0)
     cudaEvent_t ev_end = nullptr;
     if (ctx->time_kernels) {
@@ -528,14 +692,21 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, hints, hint_groups, k, d_idx, d_dist, d_count);
 }
 
+bool use_v1() {
+    static const bool v1 = getenv("PCP_TILE_V1") != nullptr;   // developer A/B switch: the round-1 kernel
+    return v1;
+}
+
 }  // namespace
 
 int knn_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
                     int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (use_v1()) return knn_tile_device_v1(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_count);
     return launch_tile<false>(ix, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count);
 }
 
 int knn_tile_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
+    if (use_v1()) return knn_tile_self_device_v1(ix, k, d_idx, d_dist, d_count);
     return launch_tile<true>(ix, nullptr, nullptr, ix->n, 3, k, d_idx, d_dist, d_count);
 }
 
