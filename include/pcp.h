@@ -132,6 +132,18 @@ PCP_API int pcp_knn(pcp_index *index, const float *queries, int64_t nq, int64_t 
  * sort because the buckets already are the query groups. */
 PCP_API int pcp_knn_self(pcp_index *index, int k, int mem, int32_t *idx, float *dist, int32_t *count);
 
+/* Brute force over the WHOLE indexed cloud -- the check the reference prints beside its tree searches,
+ * np.argsort(np.linalg.norm(db - query, axis=1))[:k]            kdtree.py:234-238, octree.py:352-356 --
+ * as a device kernel (tiles of the cloud streamed through shared memory by TMA bulk copies, every (query, point)
+ * pair evaluated, no spatial pruning).  Same outputs and tie rule as pcp_knn.  It shares no traversal code with
+ * the search kernels: the test-suite uses it as the on-device second oracle for full-size query sets. */
+PCP_API int pcp_knn_bruteforce(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats, int k, int mem,
+                               int32_t *idx, float *dist, int32_t *count);
+/* counts[i] = number of indexed points with float32 dist <= radius, by the same exhaustive kernel (the count
+ * RadiusNNResultSet.size() reports, result_set.py:72-73). */
+PCP_API int pcp_radius_count_bruteforce(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats,
+                                        float radius, int mem, int64_t *counts);
+
 /* ---- fixed-radius search -----------------------------------------------------------------------
  * Replaces kdtree_radius_search                              kdtree.py:176-208
  *      and octree_radius_search / octree_radius_search_fast  octree.py:166-259
@@ -251,6 +263,48 @@ PCP_API int pcp_iss_keypoints(pcp_index *index, float radius, double lambda21, d
  * radius).  labels: n x int32 (host or device per `mem`); n_clusters (host, may be NULL).  For an index built
  * with PCP_DEVICE the cloud passed to the build must still be alive. */
 PCP_API int pcp_dbscan(pcp_index *index, float radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters);
+
+/* ---- multi-GPU: one process per GPU, work sharded where the path shards -------------------------
+ * The reference has no distributed code on this path (single process, single thread); these entries are the
+ * B200-native extension BASELINE.json configs 4 and 5 name.
+ *   registration pairs: independent -> a contiguous range of pairs per rank (balanced by points), NO collective.
+ *   queries of a large cloud: split per rank; the reference cloud is REPLICATED -- every rank contributes a shard,
+ *     ONE ncclAllGather (NVLink / NVSwitch) rebuilds the whole cloud on every GPU, every rank builds the same
+ *     (deterministic) index and searches its own queries.  This all-gather is the only collective of the library.
+ * NCCL is bound at run time (dlopen libnccl.so.2); world == 1 needs no NCCL at all.
+ * Bootstrap: rank 0 calls pcp_multi_unique_id and hands the PCP_MULTI_ID_BYTES bytes to every rank by any means
+ * (a TCP socket, a file, the launcher's store); every rank then calls pcp_multi_create with the same id. */
+#define PCP_MULTI_ID_BYTES 128
+typedef struct pcp_multi pcp_multi;
+PCP_API int pcp_multi_unique_id(void *id128);
+PCP_API int pcp_multi_create(pcp_ctx *ctx, int rank, int world, const void *id128, pcp_multi **out);
+PCP_API int pcp_multi_destroy(pcp_multi *m);
+PCP_API int pcp_multi_info(const pcp_multi *m, int *rank, int *world, int *nccl_version, int *comm_nranks);
+/* This rank's shard of the reference cloud (shards may differ in length) -> all-gather (rank order) -> index build
+ * over the gathered cloud.  n_total (may be NULL): rows of the gathered cloud.  Collective: every rank must call. */
+PCP_API int pcp_multi_set_reference(pcp_multi *m, const float *shard_xyz, int64_t n_shard, int64_t stride_floats,
+                                    int mem, int64_t *n_total);
+/* Device time of the last pcp_multi_set_reference: the all-gather (incl. gap closing for ragged shards) and the
+ * index build, CUDA events on the context stream. */
+PCP_API int pcp_multi_last_timing(const pcp_multi *m, double *allgather_ms, double *build_ms);
+/* The gathered cloud (device pointer, rows, stride) and the rows every rank contributed (world entries). */
+PCP_API int pcp_multi_reference(const pcp_multi *m, const float **device_xyz, int64_t *n_total, int64_t *stride_floats,
+                                int64_t *shard_rows);
+PCP_API pcp_index *pcp_multi_index(pcp_multi *m);
+/* kNN of THIS rank's queries against the gathered cloud (indices = rows of the gathered cloud): pcp_knn contract. */
+PCP_API int pcp_multi_knn(pcp_multi *m, const float *queries, int64_t nq, int64_t stride_floats, int k, int mem,
+                          int32_t *idx, float *dist, int32_t *count);
+/* Contiguous pair range [first, last) of `rank`: boundaries at equal shares of the total point count. Host only. */
+PCP_API int pcp_multi_pair_range(const int64_t *src_offsets, const int64_t *tgt_offsets, int64_t n_pairs, int rank,
+                                 int world, int64_t *first, int64_t *last);
+/* pcp_icp_batch over this rank's range of a batch every rank describes identically (all arrays are the GLOBAL ones;
+ * PCP_HOST: only the rank's own rows are read / uploaded).  Output rows outside [first_pair, last_pair) are not
+ * touched; no communication. */
+PCP_API int pcp_multi_icp_batch(pcp_multi *m, const pcp_icp_params *params, int64_t n_pairs, const float *src_xyz,
+                                const int64_t *src_offsets, const float *tgt_xyz, const int64_t *tgt_offsets,
+                                int64_t stride_floats, int mem, const double *T_init, double *T_last, double *T_total,
+                                int32_t *iterations, int32_t *status, double *diff_log, int64_t *first_pair,
+                                int64_t *last_pair);
 
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */

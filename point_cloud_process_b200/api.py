@@ -7,6 +7,8 @@ import numpy as np
 from . import native
 
 _tls = threading.local()
+MAX_K = 32                 # PCP_MAX_K: register top-k width of the kNN kernels
+EMPTY_DIST = 1e10          # PCP_KNN_EMPTY_DIST (result_set.py:19-22)
 
 
 def default_context(device=0):
@@ -49,7 +51,56 @@ class SearchIndex:
     def knn(self, queries, k):
         """-> (idx (Q,k) int32, dist (Q,k) float32 Euclidean, count (Q,) int32); rows ascending by
         (distance, index); slots >= count hold (1e10, 0) like KNNResultSet (result_set.py:19-22)."""
-        return self._ix.knn(_as_cloud(queries, "queries"), int(k))
+        q, k = _as_cloud(queries, "queries"), int(k)
+        if k < 1:
+            raise ValueError("k must be >= 1")
+        if k <= MAX_K:
+            return self._ix.knn(q, k)
+        return self._knn_wide(q, k)
+
+    def _knn_wide(self, q, k):
+        """k > 32, the register top-k width of the search kernels (PCP_MAX_K): KNNResultSet accepts any capacity
+        (result_set.py:16-24), so the same result is assembled from two GPU searches -- the 32-NN distance of a
+        query bounds from below the radius that holds k neighbours; a radius search (exact float32 distances,
+        rows sorted by (distance, index)) is repeated with a growing radius for the queries still short of
+        min(k, n) hits, and the first k entries of each row are the answer.  Host work is bookkeeping only."""
+        nq, n = len(q), len(self)
+        idx = np.zeros((nq, k), np.int32)
+        dist = np.full((nq, k), EMPTY_DIST, np.float32)
+        cnt = np.zeros(nq, np.int32)
+        kk = min(k, n)
+        if nq == 0 or kk == 0:
+            return idx, dist, cnt
+        _, d32, _ = self._ix.knn(q, MAX_K)
+        # k-th distance estimate from the 32nd: volume grows with the cube of the radius
+        floor = 1e-4 * float(np.ptp(self.db, axis=0).max()) + 1e-30     # (a query sitting on > 32 duplicates)
+        r = np.maximum(d32[:, MAX_K - 1].astype(np.float64), floor) * (kk / MAX_K) ** (1.0 / 3.0) * 1.25
+        pending = np.arange(nq)
+        while len(pending):
+            rad = float(np.float32(r[pending].max()))
+            if not np.isfinite(rad):
+                rad = float(np.finfo(np.float32).max)
+            off, ridx, rdist = self._ix.radius(q[pending], rad, True)
+            got = np.diff(off)
+            done = got >= kk
+            for j in np.nonzero(done)[0]:
+                i = pending[j]
+                idx[i, :kk] = ridx[off[j]:off[j] + kk]
+                dist[i, :kk] = rdist[off[j]:off[j] + kk]
+                cnt[i] = kk
+            pending = pending[~done]
+            r[pending] = np.minimum(2.0 * rad, np.finfo(np.float32).max)
+        return idx, dist, cnt
+
+    def knn_bruteforce(self, queries, k):
+        """Same contract as knn(), computed by the exhaustive device kernel (the reference's own check,
+        np.argsort(np.linalg.norm(db - query, axis=1))[:k], kdtree.py:234-238): every (query, point) pair, no
+        spatial pruning.  The on-device second oracle of the test-suite; k <= 32."""
+        return self._ix.knn_bruteforce(_as_cloud(queries, "queries"), int(k))
+
+    def radius_count_bruteforce(self, queries, radius):
+        """Per-query number of points with float32 dist <= radius, by the exhaustive kernel."""
+        return self._ix.radius_count_bruteforce(_as_cloud(queries, "queries"), float(np.float32(radius)))
 
     def knn_self(self, k):
         """kNN of every indexed point against the cloud itself, original order."""

@@ -133,6 +133,37 @@ class Index {
         rethrow();
         return py::make_tuple(idx, dist, cnt);
     }
+    // exhaustive kernel (kdtree.py:234-238 as a device kernel): the second oracle
+    py::tuple knn_bruteforce(const py::object &queries, int k) {
+        Cloud q(queries, "queries");
+        if (k < 1) throw py::value_error("k must be >= 1");
+        auto idx = result_array<int32_t>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto dist = result_array<float>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto cnt = result_array<int32_t>({(py::ssize_t)q.n});
+        {
+            py::gil_scoped_release rel;
+            check_nogil(pcp_knn_bruteforce(ix_, q.data(), q.n, q.stride, k, PCP_HOST, idx.mutable_data(),
+                                           dist.mutable_data(), cnt.mutable_data()), "pcp_knn_bruteforce");
+        }
+        rethrow();
+        return py::make_tuple(idx, dist, cnt);
+    }
+    py::array_t<int64_t> radius_count_bruteforce(const py::object &queries, double radius) {
+        Cloud q(queries, "queries");
+        py::array_t<int64_t> counts((py::ssize_t)q.n);
+        check(pcp_radius_count_bruteforce(ix_, q.data(), q.n, q.stride, (float)radius, PCP_HOST, counts.mutable_data()),
+              "pcp_radius_count_bruteforce");
+        return counts;
+    }
+    void knn_bruteforce_device(uintptr_t q, int64_t nq, int64_t stride, int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
+        check(pcp_knn_bruteforce(ix_, reinterpret_cast<const float *>(q), nq, stride, k, PCP_DEVICE,
+                                 reinterpret_cast<int32_t *>(idx), reinterpret_cast<float *>(dist),
+                                 reinterpret_cast<int32_t *>(cnt)), "pcp_knn_bruteforce");
+    }
+    void radius_count_bruteforce_device(uintptr_t q, int64_t nq, int64_t stride, double radius, uintptr_t counts) {
+        check(pcp_radius_count_bruteforce(ix_, reinterpret_cast<const float *>(q), nq, stride, (float)radius, PCP_DEVICE,
+                                          reinterpret_cast<int64_t *>(counts)), "pcp_radius_count_bruteforce");
+    }
     py::tuple knn_self(int k) {
         if (k < 1) throw py::value_error("k must be >= 1");
         const int64_t n = size();
@@ -237,6 +268,134 @@ class Index {
     const char *what_ = "";
     std::string msg_;
 };
+
+// Multi-GPU handle (one process per GPU): pcp_multi_* of include/pcp.h
+class Multi {
+   public:
+    Multi(std::shared_ptr<Context> ctx, int rank, int world, const py::object &id) : ctx_(std::move(ctx)) {
+        std::string raw;
+        if (!id.is_none()) raw = py::cast<std::string>(py::bytes(id));
+        if (world > 1 && raw.size() != PCP_MULTI_ID_BYTES) throw py::value_error("unique id must be 128 bytes");
+        check(pcp_multi_create(ctx_->get(), rank, world, world > 1 ? raw.data() : nullptr, &m_), "pcp_multi_create");
+    }
+    ~Multi() { pcp_multi_destroy(m_); }
+    Multi(const Multi &) = delete;
+    static py::bytes unique_id() {
+        char id[PCP_MULTI_ID_BYTES];
+        check(pcp_multi_unique_id(id), "pcp_multi_unique_id");
+        return py::bytes(id, sizeof id);
+    }
+    py::dict info() const {
+        int r = 0, w = 0, v = 0, n = 0;
+        check(pcp_multi_info(m_, &r, &w, &v, &n), "pcp_multi_info");
+        py::dict d;
+        d["rank"] = r; d["world"] = w; d["nccl_version"] = v; d["comm_nranks"] = n;
+        return d;
+    }
+    int64_t set_reference(const py::object &shard) {
+        Cloud c(shard, "reference shard");
+        int64_t n = 0;
+        int rc;
+        std::string msg;
+        {
+            py::gil_scoped_release rel;
+            rc = pcp_multi_set_reference(m_, c.data(), c.n, c.stride, PCP_HOST, &n);
+            if (rc != PCP_OK) msg = pcp_last_error();
+        }
+        if (rc != PCP_OK) throw std::runtime_error("pcp_multi_set_reference: " + msg);
+        return n;
+    }
+    int64_t set_reference_device(uintptr_t p, int64_t n_shard, int64_t stride) {
+        int64_t n = 0;
+        check(pcp_multi_set_reference(m_, reinterpret_cast<const float *>(p), n_shard, stride, PCP_DEVICE, &n),
+              "pcp_multi_set_reference");
+        return n;
+    }
+    py::tuple last_timing() const {
+        double a = 0, b = 0;
+        check(pcp_multi_last_timing(m_, &a, &b), "pcp_multi_last_timing");
+        return py::make_tuple(a, b);
+    }
+    py::tuple reference() const {
+        const float *p = nullptr;
+        int64_t n = 0, st = 0;
+        int w = 0;
+        check(pcp_multi_info(m_, nullptr, &w, nullptr, nullptr), "pcp_multi_info");
+        std::vector<int64_t> rows((size_t)w);
+        check(pcp_multi_reference(m_, &p, &n, &st, rows.data()), "pcp_multi_reference");
+        return py::make_tuple(reinterpret_cast<uintptr_t>(p), n, st, rows);
+    }
+    py::tuple knn(const py::object &queries, int k) {
+        Cloud q(queries, "queries");
+        if (k < 1) throw py::value_error("k must be >= 1");
+        auto idx = result_array<int32_t>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto dist = result_array<float>({(py::ssize_t)q.n, (py::ssize_t)k});
+        auto cnt = result_array<int32_t>({(py::ssize_t)q.n});
+        check(pcp_multi_knn(m_, q.data(), q.n, q.stride, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(),
+                            cnt.mutable_data()), "pcp_multi_knn");
+        return py::make_tuple(idx, dist, cnt);
+    }
+    void knn_device(uintptr_t q, int64_t nq, int64_t stride, int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
+        check(pcp_multi_knn(m_, reinterpret_cast<const float *>(q), nq, stride, k, PCP_DEVICE,
+                            reinterpret_cast<int32_t *>(idx), reinterpret_cast<float *>(dist),
+                            reinterpret_cast<int32_t *>(cnt)), "pcp_multi_knn");
+    }
+    void knn_bruteforce_device(uintptr_t q, int64_t nq, int64_t stride, int k, uintptr_t idx, uintptr_t dist, uintptr_t cnt) {
+        check(pcp_knn_bruteforce(pcp_multi_index(m_), reinterpret_cast<const float *>(q), nq, stride, k, PCP_DEVICE,
+                                 reinterpret_cast<int32_t *>(idx), reinterpret_cast<float *>(dist),
+                                 reinterpret_cast<int32_t *>(cnt)), "pcp_knn_bruteforce");
+    }
+    // global batch (packed clouds + offsets) -> dict with this rank's range and its rows of the results
+    py::dict icp_batch(const py::object &src, const i64_array &src_off, const py::object &tgt, const i64_array &tgt_off,
+                       const f64_array &T_init, int max_iteration, double R_diff_thres, double t_diff_thres,
+                       double dist_thres, bool first_iter_broadcast) {
+        Cloud s(src, "source"), t(tgt, "target");
+        if (s.stride != t.stride) throw py::value_error("source and target must have the same number of columns");
+        const int64_t P = src_off.size() - 1;
+        if (P < 0 || tgt_off.size() != src_off.size()) throw py::value_error("offset arrays must both have n_pairs+1 entries");
+        if (T_init.size() != P * 16) throw py::value_error("T_init must be (n_pairs, 4, 4)");
+        pcp_icp_params prm;
+        pcp_icp_default_params(&prm);
+        prm.max_iteration = max_iteration;
+        prm.R_diff_thres = R_diff_thres;
+        prm.t_diff_thres = t_diff_thres;
+        prm.dist_thres = dist_thres;
+        prm.first_iter_broadcast = first_iter_broadcast ? 1 : 0;
+        py::array_t<double> T_last({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4}), T_total({(py::ssize_t)P, (py::ssize_t)4, (py::ssize_t)4});
+        py::array_t<int32_t> iters((py::ssize_t)P), status((py::ssize_t)P);
+        std::fill_n(T_last.mutable_data(), P * 16, 0.0);
+        std::fill_n(T_total.mutable_data(), P * 16, 0.0);
+        std::fill_n(iters.mutable_data(), P, 0);
+        std::fill_n(status.mutable_data(), P, -1);
+        int64_t lo = 0, hi = 0;
+        int rc;
+        std::string msg;
+        {
+            py::gil_scoped_release rel;
+            rc = pcp_multi_icp_batch(m_, &prm, P, s.data(), src_off.data(), t.data(), tgt_off.data(), s.stride, PCP_HOST,
+                                     T_init.data(), T_last.mutable_data(), T_total.mutable_data(), iters.mutable_data(),
+                                     status.mutable_data(), nullptr, &lo, &hi);
+            if (rc != PCP_OK) msg = pcp_last_error();
+        }
+        if (rc != PCP_OK) throw std::runtime_error("pcp_multi_icp_batch: " + msg);
+        py::dict d;
+        d["first_pair"] = lo; d["last_pair"] = hi;
+        d["T_last"] = T_last; d["T_total"] = T_total; d["iterations"] = iters; d["status"] = status;
+        return d;
+    }
+
+   private:
+    std::shared_ptr<Context> ctx_;
+    pcp_multi *m_ = nullptr;
+};
+
+py::tuple multi_pair_range(const i64_array &src_off, const i64_array &tgt_off, int rank, int world) {
+    const int64_t P = src_off.size() - 1;
+    if (P < 0 || tgt_off.size() != src_off.size()) throw py::value_error("offset arrays must both have n_pairs+1 entries");
+    int64_t lo = 0, hi = 0;
+    check(pcp_multi_pair_range(src_off.data(), tgt_off.data(), P, rank, world, &lo, &hi), "pcp_multi_pair_range");
+    return py::make_tuple(lo, hi);
+}
 
 // icp_batch: packed clouds + offsets -> dict(T_last, T_total, iterations, status[, diff_log])
 py::dict icp_batch(std::shared_ptr<Context> ctx, const py::object &src, const i64_array &src_off, const py::object &tgt,
@@ -398,6 +557,10 @@ PYBIND11_MODULE(_pcp, m) {
         .def("stats", &Index::stats)
         .def("knn", &Index::knn, py::arg("queries"), py::arg("k"))
         .def("knn_self", &Index::knn_self, py::arg("k"))
+        .def("knn_bruteforce", &Index::knn_bruteforce, py::arg("queries"), py::arg("k"))
+        .def("radius_count_bruteforce", &Index::radius_count_bruteforce, py::arg("queries"), py::arg("radius"))
+        .def("knn_bruteforce_device", &Index::knn_bruteforce_device)
+        .def("radius_count_bruteforce_device", &Index::radius_count_bruteforce_device)
         .def("normals", &Index::normals, py::arg("k") = 5)
         .def("normals_device", &Index::normals_device)
         .def("dbscan", &Index::dbscan, py::arg("radius") = 0.5f, py::arg("min_pts") = 10)
@@ -409,6 +572,24 @@ PYBIND11_MODULE(_pcp, m) {
         .def("radius", &Index::radius, py::arg("queries"), py::arg("radius"), py::arg("sorted") = false)
         .def("radius_count_device", &Index::radius_count_device)
         .def("radius_fill_device", &Index::radius_fill_device);
+
+    py::class_<Multi>(m, "Multi")
+        .def(py::init<std::shared_ptr<Context>, int, int, const py::object &>(), py::arg("ctx"), py::arg("rank"),
+             py::arg("world"), py::arg("unique_id") = py::none())
+        .def_static("unique_id", &Multi::unique_id)
+        .def("info", &Multi::info)
+        .def("set_reference", &Multi::set_reference, py::arg("shard"))
+        .def("set_reference_device", &Multi::set_reference_device)
+        .def("last_timing", &Multi::last_timing)
+        .def("reference", &Multi::reference)
+        .def("knn", &Multi::knn, py::arg("queries"), py::arg("k"))
+        .def("knn_device", &Multi::knn_device)
+        .def("knn_bruteforce_device", &Multi::knn_bruteforce_device)
+        .def("icp_batch", &Multi::icp_batch, py::arg("source"), py::arg("source_offsets"), py::arg("target"),
+             py::arg("target_offsets"), py::arg("T_init"), py::arg("max_iteration") = 100, py::arg("R_diff_thres") = 0.5,
+             py::arg("t_diff_thres") = 0.5, py::arg("dist_thres") = 5.0, py::arg("first_iter_broadcast") = true);
+    m.def("multi_pair_range", &multi_pair_range, py::arg("source_offsets"), py::arg("target_offsets"), py::arg("rank"),
+          py::arg("world"));
 
     m.def("icp_batch", &icp_batch, py::arg("ctx"), py::arg("source"), py::arg("source_offsets"), py::arg("target"),
           py::arg("target_offsets"), py::arg("T_init"), py::arg("max_iteration") = 100, py::arg("R_diff_thres") = 0.5,

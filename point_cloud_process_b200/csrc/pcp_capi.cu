@@ -453,6 +453,62 @@ int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int
     return PCP_OK;
 }
 
+int pcp_knn_bruteforce(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int k, int mem, int32_t *idx,
+                       float *dist, int32_t *count) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce: index is NULL");
+    PCP_TRY(check_cloud("pcp_knn_bruteforce", queries, nq, stride, mem));
+    PCP_TRY(check_k(k));
+    if (nq > 0 && (!idx || !dist)) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce: idx/dist is NULL");
+    if (nq == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const float *d_q = queries;
+    int32_t *d_idx = idx, *d_cnt = count;
+    float *d_dist = dist;
+    const size_t nres = (size_t)nq * (size_t)k;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        d_q = ctx->scratch[6].as<float>();
+        PCP_TRY(ctx->scratch[7].ensure(nres * 8 + sizeof(int32_t) * (size_t)nq));
+        d_idx = ctx->scratch[7].as<int32_t>();
+        d_dist = reinterpret_cast<float *>(d_idx + nres);
+        d_cnt = reinterpret_cast<int32_t *>(d_dist + nres);
+    }
+    PCP_TRY(knn_brute_device(ix, d_q, nq, stride, k, d_idx, d_dist, d_cnt));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
+        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
+        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_radius_count_bruteforce(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, float radius, int mem,
+                                int64_t *counts) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_radius_count_bruteforce: index is NULL");
+    PCP_TRY(check_cloud("pcp_radius_count_bruteforce", queries, nq, stride, mem));
+    if (nq > 0 && !counts) return fail(PCP_ERR_INVALID, "pcp_radius_count_bruteforce: counts is NULL");
+    if (std::isnan(radius)) return fail(PCP_ERR_INVALID, "pcp_radius_count_bruteforce: radius is NaN");
+    if (nq == 0) return PCP_OK;
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const float *d_q = queries;
+    int64_t *d_cnt = counts;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], queries, sizeof(float) * (size_t)nq * (size_t)stride));
+        d_q = ctx->scratch[6].as<float>();
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(int64_t) * (size_t)nq));
+        d_cnt = ctx->scratch[7].as<int64_t>();
+    }
+    PCP_TRY(radius_count_brute_device(ix, d_q, nq, stride, exact_d2_threshold(radius), reinterpret_cast<long long *>(d_cnt)));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, counts, d_cnt, sizeof(int64_t) * (size_t)nq));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
 int pcp_knn_self(pcp_index *ix, int k, int mem, int32_t *idx, float *dist, int32_t *count) {
     if (!ix) return fail(PCP_ERR_INVALID, "pcp_knn_self: index is NULL");
     if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_knn_self: mem must be PCP_HOST or PCP_DEVICE");

@@ -186,6 +186,12 @@ int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t
 int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
                        long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist);
 
+// brute force over the whole cloud (pcp_brute.cu): the on-device second oracle
+float exact_d2_threshold(float r);
+int knn_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, int k, int32_t *d_idx, float *d_dist,
+                     int32_t *d_count);
+int radius_count_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float d2max, long long *d_counts);
+
 // icp (pcp_icp.cu)
 int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, const float *d_src,
                      const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,

@@ -23,11 +23,6 @@
 
 namespace pcp {
 
-namespace {
-
-constexpr int kWarpsPerCta = 8;
-constexpr int kStack = kMaxLevels * kFan;
-
 // Largest float x with sqrtf(x) <= r (r >= 0, finite).  Returns -1 for r < 0 (nothing matches).
 float exact_d2_threshold(float r) {
     if (!(r >= 0.f)) return -1.f;
@@ -42,6 +37,11 @@ float exact_d2_threshold(float r) {
     }
     return x;
 }
+
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kStack = kMaxLevels * kFan;
 
 // LIST = false: warp w of the grid takes query w.
 // LIST = true:  persistent warps drain the hand-over list of the tiled kernel (pcp_radius_tile.cu): list[0] =

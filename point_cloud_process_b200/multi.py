@@ -1,14 +1,21 @@
-"""Multi-GPU plumbing: one process per GPU (torch.distributed), work sharded where the path shards.
+"""Multi-GPU plumbing: one process per GPU, work sharded where the path shards.
 
-    registration pairs      independent -> contiguous ranges of pairs per rank, NO collective on the data
-                            path; the (P,4,4) results are gathered on the host side afterwards
+    registration pairs       independent -> contiguous ranges of pairs per rank (balanced by points), NO
+                             collective on the data path; every rank keeps the rows of its own range
     queries of a large cloud independent given the whole reference cloud -> queries split per rank, the
-                            reference cloud REPLICATED: each rank holds a shard, ONE all-gather (NCCL over
-                            NVLink) rebuilds the full cloud on every GPU, each rank builds its own index
-                            (the build is deterministic) and searches its own queries
+                             reference cloud REPLICATED: each rank holds a shard, ONE ncclAllGather (NVLink)
+                             rebuilds the full cloud on every GPU, each rank builds its own index (the build
+                             is deterministic) and searches its own queries
 
-torch is used for the process group and device buffers only; search / ICP go through the C ABI.
+Everything goes through the C ABI (pcp_multi_* of include/pcp.h: NCCL is bound inside libpcp_b200.so); there is
+no torch in here.  The 128-byte NCCL id of rank 0 reaches the other ranks over a plain TCP socket
+(`exchange_unique_id`, MASTER_ADDR / MASTER_PORT + 1 of the launcher by default) or by any means of the caller.
 """
+import os
+import socket
+import struct
+import time
+
 import numpy as np
 
 
@@ -21,7 +28,7 @@ def shard_range(n, rank, world):
 
 def shard_pairs_by_points(sizes, world):
     """Contiguous pair ranges balanced by the number of points: sizes[i] = points of pair i.
-    Returns world+1 boundaries."""
+    Returns world+1 boundaries (the rule of pcp_multi_pair_range)."""
     sizes = np.asarray(sizes, np.int64)
     total = int(sizes.sum())
     cum = np.concatenate([[0], np.cumsum(sizes)])
@@ -33,75 +40,120 @@ def shard_pairs_by_points(sizes, world):
     return bounds
 
 
-def all_gather_cloud(local, group=None):
-    """All-gather row shards of a cloud (torch tensor (n_r, C), CPU for gloo / CUDA for nccl; shards may
-    differ in length) -> the full (sum n_r, C) tensor on every rank, rank order."""
-    import torch
-    import torch.distributed as dist
-    world = dist.get_world_size(group)
-    n_local = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
-    sizes = [torch.zeros_like(n_local) for _ in range(world)]
-    dist.all_gather(sizes, n_local, group=group)
-    sizes = [int(s.item()) for s in sizes]
-    n_max = max(sizes)
-    padded = local
-    if local.shape[0] != n_max:
-        padded = torch.zeros((n_max,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-        padded[:local.shape[0]] = local
-    out = torch.empty((world * n_max,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(out, padded.contiguous(), group=group)
-    if all(s == n_max for s in sizes):
-        return out
-    return torch.cat([out[r * n_max:r * n_max + sizes[r]] for r in range(world)], dim=0)
+def env_rank_world():
+    """(rank, world, local_rank) from the launcher's environment (torchrun / mpirun style), 0/1/0 when absent."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def _recv_exact(conn, n):
+    buf = b""
+    while len(buf) < n:
+        part = conn.recv(n - len(buf))
+        if not part:
+            raise ConnectionError("peer closed the rendezvous socket")
+        buf += part
+    return buf
+
+
+def exchange_bytes(payload, rank, world, addr=None, port=None, timeout=120.0):
+    """Rank 0 hands `payload` (bytes) to every other rank over TCP; returns the payload on every rank.
+    A one-shot star rendezvous: rank 0 listens on (addr, port), every other rank connects and reads."""
+    if world == 1:
+        return payload
+    addr = addr or os.environ.get("MASTER_ADDR", "127.0.0.1")
+    port = int(port or int(os.environ.get("MASTER_PORT", "29500")) + 1)
+    if rank == 0:
+        with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as srv:
+            srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+            srv.bind((addr, port))
+            srv.listen(world)
+            srv.settimeout(timeout)
+            for _ in range(world - 1):
+                conn, _ = srv.accept()
+                with conn:
+                    conn.sendall(struct.pack("<I", len(payload)) + payload)
+        return payload
+    deadline = time.monotonic() + timeout
+    while True:
+        try:
+            with socket.create_connection((addr, port), timeout=5.0) as conn:
+                n = struct.unpack("<I", _recv_exact(conn, 4))[0]
+                return _recv_exact(conn, n)
+        except (ConnectionRefusedError, socket.timeout, OSError):
+            if time.monotonic() > deadline:
+                raise
+            time.sleep(0.05)
+
+
+def exchange_unique_id(rank, world, addr=None, port=None):
+    """The NCCL unique id of rank 0 (pcp_multi_unique_id) on every rank; None for a single rank."""
+    if world == 1:
+        return None
+    from . import native
+    uid = native.Multi.unique_id() if rank == 0 else b""
+    return exchange_bytes(uid, rank, world, addr, port)
+
+
+def create(rank=None, world=None, device=None, unique_id=None, ctx=None, addr=None, port=None):
+    """pcp_multi_create for this process: rank / world default to the launcher's environment, the device to
+    LOCAL_RANK, the unique id to a TCP exchange with rank 0."""
+    from . import native
+    from .api import default_context
+    e_rank, e_world, e_local = env_rank_world()
+    rank = e_rank if rank is None else rank
+    world = e_world if world is None else world
+    device = e_local if device is None else device
+    ctx = ctx or default_context(device)
+    if world > 1 and unique_id is None:
+        unique_id = exchange_unique_id(rank, world, addr, port)
+    return native.Multi(ctx, rank, world, unique_id)
 
 
 class ShardedSearch:
     """Query-sharded exact search over a replicated reference cloud (BASELINE config 5)."""
 
-    def __init__(self, reference_shard, device=None, group=None, ctx=None):
-        import torch
-
-        from . import native
-        from .api import default_context
-        self.device = torch.cuda.current_device() if device is None else device
-        self.ctx = ctx or default_context(self.device)
-        shard = torch.as_tensor(reference_shard, dtype=torch.float32)
-        if not shard.is_cuda:
-            shard = shard.cuda(self.device)
-        self.reference = all_gather_cloud(shard.contiguous(), group)        # the one collective of this path
-        torch.cuda.current_stream().synchronize()
-        self.index = native.Index(self.ctx, self.reference.data_ptr(), self.reference.shape[0], self.reference.shape[1])
+    def __init__(self, reference_shard, multi=None, **kw):
+        self.multi = multi or create(**kw)
+        shard = np.ascontiguousarray(np.asarray(reference_shard, dtype=np.float32))
+        self.n_total = self.multi.set_reference(shard)          # the one collective of this path + the index build
+        self.allgather_ms, self.build_ms = self.multi.last_timing()
 
     def knn(self, queries, k):
-        """queries: this rank's shard, (Q, 3) CUDA tensor.  Returns CUDA tensors (idx, dist, count); indices
-        refer to rows of the gathered reference cloud."""
-        import torch
-        q = torch.as_tensor(queries, dtype=torch.float32)
-        if not q.is_cuda:
-            q = q.cuda(self.device)
-        q = q.contiguous()
-        n = q.shape[0]
-        idx = torch.empty((n, k), dtype=torch.int32, device=q.device)
-        dist = torch.empty((n, k), dtype=torch.float32, device=q.device)
-        cnt = torch.empty(n, dtype=torch.int32, device=q.device)
-        torch.cuda.current_stream().synchronize()
-        self.index.knn_device(q.data_ptr(), n, q.shape[1], k, idx.data_ptr(), dist.data_ptr(), cnt.data_ptr())
-        self.ctx.synchronize()
-        return idx, dist, cnt
+        """queries: this rank's shard (Q, 3).  Returns (idx, dist, count); indices refer to rows of the gathered
+        reference cloud (rank order)."""
+        return self.multi.knn(np.ascontiguousarray(np.asarray(queries, dtype=np.float32)), int(k))
 
 
-def icp_batch_sharded(sources, targets, T_init=None, group=None, run=None, **kw):
-    """Pair-sharded batched ICP: every rank registers its contiguous range of pairs (balanced by points) with
-    no communication, then the small per-pair results are all-gathered as Python objects.  `run` defaults to
-    the GPU icp_batch; tests on CPU inject a stand-in to exercise the sharding logic."""
-    import torch.distributed as dist
-    if run is None:
-        from .api import icp_batch as run
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
-    bounds = shard_pairs_by_points([len(s) + len(t) for s, t in zip(sources, targets)], world)
-    lo, hi = bounds[rank], bounds[rank + 1]
-    T0 = None if T_init is None else np.asarray(T_init)[lo:hi]
-    local = run(sources[lo:hi], targets[lo:hi], T_init=T0, **kw)
-    parts = [None] * world
-    dist.all_gather_object(parts, {k: np.asarray(v) for k, v in local.items()}, group=group)
-    return {k: np.concatenate([p[k] for p in parts], axis=0) for k in parts[0]}
+def icp_batch_sharded(sources, targets, T_init=None, multi=None, run=None, rank=None, world=None,
+                      max_iteration=100, R_diff_thres=0.5, t_diff_thres=0.5, dist_thres=5.0, first_iter_broadcast=True):
+    """Pair-sharded batched ICP: this rank registers its contiguous range of pairs (balanced by points) with no
+    communication.  Returns (first_pair, last_pair, results of that range).  `run` replaces the GPU solver for
+    CPU tests of the sharding logic: run(sources[lo:hi], targets[lo:hi], T_init=...) -> dict of arrays."""
+    P = len(sources)
+    if len(targets) != P:
+        raise ValueError("sources and targets must have the same length")
+    if run is not None:
+        e_rank, e_world, _ = env_rank_world()
+        rank = e_rank if rank is None else rank
+        world = e_world if world is None else world
+        bounds = shard_pairs_by_points([len(s) + len(t) for s, t in zip(sources, targets)], world)
+        lo, hi = bounds[rank], bounds[rank + 1]
+        T0 = None if T_init is None else np.asarray(T_init)[lo:hi]
+        return lo, hi, run(sources[lo:hi], targets[lo:hi], T_init=T0)
+    from .api import _as_cloud
+    multi = multi or create(rank=rank, world=world)
+    src = [_as_cloud(s, "source") for s in sources]
+    tgt = [_as_cloud(t, "target") for t in targets]
+    so = np.zeros(P + 1, np.int64)
+    to = np.zeros(P + 1, np.int64)
+    if P:
+        so[1:] = np.cumsum([len(s) for s in src])
+        to[1:] = np.cumsum([len(t) for t in tgt])
+    sp = np.concatenate(src) if P else np.zeros((0, 3), np.float32)
+    tp = np.concatenate(tgt) if P else np.zeros((0, 3), np.float32)
+    T0 = np.tile(np.eye(4), (P, 1, 1)) if T_init is None else np.ascontiguousarray(np.asarray(T_init, np.float64).reshape(P, 4, 4))
+    out = multi.icp_batch(sp, so, tp, to, T0, int(max_iteration), float(R_diff_thres), float(t_diff_thres),
+                          float(dist_thres), bool(first_iter_broadcast))
+    lo, hi = int(out.pop("first_pair")), int(out.pop("last_pair"))
+    return lo, hi, {k: np.asarray(v)[lo:hi] for k, v in out.items()}

@@ -63,8 +63,19 @@ class KNNResultSet:
     def _load(self, dist, idx, count, comparisons=0):
         """Take one row of a batched GPU search: `dist`/`idx` of length capacity, ascending
         (distance, index), slots >= count already (1e10, 0) as result_set.py:19-22 leaves them."""
-        self.count = int(count)
-        self.dist_index_list = [DistIndex(d, int(i)) for d, i in zip(dist, idx)]
+        count = int(count)
+        row = [DistIndex(d, int(i)) for d, i in zip(dist[:count], idx[:count])]
+        if self.count:
+            # the set already holds candidates (earlier add_point calls or an earlier search on the same object):
+            # the reference accumulates through add_point (result_set.py:35-53) -- feed the row through it, in
+            # its (distance, index) order, so that ties behave as they do there
+            counter = self.comparison_counter
+            for d in row:
+                self.add_point(d.distance, d.index)
+            self.comparison_counter = counter + int(comparisons)
+            return
+        self.count = len(row)
+        self.dist_index_list = row + [DistIndex(EMPTY_DIST, 0) for _ in range(self.capacity - len(row))]
         self.worst_dist = self.dist_index_list[self.capacity - 1].distance if self.capacity else EMPTY_DIST
         self.comparison_counter += int(comparisons)
 

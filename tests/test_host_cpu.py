@@ -207,3 +207,23 @@ def test_front_end_modules_mirror_reference_names():
     for name in ("get_P_from_Rt", "is_registration_successful", "get_P_diff", "read_oxford_bin", "read_reg_results",
                  "reg_result_row_to_array", "evaluate_rt"):
         assert hasattr(evaluate_rt, name)
+
+
+def test_knn_result_set_load_merges_like_add_point():
+    """KNNResultSet._load on a set that already holds candidates merges (result_set.py:35-53 semantics: a later
+    arrival goes behind equal distances, the list stays bounded)."""
+    from point_cloud_process_b200.result_set import KNNResultSet
+    rng = np.random.default_rng(3)
+    for cap in (1, 4, 8):
+        rows = [np.sort(rng.integers(0, 12, cap).astype(np.float32)) for _ in range(3)]
+        ids = [rng.integers(0, 1000, cap) for _ in range(3)]
+        a, b = KNNResultSet(cap), KNNResultSet(cap)
+        for d, i in zip(rows, ids):
+            a._load(d, i, cap)
+            for x, y in zip(d, i):
+                b.add_point(x, int(y))
+        assert [(x.distance, x.index) for x in a.dist_index_list] == [(x.distance, x.index) for x in b.dist_index_list]
+        assert a.count == b.count and a.worst_dist == b.worst_dist
+    part = KNNResultSet(4)
+    part._load(np.float32([1, 2, 1e10, 1e10]), [7, 8, 0, 0], 2)
+    assert part.count == 2 and part.worst_dist == 1e10 and part.dist_index_list[2].index == 0

@@ -169,7 +169,9 @@ def test_shape_errors(pcp, kitti):
     with pytest.raises(ValueError):
         pcp.SearchIndex(kitti[:100]).knn(kitti[:4], 0)
     with pytest.raises(RuntimeError):
-        pcp.SearchIndex(kitti[:100]).knn(kitti[:4], 64)     # k > PCP_MAX_K: unsupported, loudly
+        pcp.native.Index(pcp.default_context(), kitti[:100]).knn(kitti[:4], 64)   # C ABI: k > PCP_MAX_K is unsupported, loudly
+    idx, dist, cnt = pcp.SearchIndex(kitti[:100]).knn(kitti[:4], 64)   # the shim assembles wide rows (tests/test_shims_gpu.py)
+    assert idx.shape == (4, 64) and (cnt == 64).all()
 
 
 def test_knn_uniform_1m_properties(pcp):
@@ -339,3 +341,74 @@ def test_radius_large_query_set_paths_agree():
     for o in outs[1:]:
         for key in outs[0]:
             assert np.array_equal(outs[0][key], o[key]), key
+
+
+def test_bruteforce_kernel_vs_cpu_oracle(pcp):
+    """The exhaustive device kernel (second oracle, kdtree.py:234-238) against the CPU brute force: every list
+    width, k below the width, fewer points than k, duplicates, queries outside the cloud, tile boundaries."""
+    from oracle import knn_oracle
+    rng = np.random.default_rng(31)
+    for n in (1, 31, 33, 1024, 1025, 5000):
+        db = (rng.random((n, 3)) * np.float32([30, 30, 4])).astype(np.float32)
+        if n > 100:
+            db[7:47] = db[7]                                    # 40 exact duplicates
+        q = np.concatenate([db[rng.choice(n, min(n, 150))], (rng.random((50, 3)) * 60 - 15).astype(np.float32)])
+        ix = pcp.SearchIndex(db)
+        for k in (1, 3, 8, 11, 16, 32):
+            idx, dist, cnt = ix.knn_bruteforce(q, k)
+            b_dist, b_idx, b_cnt = knn_oracle.bruteforce_knn(db, q, k, threads=8)
+            assert np.array_equal(dist, b_dist) and np.array_equal(idx, b_idx.astype(np.int32)) and np.array_equal(cnt, b_cnt), (n, k)
+        for r in (0.0, 0.7, 3.0):
+            c = ix.radius_count_bruteforce(q, r)
+            off, _, _ = ix.radius(q, r)
+            assert np.array_equal(c, np.diff(off)), (n, r)
+
+
+@pytest.mark.parametrize("name", ["kitti", "uniform1m"])
+def test_full_set_parity_vs_bruteforce_kernel(pcp, kitti, name):
+    """FULL-set parity at config size (C1: every KITTI point, k = 8 and r = 1.0; C3: 1 M uniform points, k = 16 and
+    r = 0.5): the tiled kernels against the exhaustive device kernel, every query, bit-equal indices and float32
+    distances -- where round 1 could only sample 256 queries against the CPU."""
+    if name == "kitti":
+        db, k, r = kitti, 8, 1.0
+    else:
+        db, k, r = (np.random.default_rng(1234).random((1_000_000, 3)) * 25.4).astype(np.float32), 16, 0.5
+    ix = pcp.SearchIndex(db)
+    idx, dist, cnt = ix.knn(db, k)
+    b_idx, b_dist, b_cnt = ix.knn_bruteforce(db, k)
+    assert np.array_equal(dist, b_dist) and np.array_equal(cnt, b_cnt)
+    assert np.array_equal(idx, b_idx)
+    s_idx, s_dist, _ = ix.knn_self(k)
+    assert np.array_equal(s_idx, b_idx) and np.array_equal(s_dist, b_dist)
+    off, _, _ = ix.radius(db, r)
+    assert np.array_equal(np.diff(off), ix.radius_count_bruteforce(db, r))
+
+
+def test_multi_single_rank_and_two_rank_c5(pcp):
+    """pcp_multi_* (C ABI): world 1 needs no NCCL and must equal the plain index; with >= 2 GPUs a scaled config 5
+    runs under torchrun (ncclAllGather of the reference shards inside the library, queries sharded) and every
+    sampled query equals the exhaustive device kernel."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from point_cloud_process_b200 import multi
+    rng = np.random.default_rng(17)
+    ref = (rng.random((50_000, 3)) * 20).astype(np.float32)
+    q = (rng.random((9000, 3)) * 20).astype(np.float32)
+    m = multi.create(rank=0, world=1, device=0)
+    assert m.set_reference(ref) == len(ref) and m.info()["comm_nranks"] == 1
+    idx, dist, cnt = m.knn(q, 16)
+    i2, d2, c2 = pcp.SearchIndex(ref).knn(q, 16)
+    assert np.array_equal(idx, i2) and np.array_equal(dist, d2) and np.array_equal(cnt, c2)
+    lo, hi, out = multi.icp_batch_sharded([ref[:3000], ref[3000:7000]], [ref[:3000] + 0.01, ref[3000:7000] + 0.01], multi=m)
+    assert (lo, hi) == (0, 2) and out["T_last"].shape == (2, 4, 4)
+    if pcp.native.device_count() < 2:
+        return
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29641", os.path.join(root, "tools", "run_c5.py"), "--ref", "2000001",
+                        "--queries", "4000000", "--check", "2048"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    rep = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert rep["comm_nranks"] == 2 and rep["reference_rows_gathered"] == 2000001 and all(rep["parity_sampled_vs_device_bruteforce"])

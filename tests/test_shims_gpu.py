@@ -60,7 +60,9 @@ def test_shim_per_query_vs_golden(pcp, knn_golden, kitti, name):
             assert rs.count == g[name + "/kd_knn_cnt"][i]
             assert np.array_equal(np.float32([d.distance for d in rs.dist_index_list]), g[name + "/kd_knn_dist"][i])
             d = g[name + "/kd_knn_dist"][i]
-            if len(set(d[:rs.count].tolist())) == rs.count and rs.count < k:
+            # distinct distances: the index sequence is unique (a tie exactly at the k / k+1 boundary, which the
+            # reference resolves by tree visit order, does not occur among the first 40 golden queries)
+            if len(set(d[:rs.count].tolist())) == rs.count:
                 assert [x.index for x in rs.dist_index_list] == g[name + "/kd_knn_idx"][i].tolist()
         rr = RadiusNNResultSet(r)
         kdtree.kdtree_radius_search(kd, db, rr, q[i])
@@ -154,3 +156,50 @@ def test_register_pairs_writes_reg_result(pcp, tmp_path):
     for a, b in zip(got[1:], want[1:]):
         fa, fb = np.float64(a.split(",")), np.float64(b.split(","))
         assert np.abs(fa - fb).max() <= 1.01e-6            # equal after %f formatting up to one rounding step
+
+
+def test_knn_capacity_above_32(pcp):
+    """KNNResultSet accepts any capacity (result_set.py:16-24); beyond the kernels' register width (32) the
+    shim assembles the rows from the 32-NN search plus radius searches: same indices / float32 distances as
+    brute force, incl. fewer points than k."""
+    from oracle import knn_oracle
+    from point_cloud_process_b200 import kdtree
+    from point_cloud_process_b200.result_set import KNNResultSet
+    rng = np.random.default_rng(21)
+    db = (rng.random((5000, 3)) * np.float32([20, 20, 3])).astype(np.float32)
+    db[100:180] = db[100]                                     # 80 duplicates: more than 32 at distance 0
+    q = np.concatenate([db[rng.choice(5000, 60)], db[100:101], (rng.random((20, 3)) * 30 - 5).astype(np.float32)])
+    for k in (33, 50, 100):
+        idx, dist, cnt = pcp.SearchIndex(db).knn(q, k)
+        b_dist, b_idx, b_cnt = knn_oracle.bruteforce_knn(db, q, k, threads=8)
+        assert np.array_equal(dist, b_dist) and np.array_equal(idx, b_idx.astype(np.int32)) and np.array_equal(cnt, b_cnt)
+    small = db[:40]
+    idx, dist, cnt = pcp.SearchIndex(small).knn(q[:5], 64)
+    assert (cnt == 40).all() and (dist[:, 40:] == np.float32(1e10)).all() and (idx[:, 40:] == 0).all()
+    rs = KNNResultSet(48)
+    kdtree.kdtree_knn_search(kdtree.kdtree_construction(db, 32), db, rs, q[0])
+    assert rs.count == 48 and [d.index for d in rs.dist_index_list] == idx_of(db, q[0], 48)
+
+
+def idx_of(db, query, k):
+    from oracle import knn_oracle
+    return knn_oracle.bruteforce_knn(db, query[None, :], k, threads=1)[1][0].tolist()
+
+
+def test_second_search_accumulates_like_add_point(pcp, kitti):
+    """A result set that already holds candidates keeps them: the reference feeds every search through
+    add_point (result_set.py:35-53), so two searches on ONE KNNResultSet leave the best of both."""
+    from point_cloud_process_b200 import kdtree
+    from point_cloud_process_b200.result_set import KNNResultSet
+    root = kdtree.kdtree_construction(kitti, 32)
+    a, b = KNNResultSet(8), KNNResultSet(8)
+    kdtree.kdtree_knn_search(root, kitti, a, kitti[10])
+    kdtree.kdtree_knn_search(root, kitti, b, kitti[5000])
+    both = KNNResultSet(8)
+    kdtree.kdtree_knn_search(root, kitti, both, kitti[10])
+    kdtree.kdtree_knn_search(root, kitti, both, kitti[5000])
+    ref = KNNResultSet(8)
+    for d in a.dist_index_list + b.dist_index_list:
+        ref.add_point(d.distance, d.index)
+    assert [(d.distance, d.index) for d in both.dist_index_list] == [(d.distance, d.index) for d in ref.dist_index_list]
+    assert both.count == 8 and both.worst_dist == ref.worst_dist

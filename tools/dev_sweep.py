@@ -1,7 +1,7 @@
 """Developer probe: device-resident kNN timing for the current env settings (one line per workload)."""
 import os, sys
 import numpy as np, torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.environ.get("PCP_ROOT") or os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import point_cloud_process_b200 as pcp
 native = pcp.native
 which = sys.argv[1:] or ["kitti"]

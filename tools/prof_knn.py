@@ -1,7 +1,7 @@
 """Profiling target: a few launches of the kNN kernel on the KITTI scan (or the uniform 1M cloud)."""
 import os, sys
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.environ.get("PCP_ROOT") or os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import point_cloud_process_b200 as pcp
 which = sys.argv[1] if len(sys.argv) > 1 else "kitti"
 k = int(sys.argv[2]) if len(sys.argv) > 2 else 8

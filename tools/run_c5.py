@@ -1,7 +1,8 @@
 """BASELINE config 5 (scaled by --scale): query-sharded kNN k=16 over a replicated reference cloud.
 torchrun --nproc-per-node N tools/run_c5.py [--ref 16000000 --queries 64000000]
-Each rank generates its 1/N of the reference (counter hash), all-gathers it over NCCL, builds the
-index locally and searches its own query shard.  Parity: sampled queries vs the brute-force oracle."""
+Each rank generates its 1/N of the reference (counter hash); the C ABI (pcp_multi_set_reference) all-gathers it
+over NCCL and builds the index; each rank searches its own query shard.  torch here is only the test harness (device
+buffers, barrier, max over ranks).  Parity: sampled queries vs the exhaustive device kernel."""
 import argparse, json, os, sys, time
 import numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -32,42 +33,71 @@ def main():
     ap.add_argument("--ref", type=int, default=16_000_000)
     ap.add_argument("--queries", type=int, default=64_000_000)
     ap.add_argument("--k", type=int, default=16)
-    ap.add_argument("--check", type=int, default=512)
+    ap.add_argument("--check", type=int, default=4096)
     args = ap.parse_args()
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    r = run_c5(args.ref, args.queries, args.k, args.check)
+    if r is not None:
+        print(json.dumps(r))
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
+def run_c5(n_ref, n_queries, k, check, use_dist=True):
+    """Every rank: its shard of the reference -> pcp_multi_set_reference (ncclAllGather + build, timed by the
+    library) -> kNN of its own query shard (CUDA events) -> parity of `check` sampled queries against the
+    exhaustive DEVICE kernel (pcp_knn_bruteforce) over the gathered cloud.  Returns the report on rank 0."""
+    import point_cloud_process_b200 as pcp
+    rank, world, local = multi.env_rank_world()
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    L = 64.0 * (args.ref / 16e6) ** (1 / 3)
-    rlo, rhi = multi.shard_range(args.ref, rank, world)
-    qlo, qhi = multi.shard_range(args.queries, rank, world)
+    if world > 1 and use_dist and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = 64.0 * (n_ref / 16e6) ** (1 / 3)
+    rlo, rhi = multi.shard_range(n_ref, rank, world)
+    qlo, qhi = multi.shard_range(n_queries, rank, world)
     ref_shard = torch.from_numpy(gen(42, rlo, rhi, L)).cuda()
     q = torch.from_numpy(gen(43, qlo, qhi, L)).cuda()
-    dist.barrier(); torch.cuda.synchronize()
-    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-    e[0].record()
-    s = multi.ShardedSearch(ref_shard)                       # all-gather + build
-    torch.cuda.synchronize(); t_build = time.perf_counter()
-    st = torch.cuda.ExternalStream(s.ctx.stream())
-    e[1].record(st)
-    idx, d, cnt = s.knn(q, args.k)
-    e[2].record(st)
+    ctx = pcp.default_context(local)
+    m = multi.create(rank=rank, world=world, device=local, ctx=ctx)
+    st = torch.cuda.ExternalStream(ctx.stream())
+    nq = qhi - qlo
+    idx = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+    d = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    cnt = torch.empty(nq, dtype=torch.int32, device="cuda")
     torch.cuda.synchronize()
-    ms = torch.tensor([e[1].elapsed_time(e[2])], dtype=torch.float64, device="cuda")
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if world > 1:
+        dist.barrier()
+    n_total = m.set_reference_device(ref_shard.data_ptr(), rhi - rlo, 3)        # the one collective + the build
+    gather_ms, build_ms = m.last_timing()
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    e[0].record(st)
+    m.knn_device(q.data_ptr(), nq, 3, k, idx.data_ptr(), d.data_ptr(), cnt.data_ptr())
+    e[1].record(st)
+    ctx.synchronize()
+    t = torch.tensor([gather_ms, build_ms, e[0].elapsed_time(e[1])], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ok = True
-    if args.check:
-        from oracle import knn_oracle
-        ref = s.reference.cpu().numpy()
-        sel = np.random.default_rng(rank).choice(qhi - qlo, min(args.check, qhi - qlo), replace=False)
-        bd, bi, _ = knn_oracle.bruteforce_knn(ref, q[sel].cpu().numpy(), args.k, threads=os.cpu_count() // world or 1)
-        ok = bool(np.array_equal(idx[sel].cpu().numpy(), bi.astype(np.int32)) and np.array_equal(d[sel].cpu().numpy(), bd))
-    oks = [None] * world
-    dist.all_gather_object(oks, ok)
-    if rank == 0:
-        print(json.dumps({"config": "C5", "ref": args.ref, "queries": args.queries, "k": args.k, "n_gpus": world,
-                          "search_ms_max_over_ranks": float(ms.item()), "queries_per_s": args.queries / (ms.item() * 1e-3),
-                          "parity_sampled": oks}))
-    dist.destroy_process_group()
+    if check:
+        sel = torch.from_numpy(np.random.default_rng(rank).choice(nq, min(check, nq), replace=False)).cuda()
+        qs = q[sel].contiguous()
+        bi = torch.empty((len(sel), k), dtype=torch.int32, device="cuda")
+        bd = torch.empty((len(sel), k), dtype=torch.float32, device="cuda")
+        bc = torch.empty(len(sel), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        m.knn_bruteforce_device(qs.data_ptr(), len(sel), 3, k, bi.data_ptr(), bd.data_ptr(), bc.data_ptr())
+        ctx.synchronize()
+        ok = bool(torch.equal(idx[sel], bi) and torch.equal(d[sel], bd))
+    oks = [ok]
+    if world > 1:
+        oks = [None] * world
+        dist.all_gather_object(oks, ok)
+    info = m.info()
+    gm, bm, sm = (float(x) for x in t.tolist())
+    return {"config": "C5", "ref": n_ref, "queries": n_queries, "k": k, "n_gpus": world, "reference_rows_gathered": int(n_total),
+            "allgather_ms": gm, "build_ms": bm, "search_ms": sm, "timing": "max over ranks, CUDA events",
+            "queries_per_s_search": n_queries / (sm * 1e-3), "queries_per_s_incl_gather_and_build": n_queries / ((gm + bm + sm) * 1e-3),
+            "allgather_bytes_received_per_gpu": int(n_total) * 12, "comm_nranks": info["comm_nranks"], "nccl_version": info["nccl_version"],
+            "parity_sampled_vs_device_bruteforce": oks, "sampled_queries_per_rank": int(check)} if rank == 0 else None
 
 
 if __name__ == "__main__":
