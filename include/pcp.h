@@ -96,6 +96,20 @@ PCP_API int pcp_ctx_read_kernel_timing(pcp_ctx *ctx, double *total_ms, int64_t *
 PCP_API int pcp_ctx_enable_counters(pcp_ctx *ctx, int enable);
 PCP_API int pcp_ctx_read_counters(pcp_ctx *ctx, uint64_t out[8]);
 
+/* ---- CUDA graphs --------------------------------------------------------------------------------------------
+ * A fixed sequence of PCP_DEVICE calls on one context (e.g. pcp_index_rebuild + pcp_knn of one LiDAR frame: ~20
+ * kernel launches on two streams) captured once and replayed with ONE launch per step: the device pointers and
+ * shapes of the captured calls are baked in, the DATA behind them may change between launches.  The calls
+ * between begin and end are recorded, not executed; run the same sequence once before capturing (the library's
+ * scratch buffers must already have their size -- a capture in which one had to grow is refused).
+ * PCP_HOST calls cannot be captured (they synchronise).  pcp_graph_launch is asynchronous on the context stream. */
+typedef struct pcp_graph pcp_graph;
+PCP_API int pcp_graph_begin(pcp_ctx *ctx);
+PCP_API int pcp_graph_end(pcp_ctx *ctx, pcp_graph **out);
+PCP_API int pcp_graph_launch(pcp_graph *graph);
+PCP_API int64_t pcp_graph_nodes(const pcp_graph *graph);
+PCP_API int pcp_graph_destroy(pcp_graph *graph);
+
 /* ---- index build ---------------------------------------------------------------------------
  * Replaces kdtree_construction(db_np, leaf_size)            kdtree.py:119-137
  *      and octree_construction(db_np, leaf_size, min_extent) octree.py:310-328.
@@ -198,6 +212,11 @@ PCP_API int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_
                   const float *tgt_xyz, const int64_t *tgt_offsets, int64_t stride_floats, int mem,
                   const double *T_init, double *T_last, double *T_total, int32_t *iterations,
                   int32_t *status, double *diff_log);
+
+/* Bookkeeping of the last pcp_icp_batch on this context: kernels launched by its iteration loop, host-blocking
+ * synchronisations (1 = only the final result copy), iterations enqueued (blocks of 4, 8, 16, ... run without
+ * a host read in between; a converged pair's CTAs return at once). */
+PCP_API int pcp_icp_last_stats(pcp_ctx *ctx, int64_t *launches, int64_t *host_syncs, int64_t *iterations_enqueued);
 
 /* procrustes_transformation(A, B) -> (R, t, cost)               main.py:131-141, icp_template.py:43-54
  * on GIVEN correspondences: A, B are 3 x n float64 row-major (one column per point, the reference's

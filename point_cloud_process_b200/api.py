@@ -95,7 +95,7 @@ class SearchIndex:
     def knn_bruteforce(self, queries, k):
         """Same contract as knn(), computed by the exhaustive device kernel (the reference's own check,
         np.argsort(np.linalg.norm(db - query, axis=1))[:k], kdtree.py:234-238): every (query, point) pair, no
-        spatial pruning.  The on-device second oracle of the test-suite; k <= 32."""
+        spatial pruning.  The on-device exhaustive cross-check of the test-suite; k <= 32."""
         return self._ix.knn_bruteforce(_as_cloud(queries, "queries"), int(k))
 
     def radius_count_bruteforce(self, queries, radius):

@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -63,6 +64,19 @@ struct Cloud {
     const float *data() const { return arr.data(); }
 };
 
+// CUDA graph of captured PCP_DEVICE calls (pcp_graph_*)
+class Graph {
+   public:
+    explicit Graph(pcp_graph *g) : g_(g) {}
+    ~Graph() { pcp_graph_destroy(g_); }
+    Graph(const Graph &) = delete;
+    void launch() { check(pcp_graph_launch(g_), "pcp_graph_launch"); }
+    int64_t nodes() const { return pcp_graph_nodes(g_); }
+
+   private:
+    pcp_graph *g_;
+};
+
 class Context {
    public:
     explicit Context(int device) { check(pcp_ctx_create(device, &ctx_), "pcp_ctx_create"); }
@@ -79,6 +93,17 @@ class Context {
         int64_t n = 0;
         check(pcp_ctx_read_kernel_timing(ctx_, &ms, &n), "pcp_ctx_read_kernel_timing");
         return py::make_tuple(ms, n);
+    }
+    void graph_begin() { check(pcp_graph_begin(ctx_), "pcp_graph_begin"); }
+    std::unique_ptr<Graph> graph_end() {
+        pcp_graph *g = nullptr;
+        check(pcp_graph_end(ctx_, &g), "pcp_graph_end");
+        return std::unique_ptr<Graph>(new Graph(g));
+    }
+    py::tuple icp_last_stats() {
+        int64_t l = 0, s = 0, e = 0;
+        check(pcp_icp_last_stats(ctx_, &l, &s, &e), "pcp_icp_last_stats");
+        return py::make_tuple(l, s, e);
     }
     std::vector<uint64_t> read_counters() {
         std::vector<uint64_t> v(8);
@@ -133,7 +158,7 @@ class Index {
         rethrow();
         return py::make_tuple(idx, dist, cnt);
     }
-    // exhaustive kernel (kdtree.py:234-238 as a device kernel): the second oracle
+    // exhaustive kernel (kdtree.py:234-238 as a device kernel): the exhaustive cross-check
     py::tuple knn_bruteforce(const py::object &queries, int k) {
         Cloud q(queries, "queries");
         if (k < 1) throw py::value_error("k must be >= 1");
@@ -545,7 +570,11 @@ PYBIND11_MODULE(_pcp, m) {
         .def("enable_counters", &Context::enable_counters, py::arg("on") = true)
         .def("read_counters", &Context::read_counters)
         .def("enable_kernel_timing", &Context::enable_kernel_timing)
-        .def("read_kernel_timing", &Context::read_kernel_timing);
+        .def("read_kernel_timing", &Context::read_kernel_timing)
+        .def("icp_last_stats", &Context::icp_last_stats)
+        .def("graph_begin", &Context::graph_begin)
+        .def("graph_end", &Context::graph_end);
+    py::class_<Graph>(m, "Graph").def("launch", &Graph::launch).def("nodes", &Graph::nodes);
 
     py::class_<Index>(m, "Index")
         .def(py::init<std::shared_ptr<Context>, const py::object &>(), py::arg("ctx"), py::arg("points"))

@@ -1,4 +1,4 @@
-// Brute-force exact kNN / radius count over the WHOLE indexed cloud: the on-device second oracle
+// Brute-force exact kNN / radius count over the WHOLE indexed cloud: the on-device exhaustive cross-check
 // (SURVEY section 7 step 2 / kernel K5).  Replaces the check the reference prints next to its tree
 // searches -- np.argsort(np.linalg.norm(db - query, axis=1))[:k], kdtree.py:234-238, octree.py:352-356 --
 // for full query sets: every (query, point) pair is evaluated, no spatial pruning, so it shares NO traversal

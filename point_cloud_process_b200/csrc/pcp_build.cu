@@ -516,7 +516,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         bbox_kernel<<<dim3(bx, gy), 256, 0, st>>>(d_xyz, stride, dv + p0);
         ctx->launches += 1;
     }
-    if (b->ev_bbox) PCP_CUDA(cudaEventRecord(b->ev_bbox, st));   // query keys only need the boxes, not the sorted cloud
+    if (b->ev_bbox_record) PCP_CUDA(cudaEventRecord(b->ev_bbox_record, st));   // query keys only need the boxes, not the sorted cloud
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
         if (wide64)
@@ -569,6 +569,8 @@ int index_build_device(pcp_index *ix, const float *d_xyz, int64_t n, int64_t str
     ix->built_stride = stride;
     if (!ix->b.ev_bbox) PCP_CUDA(cudaEventCreateWithFlags(&ix->b.ev_bbox, cudaEventDisableTiming));
     ix->b.ctx = ix->ctx;
+    ix->b.ev_bbox_record = ix->ctx->capturing ? ix->ctx->ev_cap_bbox : ix->b.ev_bbox;
+    if (ix->ctx->capturing) ix->ctx->cap_has_bbox = true;
     const int64_t offs[2] = {0, n};
     return batch_build_device(&ix->b, d_xyz, stride, 1, offs);
 }

@@ -28,8 +28,13 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
     return e == cudaErrorMemoryAllocation ? PCP_ERR_OOM : PCP_ERR_CUDA;
 }
 
+static thread_local bool g_capture_on = false, g_capture_grew = false;
+void capture_note_begin() { g_capture_on = true; g_capture_grew = false; }
+bool capture_note_grew() { g_capture_on = false; return g_capture_grew; }
+
 int DevBuf::ensure(size_t bytes) {
     if (bytes <= cap) return PCP_OK;
+    if (g_capture_on) g_capture_grew = true;
     size_t want = bytes + bytes / 8 + 256;
     void *np = nullptr;
     cudaError_t e = cudaMalloc(&np, want);
@@ -251,6 +256,8 @@ int pcp_ctx_create(int device, pcp_ctx **out) {
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_q_ready, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_cap_bbox, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_cap_q, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_search_end, cudaEventDisableTiming) != cudaSuccess) {
         cudaGetLastError();
         pcp_ctx_destroy(ctx);
@@ -283,6 +290,8 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
     if (ctx->ev_q_ready) cudaEventDestroy(ctx->ev_q_ready);
     if (ctx->ev_search_end) cudaEventDestroy(ctx->ev_search_end);
+    if (ctx->ev_cap_bbox) cudaEventDestroy(ctx->ev_cap_bbox);
+    if (ctx->ev_cap_q) cudaEventDestroy(ctx->ev_cap_q);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -640,6 +649,88 @@ int pcp_icp_batch(pcp_ctx *ctx, const pcp_icp_params *params, int64_t n_pairs, c
                                     T_total, iterations, status, diff_log, src_ready);
     if (rc != PCP_OK && src_ready) cudaStreamSynchronize(ctx->copy_stream);   // the caller's buffer is free on return
     return rc;
+}
+
+// ---------------------------------------------------------------------------------------------- CUDA graphs
+
+struct pcp_graph {
+    pcp_ctx *ctx = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    size_t nodes = 0;
+};
+
+int pcp_graph_begin(pcp_ctx *ctx) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_graph_begin: ctx is NULL");
+    if (ctx->capturing) return fail(PCP_ERR_INVALID, "pcp_graph_begin: a capture is already open on this context");
+    DeviceGuard g(ctx->device);
+    PCP_CUDA(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+    ctx->capturing = true;
+    ctx->cap_has_bbox = false;
+    capture_note_begin();
+    return PCP_OK;
+}
+
+int pcp_graph_end(pcp_ctx *ctx, pcp_graph **out) {
+    if (!ctx || !out) return fail(PCP_ERR_INVALID, "pcp_graph_end: ctx/out is NULL");
+    if (!ctx->capturing) return fail(PCP_ERR_INVALID, "pcp_graph_end: no capture is open on this context");
+    *out = nullptr;
+    DeviceGuard g(ctx->device);
+    ctx->capturing = false;
+    const bool grew = capture_note_grew();
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    if (e != cudaSuccess || !graph) {
+        cudaGetLastError();
+        return fail(PCP_ERR_CUDA, std::string("pcp_graph_end: capture failed (") + cudaGetErrorString(e) +
+                                      "): only PCP_DEVICE calls of this context may be captured");
+    }
+    if (grew) {
+        cudaGraphDestroy(graph);
+        return fail(PCP_ERR_INVALID, "pcp_graph_end: a library buffer had to grow during the capture; run the same "
+                                     "calls once before capturing them");
+    }
+    pcp_graph *pg = new (std::nothrow) pcp_graph();
+    if (!pg) { cudaGraphDestroy(graph); return fail(PCP_ERR_OOM, "pcp_graph_end: out of host memory"); }
+    pg->ctx = ctx;
+    pg->graph = graph;
+    cudaGraphGetNodes(graph, nullptr, &pg->nodes);
+    e = cudaGraphInstantiate(&pg->exec, graph, 0);
+    if (e != cudaSuccess) {
+        cudaGraphDestroy(graph);
+        delete pg;
+        return cuda_fail(e, "cudaGraphInstantiate", __FILE__, __LINE__);
+    }
+    *out = pg;
+    return PCP_OK;
+}
+
+int pcp_graph_launch(pcp_graph *g) {
+    if (!g) return fail(PCP_ERR_INVALID, "pcp_graph_launch: graph is NULL");
+    DeviceGuard dg(g->ctx->device);
+    PCP_CUDA(cudaGraphLaunch(g->exec, g->ctx->stream));
+    g->ctx->launches += (int64_t)g->nodes;
+    return PCP_OK;
+}
+
+int64_t pcp_graph_nodes(const pcp_graph *g) { return g ? (int64_t)g->nodes : 0; }
+
+int pcp_graph_destroy(pcp_graph *g) {
+    if (!g) return PCP_OK;
+    DeviceGuard dg(g->ctx->device);
+    cudaStreamSynchronize(g->ctx->stream);
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->graph) cudaGraphDestroy(g->graph);
+    delete g;
+    return PCP_OK;
+}
+
+int pcp_icp_last_stats(pcp_ctx *ctx, int64_t *launches, int64_t *host_syncs, int64_t *iterations_enqueued) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_icp_last_stats: ctx is NULL");
+    if (launches) *launches = ctx->icp_last_launches;
+    if (host_syncs) *host_syncs = ctx->icp_last_syncs;
+    if (iterations_enqueued) *iterations_enqueued = ctx->icp_last_enqueued;
+    return PCP_OK;
 }
 
 int pcp_procrustes(pcp_ctx *ctx, const double *A, const double *B, int64_t n, int mem, double *R, double *t, double *cost) {

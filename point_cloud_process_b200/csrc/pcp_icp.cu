@@ -775,35 +775,53 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
     int h_active = max_it > 0 ? (int)P : 0;
     PCP_CUDA(cudaMemcpyAsync(b_act.p, &h_active, sizeof(int), cudaMemcpyHostToDevice, st));
 
-    int next_check = 1;
-    for (int it = 0; it < max_it && h_active > 0; ++it) {
-        for (int64_t p0 = 0; p0 < P; p0 += 65535) {
-            const unsigned gy = (unsigned)std::min<int64_t>(65535, P - p0);
-            if (use_tile)
-                icp_assoc_tile_kernel<<<dim3((unsigned)chunks, gy), kTileAssocWarps * 32, 0, st>>>(
-                    tb.d_views() + p0, sb.d_views() + p0, b_states.as<IcpState>() + p0,
-                    b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
-            else
-                icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
-                    tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
-                    b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+    // No host round trip inside an iteration, and none between the iterations of a block: blocks of 4, 8, 16, ...
+    // iterations are enqueued back to back (a pair that has stopped makes its CTAs return at once, so the
+    // iterations enqueued past convergence cost a launch each), and the copy that ends a block brings back the
+    // final states together with the "pairs still active" word.  The reference's own setting (main.py:98-102:
+    // 1-2 iterations) therefore finishes with ONE synchronisation -- the result copy itself.
+    const int64_t launches0 = ctx->launches;
+    int it = 0, block = 4, syncs = 0;
+    while (it < max_it && h_active > 0) {
+        const int upto = std::min(max_it, it + block);
+        for (; it < upto; ++it) {
+            for (int64_t p0 = 0; p0 < P; p0 += 65535) {
+                const unsigned gy = (unsigned)std::min<int64_t>(65535, P - p0);
+                if (use_tile)
+                    icp_assoc_tile_kernel<<<dim3((unsigned)chunks, gy), kTileAssocWarps * 32, 0, st>>>(
+                        tb.d_views() + p0, sb.d_views() + p0, b_states.as<IcpState>() + p0,
+                        b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+                else
+                    icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
+                        tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
+                        b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+                ctx->launches += 1;
+            }
+            icp_solve_kernel<<<(unsigned)((P * 32 + 127) / 128), 128, 0, st>>>(
+                b_states.as<IcpState>(), b_part.as<double>(), b_off.as<long long>(), P, chunks, it, max_it, prm.R_diff_thres,
+                prm.t_diff_thres, prm.first_iter_broadcast, d_log, b_act.as<int>(), use_tile ? sb.d_views() : nullptr);
             ctx->launches += 1;
         }
-        icp_solve_kernel<<<(unsigned)((P * 32 + 127) / 128), 128, 0, st>>>(
-            b_states.as<IcpState>(), b_part.as<double>(), b_off.as<long long>(), P, chunks, it, max_it, prm.R_diff_thres,
-            prm.t_diff_thres, prm.first_iter_broadcast, d_log, b_act.as<int>(), use_tile ? sb.d_views() : nullptr);
-        ctx->launches += 1;
-        if (it + 1 == next_check && it + 1 < max_it) {
-            // not on the data path: one word tells the host whether any pair still iterates
-            PCP_CUDA(cudaMemcpyAsync(&h_active, b_act.p, sizeof(int), cudaMemcpyDeviceToHost, st));
-            PCP_CUDA(cudaStreamSynchronize(st));
-            next_check = next_check < 4 ? next_check + 1 : next_check + (next_check + 1) / 2;
-        }
+        PCP_CUDA(cudaGetLastError());
+        PCP_CUDA(cudaMemcpyAsync(h_states.data(), b_states.p, sizeof(IcpState) * (size_t)P, cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaMemcpyAsync(&h_active, b_act.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaStreamSynchronize(st));
+        ++syncs;
+        block *= 2;
     }
-    PCP_CUDA(cudaGetLastError());
-    PCP_CUDA(cudaMemcpyAsync(h_states.data(), b_states.p, sizeof(IcpState) * (size_t)P, cudaMemcpyDeviceToHost, st));
-    if (d_log) PCP_CUDA(cudaMemcpyAsync(h_log, d_log, sizeof(double) * 2 * (size_t)P * (size_t)max_it, cudaMemcpyDeviceToHost, st));
-    PCP_CUDA(cudaStreamSynchronize(st));
+    if (syncs == 0) {   // max_iteration == 0: the states as initialised
+        PCP_CUDA(cudaMemcpyAsync(h_states.data(), b_states.p, sizeof(IcpState) * (size_t)P, cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaStreamSynchronize(st));
+        ++syncs;
+    }
+    if (d_log) {
+        PCP_CUDA(cudaMemcpyAsync(h_log, d_log, sizeof(double) * 2 * (size_t)P * (size_t)max_it, cudaMemcpyDeviceToHost, st));
+        PCP_CUDA(cudaStreamSynchronize(st));
+        ++syncs;
+    }
+    ctx->icp_last_launches = ctx->launches - launches0;
+    ctx->icp_last_syncs = syncs;
+    ctx->icp_last_enqueued = it;
     for (int64_t p = 0; p < P; ++p) {
         const IcpState &s = h_states[(size_t)p];
         const double bottom[4] = {0, 0, 0, 1};

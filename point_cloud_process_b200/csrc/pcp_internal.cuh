@@ -15,6 +15,10 @@ namespace pcp {
 // ------------------------------------------------------------------------------------------------
 // errors
 void set_error(const std::string &msg);
+// graph capture on this thread: DevBuf::ensure notes a buffer that had to grow (the captured graph would then
+// hold pointers of a call pattern that was never run before: capture is refused)
+void capture_note_begin();
+bool capture_note_grew();
 int fail(int code, const std::string &msg);
 int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 
@@ -92,6 +96,7 @@ struct BatchIndex {
     int64_t level_max_cnt[kMaxLevels] = {0};
     std::vector<IndexView> h_views;
     cudaEvent_t ev_bbox = nullptr;   // optional: recorded on the build stream once the segment bounding boxes are final
+    cudaEvent_t ev_bbox_record = nullptr;   // the event the running build records (ev_bbox, or the capture's own)
     DevBuf pts, pts2, box_lo, box_hi, half, bbox, views, keys_a, keys_b, vals_a, vals_b;
     const IndexView *d_views() const { return views.as<IndexView>(); }
     void release();
@@ -113,7 +118,13 @@ struct pcp_ctx {
     pcp::DevBuf q_keys[3], q_perm, cub_tmp_side;
     cudaEvent_t ev_q_ready = nullptr;     // side stream: permutation of the current query set complete
     cudaEvent_t ev_search_end = nullptr;  // main stream: last search that read q_perm has finished
+    // CUDA-graph capture (pcp_graph_begin / pcp_graph_end): the stream is capturing; the fork / join of the side
+    // stream uses events of its own (an event recorded inside a capture must not be waited on outside of it)
+    bool capturing = false, cap_has_bbox = false;
+    cudaEvent_t ev_cap_bbox = nullptr, ev_cap_q = nullptr;
     int64_t launches = 0;
+    // last pcp_icp_batch: kernels launched in its iteration loop, host synchronisations, iterations enqueued
+    int64_t icp_last_launches = 0, icp_last_syncs = 0, icp_last_enqueued = 0;
     pcp::DevBuf cub_tmp;           // CUB temporary storage
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
     pcp::PinBuf pin[4];            // pinned staging for host<->device copies
@@ -186,7 +197,7 @@ int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t
 int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
                        long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist);
 
-// brute force over the whole cloud (pcp_brute.cu): the on-device second oracle
+// brute force over the whole cloud (pcp_brute.cu): the on-device exhaustive cross-check
 float exact_d2_threshold(float r);
 int knn_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, int k, int32_t *d_idx, float *d_dist,
                      int32_t *d_count);

@@ -145,13 +145,22 @@ int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, cons
         if (side_ok || (d_q == ix->built_from && stride == ix->built_stride && nq == ix->n)) {
             PCP_TRY(ctx->q_perm.ensure(sizeof(uint32_t) * (size_t)nq));
             cudaStream_t side = ctx->copy_stream;
-            PCP_CUDA(cudaStreamWaitEvent(side, ix->b.ev_bbox, 0));          // boxes of THIS index final
-            PCP_CUDA(cudaStreamWaitEvent(side, ctx->ev_search_end, 0));     // last reader of q_perm done
+            if (ctx->capturing) {
+                // inside a graph capture: fork the side stream from the build's bounding-box event when this capture
+                // holds the build (first search after it), else from the main stream as it stands; join below
+                if (!ctx->cap_has_bbox) PCP_CUDA(cudaEventRecord(ctx->ev_cap_bbox, ctx->stream));
+                ctx->cap_has_bbox = false;
+                PCP_CUDA(cudaStreamWaitEvent(side, ctx->ev_cap_bbox, 0));
+            } else {
+                PCP_CUDA(cudaStreamWaitEvent(side, ix->b.ev_bbox, 0));          // boxes of THIS index final
+                PCP_CUDA(cudaStreamWaitEvent(side, ctx->ev_search_end, 0));     // last reader of q_perm done
+            }
             PCP_TRY(sort_queries_on(ix, d_q, nq, stride, ctx->q_perm.as<uint32_t>(), side, ctx->q_keys, ctx->cub_tmp_side));
-            PCP_CUDA(cudaEventRecord(ctx->ev_q_ready, side));
-            PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_q_ready, 0));
+            cudaEvent_t ready = ctx->capturing ? ctx->ev_cap_q : ctx->ev_q_ready;
+            PCP_CUDA(cudaEventRecord(ready, side));
+            PCP_CUDA(cudaStreamWaitEvent(ctx->stream, ready, 0));
             PCP_TRY(knn_tile_device(ix, d_q, nq, stride, ctx->q_perm.as<uint32_t>(), k, d_idx, d_dist, d_count));
-            PCP_CUDA(cudaEventRecord(ctx->ev_search_end, ctx->stream));
+            if (!ctx->capturing) PCP_CUDA(cudaEventRecord(ctx->ev_search_end, ctx->stream));
             return PCP_OK;
         }
         PCP_TRY(ctx->scratch[3].ensure(sizeof(uint32_t) * (size_t)nq));

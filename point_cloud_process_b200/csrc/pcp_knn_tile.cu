@@ -627,7 +627,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     const unsigned max_scans = e_scans ? (unsigned)atoi(e_scans) : small_grid ? kScansPerSlot * std::max(K, 4) : 0xffffffffu;
     const unsigned max_tests = e_tests ? (unsigned)atoi(e_tests) : small_grid ? kTestsPerSlot * std::max(K, 4) : 0xffffffffu;
     unsigned *dbg = nullptr;
-    const char *dump = ctr ? getenv("PCP_DUMP_GROUPS") : nullptr;     // developer aid: per-group work counters
+    const char *dump = ctr && !ctx->capturing ? getenv("PCP_DUMP_GROUPS") : nullptr;     // developer aid: per-group work counters
     if (dump) {
         PCP_TRY(ctx->scratch[4].ensure(sizeof(unsigned) * 8 * (size_t)n_groups));
         dbg = ctx->scratch[4].as<unsigned>();
@@ -661,7 +661,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
                                                                        hint_groups, (unsigned)wbytes);                 \
     } while (0)
     cudaEvent_t ev_end = nullptr;
-    if (ctx->time_kernels) {
+    if (ctx->time_kernels && !ctx->capturing) {
         if (ctx->timing_used == ctx->timing_events.size()) {
             cudaEvent_t a, b;
             PCP_CUDA(cudaEventCreate(&a));

@@ -412,3 +412,54 @@ def test_multi_single_rank_and_two_rank_c5(pcp):
     assert r.returncode == 0, r.stderr[-2000:]
     rep = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
     assert rep["comm_nranks"] == 2 and rep["reference_rows_gathered"] == 2000001 and all(rep["parity_sampled_vs_device_bruteforce"])
+
+
+def test_cuda_graph_of_build_and_knn(pcp, kitti):
+    """pcp_graph_*: index rebuild + kNN of one frame captured once and replayed; the data behind the captured
+    device pointers changes between launches and every replay equals the plain calls.  A capture that needs a
+    buffer to grow is refused."""
+    import torch
+    native = pcp.native
+    ctx = native.Context(0)
+    n, k = len(kitti), 8
+    d = torch.from_numpy(kitti).cuda()
+    idx = torch.empty((n, k), dtype=torch.int32, device="cuda")
+    dst = torch.empty((n, k), dtype=torch.float32, device="cuda")
+    cnt = torch.empty(n, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ix = native.Index(ctx, d.data_ptr(), n, 3)
+
+    def step():
+        ix.rebuild_device(d.data_ptr(), n, 3)
+        ix.knn_device(d.data_ptr(), n, 3, k, idx.data_ptr(), dst.data_ptr(), cnt.data_ptr())
+    step()
+    ctx.synchronize()
+    want = [(idx.clone(), dst.clone())]
+    ctx.graph_begin()
+    step()
+    g = ctx.graph_end()
+    assert g.nodes() >= 10
+    frames = [kitti, (kitti[::-1] * np.float32(1.01)).copy(), kitti + np.float32(0.25)]
+    for f in frames[1:]:
+        d.copy_(torch.from_numpy(f).cuda())
+        torch.cuda.synchronize()
+        step()
+        ctx.synchronize()
+        want.append((idx.clone(), dst.clone()))
+    for f, (wi, wd) in zip(frames, want):
+        d.copy_(torch.from_numpy(f).cuda())
+        idx.zero_(); dst.zero_()
+        torch.cuda.synchronize()
+        g.launch()
+        ctx.synchronize()
+        assert torch.equal(idx, wi) and torch.equal(dst, wd)
+    # a capture whose calls were never run at that size must be refused, and the context stays usable
+    big = torch.from_numpy(np.concatenate([kitti, kitti + np.float32(200.0)])).cuda()
+    torch.cuda.synchronize()
+    ctx.graph_begin()
+    ix.rebuild_device(big.data_ptr(), len(big), 3)
+    with pytest.raises(ValueError):
+        ctx.graph_end()
+    step()
+    ctx.synchronize()
+    assert torch.equal(idx, want[-1][0])
