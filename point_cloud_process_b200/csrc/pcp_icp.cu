@@ -228,7 +228,7 @@ __device__ __forceinline__ float nn1_gate_fast(double best, float E) {
 __global__ void __launch_bounds__(kTileAssocWarps * 32, 32 / kTileAssocWarps)
 icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *__restrict__ src_views,
                       const IcpState *__restrict__ states, double *__restrict__ partials, int chunks_per_pair,
-                      double dist_thres) {
+                      double dist_thres, unsigned long long *__restrict__ ctr) {
     __shared__ float4 s_tile[kTileAssocWarps][32];
     __shared__ float4 s_box[kTileAssocWarps][128];   // half-bucket boxes of the open level-1 node
     __shared__ unsigned s_lb[kTileAssocWarps][kMaxLevels][32];
@@ -278,7 +278,9 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
             return (__any_sync(kFullMask, a) ? 1u : 0u) | (__any_sync(kFullMask, b) ? 2u : 0u);
         };
         float m32 = __int_as_float(0x7f800000);                // smallest float32 d^2 this lane has seen
+        unsigned n_pts = 0;                                    // work counter: points evaluated per lane
         auto scan_bucket = [&](const float4 pv, unsigned halves) {
+            n_pts += 16u * __popc(halves);
             __syncwarp();
             tile[lane] = pv;
             __syncwarp();
@@ -407,6 +409,10 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
             }
         }
         matched = active && best_id != kDone && best < dist_thres;   // main.py:119
+        if (ctr) {   // pcp_ctx_enable_counters: [0] distance evaluations, [4] source groups
+            const unsigned n_act = __popc(__ballot_sync(kFullMask, active));
+            if (lane == 0) { atomicAdd(ctr + 0, (unsigned long long)n_pts * n_act); atomicAdd(ctr + 4, 1ull); }
+        }
     }
     double acc[kSums];
 #pragma unroll
@@ -790,7 +796,7 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
                 if (use_tile)
                     icp_assoc_tile_kernel<<<dim3((unsigned)chunks, gy), kTileAssocWarps * 32, 0, st>>>(
                         tb.d_views() + p0, sb.d_views() + p0, b_states.as<IcpState>() + p0,
-                        b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres);
+                        b_part.as<double>() + (size_t)p0 * chunks * kSums, chunks, prm.dist_thres, ctx->ctr());
                 else
                     icp_assoc_kernel<<<dim3((unsigned)chunks, gy), kAssocWarps * 32, 0, st>>>(
                         tb.d_views() + p0, d_src, b_off.as<long long>() + p0, stride, b_states.as<IcpState>() + p0,
