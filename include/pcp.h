@@ -125,6 +125,11 @@ PCP_API int64_t pcp_index_size(const pcp_index *index);
 /* Device-resident internals for diagnostics / benches: number of buckets and hierarchy levels. */
 PCP_API int pcp_index_stats(const pcp_index *index, int64_t *n_buckets, int *n_levels);
 
+/* float64 originals of the rows the index was built from (n x 3 doubles, row i = point i): the library's search
+ * structure is float32, but the consumers whose reference works in float64 (pcp_iss_keypoints, pcp_dbscan: scipy
+ * cKDTree on the float64 cloud) decide borderline neighbour pairs on these.  Dropped by the next rebuild. */
+PCP_API int pcp_index_attach_f64(pcp_index *index, const double *xyz, int64_t n, int64_t stride_doubles, int mem);
+
 /* ---- k nearest neighbours --------------------------------------------------------------------
  * Replaces kdtree_knn_search(root, db, result_set, query)   kdtree.py:141-172
  *      and octree_knn_search(root, db, result_set, query)   octree.py:262-306
@@ -264,12 +269,19 @@ PCP_API int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride_fl
  * eigenvalues descending, candidate iff l2/l1 < lambda21 and l3/l2 < lambda32 (:52-57), non-maximum suppression
  * with non_max_radius in descending l3 (ties: ascending index), stopping once MORE than iss_count keypoints are
  * kept (:59-73; so at most iss_count + 1 indices are written -- size `keypoints` accordingly).
- * Neighbourhoods are the library's radius search (float32 distance <= radius, result_set.py:80); the reference
- * uses scipy's cKDTree in float64, which can differ only for pairs within one float32 ulp of the radius.
+ * Neighbourhoods follow scipy's cKDTree, which the reference searches with (ISS.py:40): the radius search's float32
+ * candidates are re-decided in FLOAT64 wherever the float32 distance is within its rounding band of the radius
+ * (squared differences summed x, y, z against radius * radius) -- on the float64 originals of the rows when they
+ * were attached with pcp_index_attach_f64, else on the float32 rows widened exactly.
  * keypoints / n_keypoints: host memory; lambda3 (host, may be NULL): n doubles, l3 of every candidate, NaN elsewhere.
  * For an index built with PCP_DEVICE the cloud passed to the build must still be alive. */
-PCP_API int pcp_iss_keypoints(pcp_index *index, float radius, double lambda21, double lambda32, float non_max_radius,
+PCP_API int pcp_iss_keypoints(pcp_index *index, double radius, double lambda21, double lambda32, double non_max_radius,
                               int iss_count, int32_t *keypoints, int32_t *n_keypoints, double *lambda3);
+
+/* counts[i] = number of indexed points within `radius` of indexed point i (itself included), decided as scipy's
+ * float64 cKDTree decides it -- the neighbourhood sizes behind the ISS weights (ISS.py:49) and the DBSCAN core test
+ * (dbscan.py:20-24): float32 candidates, float64 decision in the rounding band (see pcp_iss_keypoints).  Host output. */
+PCP_API int pcp_neighbor_counts_f64(pcp_index *index, double radius, int64_t *counts);
 
 /* pcp_dbscan replaces DBSCAN(radius, Min_Pts).fit(data) + predict() of Cluster_dbscan/dbscan.py:4-38 over the
  * indexed cloud: labels[i] = cluster number (0, 1, ... in the order the reference opens them: seeds are popped
@@ -277,11 +289,10 @@ PCP_API int pcp_iss_keypoints(pcp_index *index, float radius, double lambda21, d
  * its order-dependent rules: a popped point with fewer than Min_Pts neighbours (self included) stays noise for
  * good (:20-22), a point with >= Min_Pts opens a cluster (:24), a claimed point expands it only with MORE than
  * Min_Pts neighbours (:31-32).  Computed on the radius CSR as connected components of the expanding points plus a
- * rank-ordered fixed point for the rest.  Neighbourhoods: float32 dist <= radius
- * (result_set.py:80); scipy's KDTree in the reference is float64 (differs only within one float32 ulp of the
- * radius).  labels: n x int32 (host or device per `mem`); n_clusters (host, may be NULL).  For an index built
+ * rank-ordered fixed point for the rest.  Neighbourhoods follow scipy's float64 KDTree
+ * (dbscan.py:13): borderline pairs of the float32 search are re-decided in float64 (see pcp_iss_keypoints).  labels: n x int32 (host or device per `mem`); n_clusters (host, may be NULL).  For an index built
  * with PCP_DEVICE the cloud passed to the build must still be alive. */
-PCP_API int pcp_dbscan(pcp_index *index, float radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters);
+PCP_API int pcp_dbscan(pcp_index *index, double radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters);
 
 /* ---- multi-GPU: one process per GPU, work sharded where the path shards -------------------------
  * The reference has no distributed code on this path (single process, single thread); these entries are the

@@ -137,6 +137,15 @@ class Index {
         check(pcp_index_rebuild(ix_, reinterpret_cast<const float *>(dptr), n, stride, PCP_DEVICE), "pcp_index_rebuild");
     }
     int64_t size() const { return pcp_index_size(ix_); }
+    py::array_t<int64_t> neighbor_counts_f64(double radius) {
+        py::array_t<int64_t> c((py::ssize_t)size());
+        check(pcp_neighbor_counts_f64(ix_, radius, c.mutable_data()), "pcp_neighbor_counts_f64");
+        return c;
+    }
+    void attach_f64(const f64_array &xyz) {
+        if (xyz.ndim() != 2 || xyz.shape(1) < 3) throw py::value_error("attach_f64: expected (N, >= 3) float64 rows");
+        check(pcp_index_attach_f64(ix_, xyz.data(), xyz.shape(0), xyz.shape(1), PCP_HOST), "pcp_index_attach_f64");
+    }
     py::tuple stats() const {
         int64_t nb = 0;
         int nl = 0;
@@ -212,7 +221,7 @@ class Index {
         return py::make_tuple(nrm, ev);
     }
     // ISS.py:40-73 -> (keypoint indices in selection order, lambda3 (N,) with NaN for non-candidates)
-    py::tuple iss_keypoints(float radius, double lambda21, double lambda32, float non_max_radius, int iss_count) {
+    py::tuple iss_keypoints(double radius, double lambda21, double lambda32, double non_max_radius, int iss_count) {
         if (iss_count < 0) throw py::value_error("iss_count must be >= 0");
         std::vector<int32_t> kp((size_t)iss_count + 1);
         int32_t nk = 0;
@@ -224,13 +233,13 @@ class Index {
         return py::make_tuple(out, l3);
     }
     // DBSCAN.fit + predict of Cluster_dbscan/dbscan.py:10-38 -> (labels (N,) int32, number of clusters)
-    py::tuple dbscan(float radius, int min_pts) {
+    py::tuple dbscan(double radius, int min_pts) {
         auto lab = result_array<int32_t>({(py::ssize_t)size()});
         int32_t nc = 0;
         check(pcp_dbscan(ix_, radius, min_pts, PCP_HOST, lab.mutable_data(), &nc), "pcp_dbscan");
         return py::make_tuple(lab, nc);
     }
-    int dbscan_device(float radius, int min_pts, uintptr_t labels) {
+    int dbscan_device(double radius, int min_pts, uintptr_t labels) {
         int32_t nc = 0;
         check(pcp_dbscan(ix_, radius, min_pts, PCP_DEVICE, reinterpret_cast<int32_t *>(labels), &nc), "pcp_dbscan");
         return nc;
@@ -583,6 +592,8 @@ PYBIND11_MODULE(_pcp, m) {
         .def("rebuild", &Index::rebuild, py::arg("points"))
         .def("rebuild_device", &Index::rebuild_device, py::arg("device_ptr"), py::arg("n"), py::arg("stride_floats") = 3)
         .def("size", &Index::size)
+        .def("attach_f64", &Index::attach_f64, py::arg("xyz"))
+        .def("neighbor_counts_f64", &Index::neighbor_counts_f64, py::arg("radius"))
         .def("stats", &Index::stats)
         .def("knn", &Index::knn, py::arg("queries"), py::arg("k"))
         .def("knn_self", &Index::knn_self, py::arg("k"))

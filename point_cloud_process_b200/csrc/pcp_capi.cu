@@ -371,6 +371,7 @@ int pcp_index_rebuild(pcp_index *ix, const float *xyz, int64_t n, int64_t stride
     PCP_TRY(check_cloud("pcp_index_build", xyz, n, stride, mem));
     pcp_ctx *ctx = ix->ctx;
     DeviceGuard g(ctx->device);
+    ix->xyz64_n = -1;                                   // float64 rows of an earlier cloud do not describe this one
     const float *d_xyz = xyz;
     if (mem == PCP_HOST && n > 0) {
         PCP_TRY(upload(ctx, 0, ix->src_copy, xyz, sizeof(float) * (size_t)n * (size_t)stride));
@@ -381,6 +382,37 @@ int pcp_index_rebuild(pcp_index *ix, const float *xyz, int64_t n, int64_t stride
     // PCP_HOST: the caller's buffer is free once the upload is done; the build itself stays queued (every later
     // call on this context is ordered behind it on the stream)
     if (mem == PCP_HOST && n > 0) PCP_CUDA(cudaEventSynchronize(ctx->ev_copy));
+    return PCP_OK;
+}
+
+int pcp_index_attach_f64(pcp_index *ix, const double *xyz, int64_t n, int64_t stride, int mem) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_index_attach_f64: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_index_attach_f64: mem must be PCP_HOST or PCP_DEVICE");
+    if (n != ix->n) return fail(PCP_ERR_INVALID, "pcp_index_attach_f64: row count differs from the indexed cloud");
+    if (stride < 3) return fail(PCP_ERR_INVALID, "pcp_index_attach_f64: stride_doubles must be >= 3");
+    if (n > 0 && !xyz) return fail(PCP_ERR_INVALID, "pcp_index_attach_f64: xyz is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    std::vector<double> rows((size_t)n * (size_t)stride), packed((size_t)n * 3);
+    if (n > 0) {
+        if (mem == PCP_DEVICE) {
+            PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+            PCP_CUDA(cudaMemcpy(rows.data(), xyz, sizeof(double) * rows.size(), cudaMemcpyDeviceToHost));
+            xyz = rows.data();
+        }
+        double mx = 0.0;
+        for (int64_t i = 0; i < n; ++i)
+            for (int a = 0; a < 3; ++a) {
+                const double v = xyz[i * stride + a];
+                packed[(size_t)i * 3 + a] = v;
+                mx = std::max(mx, std::fabs(v));
+            }
+        ix->xyz64_max_abs = mx;
+        PCP_TRY(ix->xyz64.ensure(sizeof(double) * packed.size()));
+        PCP_CUDA(cudaMemcpyAsync(ix->xyz64.p, packed.data(), sizeof(double) * packed.size(), cudaMemcpyHostToDevice, ctx->stream));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ix->xyz64_n = n;
     return PCP_OK;
 }
 
@@ -406,6 +438,7 @@ int pcp_index_destroy(pcp_index *ix) {
     cudaStreamSynchronize(ix->ctx->stream);
     ix->b.release();
     ix->src_copy.release();
+    ix->xyz64.release();
     delete ix;
     return PCP_OK;
 }
@@ -820,11 +853,11 @@ int pcp_pca(pcp_ctx *ctx, const float *xyz, int64_t n, int64_t stride, int mem, 
     return pca_device(ctx, d_xyz, n, stride, eigenvalues, eigenvectors);
 }
 
-int pcp_iss_keypoints(pcp_index *ix, float radius, double lambda21, double lambda32, float non_max_radius, int iss_count,
+int pcp_iss_keypoints(pcp_index *ix, double radius, double lambda21, double lambda32, double non_max_radius, int iss_count,
                       int32_t *keypoints, int32_t *n_keypoints, double *lambda3) {
     if (!ix) return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: index is NULL");
     if (!keypoints || !n_keypoints) return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: keypoints/n_keypoints is NULL");
-    if (!(radius > 0.f) || !(non_max_radius >= 0.f) || std::isnan(lambda21) || std::isnan(lambda32) || iss_count < 0)
+    if (!(radius > 0.0) || !(non_max_radius >= 0.0) || std::isnan(lambda21) || std::isnan(lambda32) || iss_count < 0)
         return fail(PCP_ERR_INVALID, "pcp_iss_keypoints: radius must be > 0, non_max_radius >= 0, iss_count >= 0");
     *n_keypoints = 0;
     const int64_t n = ix->n;
@@ -844,10 +877,28 @@ int pcp_iss_keypoints(pcp_index *ix, float radius, double lambda21, double lambd
     return PCP_OK;
 }
 
-int pcp_dbscan(pcp_index *ix, float radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters) {
+int pcp_neighbor_counts_f64(pcp_index *ix, double radius, int64_t *counts) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_neighbor_counts_f64: index is NULL");
+    if (!(radius >= 0.0)) return fail(PCP_ERR_INVALID, "pcp_neighbor_counts_f64: radius must be >= 0");
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    if (!counts) return fail(PCP_ERR_INVALID, "pcp_neighbor_counts_f64: counts is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    PCP_TRY(ctx->scratch[7].ensure(sizeof(int64_t) * (size_t)(n + 1)));
+    int64_t *d_off = ctx->scratch[7].as<int64_t>();
+    PCP_TRY(radius_count_device(ix, ix->built_from, n, ix->built_stride, (float)radius, d_off, true, radius));
+    std::vector<int64_t> off((size_t)n + 1);
+    PCP_CUDA(cudaMemcpyAsync(off.data(), d_off, sizeof(int64_t) * off.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int64_t i = 0; i < n; ++i) counts[i] = off[(size_t)i + 1] - off[(size_t)i];
+    return PCP_OK;
+}
+
+int pcp_dbscan(pcp_index *ix, double radius, int min_pts, int mem, int32_t *labels, int32_t *n_clusters) {
     if (!ix) return fail(PCP_ERR_INVALID, "pcp_dbscan: index is NULL");
     if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_dbscan: mem must be PCP_HOST or PCP_DEVICE");
-    if (!(radius >= 0.f)) return fail(PCP_ERR_INVALID, "pcp_dbscan: radius must be >= 0");
+    if (!(radius >= 0.0)) return fail(PCP_ERR_INVALID, "pcp_dbscan: radius must be >= 0");
     int32_t dummy = 0;
     if (!n_clusters) n_clusters = &dummy;
     *n_clusters = 0;

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(256) db_label_kernel(const long long *__restri
 
 }  // namespace
 
-int dbscan_device(pcp_index *ix, float radius, int min_pts, int32_t *d_labels, int32_t *h_n_clusters) {
+int dbscan_device(pcp_index *ix, double radius, int min_pts, int32_t *d_labels, int32_t *h_n_clusters) {
     pcp_ctx *ctx = ix->ctx;
     cudaStream_t st = ctx->stream;
     const int64_t n = ix->n;
@@ -190,13 +190,14 @@ int dbscan_device(pcp_index *ix, float radius, int min_pts, int32_t *d_labels, i
     const int64_t stride = ix->built_stride;
     DevBuf &b_off = ctx->iss_buf[0], &b_idx = ctx->iss_buf[1], &b_dist = ctx->iss_buf[2], &b_misc = ctx->iss_buf[3];
     PCP_TRY(b_off.ensure(sizeof(int64_t) * (size_t)(n + 1)));
-    PCP_TRY(radius_count_device(ix, d_xyz, n, stride, radius, b_off.as<int64_t>()));
+    // neighbourhoods as scipy's float64 KDTree decides them (dbscan.py:13)
+    PCP_TRY(radius_count_device(ix, d_xyz, n, stride, (float)radius, b_off.as<int64_t>(), true, radius));
     long long M = 0;
     PCP_CUDA(cudaMemcpyAsync(&M, b_off.as<int64_t>() + n, sizeof(M), cudaMemcpyDeviceToHost, st));
     PCP_CUDA(cudaStreamSynchronize(st));
     PCP_TRY(b_idx.ensure(sizeof(int32_t) * (size_t)M));
     PCP_TRY(b_dist.ensure(sizeof(float) * (size_t)M));
-    PCP_TRY(radius_fill_device(ix, d_xyz, n, stride, radius, b_off.as<int64_t>(), b_idx.as<int32_t>(), b_dist.as<float>(), 0));
+    PCP_TRY(radius_fill_device(ix, d_xyz, n, stride, (float)radius, b_off.as<int64_t>(), b_idx.as<int32_t>(), b_dist.as<float>(), 0, true, radius));
     const long long *off = b_off.as<long long>();
     const int32_t *nbr = b_idx.as<int32_t>();
     // misc: comp | vmax | umax | flag | incl (n int each) | counters (4 u32) | kind | state (n u8 each)

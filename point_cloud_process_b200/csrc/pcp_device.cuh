@@ -126,6 +126,29 @@ __device__ __forceinline__ float d2_gate(float s) {
     return __fmul_ru(__fmul_ru(s, s), 1.00000024f);
 }
 
+// Radius predicate.  Default (lesson2 contract, result_set.py:80 on float32 distances): d2 <= lo with lo = hi = the
+// largest float32 d2 whose rounded sqrt is <= r.  exact64 (the consumers whose reference searches with scipy's
+// float64 cKDTree: ISS.py:40, dbscan.py:13): a float32 d2 at or below `lo` is certainly inside and one above `hi`
+// certainly outside the float64 ball; in the band between them the pair is decided in float64 -- differences and
+// squares in cKDTree's order (x, y, z accumulated left to right, unfused) against r * r -- on the float64 originals
+// of the rows when they are attached (pcp_index_attach_f64), else on the float32 rows widened exactly.
+struct RadiusTest {
+    float lo, hi;
+    double r2;
+    const double *q64, *p64;     // float64 rows of the queries / the indexed cloud (3 doubles per row), or nullptr
+};
+__device__ __forceinline__ bool radius_hit(const RadiusTest &t, float d2, float qx, float qy, float qz, float px, float py,
+                                           float pz, long long qrow, unsigned prow) {
+    if (d2 <= t.lo) return true;                 // NaN pads never hit
+    if (!(d2 <= t.hi)) return false;
+    double ax = qx, ay = qy, az = qz, bx = px, by = py, bz = pz;
+    if (t.q64) { ax = t.q64[qrow * 3]; ay = t.q64[qrow * 3 + 1]; az = t.q64[qrow * 3 + 2]; }
+    if (t.p64) { bx = t.p64[(long long)prow * 3]; by = t.p64[(long long)prow * 3 + 1]; bz = t.p64[(long long)prow * 3 + 2]; }
+    const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    const double d = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    return d <= t.r2;
+}
+
 // (distance, index) packed so that one unsigned 64-bit compare is the lexicographic order:
 // distances are >= +0, whose IEEE bit patterns are monotone as unsigned integers.
 __device__ __forceinline__ unsigned long long pack_key(float s, unsigned idx) {

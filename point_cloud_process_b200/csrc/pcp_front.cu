@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(256) iss_nms_round_kernel(const unsigned *__re
 
 }  // namespace
 
-int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, float nms_radius, int iss_count,
+int iss_device(pcp_index *ix, double radius, double lambda21, double lambda32, double nms_radius, int iss_count,
                int32_t *h_keypoints, int32_t *h_n_keypoints, double *d_lambda3_out) {
     pcp_ctx *ctx = ix->ctx;
     cudaStream_t st = ctx->stream;
@@ -743,14 +743,14 @@ int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, fl
     const float *d_xyz = ix->built_from;
     const int64_t stride = ix->built_stride;
     DevBuf &b_off = ctx->iss_buf[0], &b_idx = ctx->iss_buf[1], &b_dist = ctx->iss_buf[2], &b_misc = ctx->iss_buf[3];
-    auto csr = [&](float r, long long *M) -> int {
+    auto csr = [&](double r, long long *M) -> int {   // neighbourhoods as scipy's float64 cKDTree decides them (ISS.py:40)
         PCP_TRY(b_off.ensure(sizeof(int64_t) * (size_t)(n + 1)));
-        PCP_TRY(radius_count_device(ix, d_xyz, n, stride, r, b_off.as<int64_t>()));
+        PCP_TRY(radius_count_device(ix, d_xyz, n, stride, (float)r, b_off.as<int64_t>(), true, r));
         PCP_CUDA(cudaMemcpyAsync(M, b_off.as<int64_t>() + n, sizeof(long long), cudaMemcpyDeviceToHost, st));
         PCP_CUDA(cudaStreamSynchronize(st));
         PCP_TRY(b_idx.ensure(sizeof(int32_t) * (size_t)*M));
         PCP_TRY(b_dist.ensure(sizeof(float) * (size_t)*M));
-        return radius_fill_device(ix, d_xyz, n, stride, r, b_off.as<int64_t>(), b_idx.as<int32_t>(), b_dist.as<float>(), 0);
+        return radius_fill_device(ix, d_xyz, n, stride, (float)r, b_off.as<int64_t>(), b_idx.as<int32_t>(), b_dist.as<float>(), 0, true, r);
     };
     long long M = 0;
     PCP_TRY(csr(radius, &M));

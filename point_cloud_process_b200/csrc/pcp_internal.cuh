@@ -10,6 +10,8 @@
 
 #include "pcp.h"
 
+namespace pcp { struct RadiusTest; }
+
 namespace pcp {
 
 // ------------------------------------------------------------------------------------------------
@@ -157,6 +159,10 @@ struct pcp_index {
     int64_t built_stride = 0;
     pcp::BatchIndex b;       // P == 1
     pcp::DevBuf src_copy;
+    // float64 originals of the indexed rows (pcp_index_attach_f64): n x 3 doubles, dropped by the next rebuild
+    pcp::DevBuf xyz64;
+    int64_t xyz64_n = -1;
+    double xyz64_max_abs = 0.0;
 };
 
 namespace pcp {
@@ -186,15 +192,17 @@ int knn_warp_list_device(pcp_index *ix, bool self, const float *d_q, int64_t nq,
                          float *d_dist, int32_t *d_count);
 // 0 = choose by query count, 1 = warp-per-query kernel, 2 = tiled kernel (PCP_KNN_KERNEL=warp|tile, for tests)
 int knn_kernel_choice();
+// exact64: borderline pairs are decided in float64 (RadiusTest, pcp_device.cuh) -- scipy's semantics for ISS / DBSCAN
 int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
-                        int64_t *d_offsets);
+                        int64_t *d_offsets, bool exact64 = false, double radius64 = -1.0);
 int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
-                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted);
+                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted, bool exact64 = false,
+                       double radius64 = -1.0);
 // tiled kernel (pcp_radius_tile.cu): COUNT when d_counts != nullptr, else FILL
 int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
-                            const uint32_t *d_list, float d2max, long long *d_counts, const long long *d_offsets,
+                            const uint32_t *d_list, const RadiusTest &d2max, long long *d_counts, const long long *d_offsets,
                             int32_t *d_idx, float *d_dist);
-int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
+int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, const RadiusTest &d2max,
                        long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist);
 
 // brute force over the whole cloud (pcp_brute.cu): the on-device exhaustive cross-check
@@ -213,10 +221,10 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, c
 int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double leaf, int mode,
                         unsigned long long seed, int64_t *n_out);
 int normals_device(pcp_index *ix, int k, double *d_normals, double *d_evals);
-int iss_device(pcp_index *ix, float radius, double lambda21, double lambda32, float nms_radius, int iss_count,
+int iss_device(pcp_index *ix, double radius, double lambda21, double lambda32, double nms_radius, int iss_count,
                int32_t *h_keypoints, int32_t *h_n_keypoints, double *d_lambda3_out);
 // DBSCAN on the radius CSR (pcp_dbscan.cu)
-int dbscan_device(pcp_index *ix, float radius, int min_pts, int32_t *d_labels, int32_t *h_n_clusters);
+int dbscan_device(pcp_index *ix, double radius, int min_pts, int32_t *d_labels, int32_t *h_n_clusters);
 int pca_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t stride, double *h_w, double *h_V);
 
 int procrustes_device(pcp_ctx *ctx, const double *d_A, const double *d_B, int64_t n, double *h_R, double *h_t,

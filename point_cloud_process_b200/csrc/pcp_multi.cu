@@ -15,6 +15,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -45,6 +46,11 @@ NcclApi &nccl() {
             api.lib = dlopen(name, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
             if (api.lib) break;
         }
+        // PCP_NCCL_LIB: an explicit path (multi.py points it at the NCCL wheel next to torch, so that a later
+        // `import torch` in the same process finds its own, newer libnccl.so.2 already loaded instead of an older
+        // system copy under the same soname)
+        if (!api.lib)
+            if (const char *path = getenv("PCP_NCCL_LIB")) api.lib = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
         if (!api.lib)
             for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
                 api.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
@@ -157,8 +163,10 @@ int pcp_multi_info(const pcp_multi *m, int *rank, int *world, int *nccl_version,
     if (world) *world = m->world;
     if (nccl_version) {
         *nccl_version = 0;
-        NcclApi &api = nccl();
-        if (m->world > 1 && api.GetVersion) api.GetVersion(nccl_version);
+        if (m->world > 1) {                      // (a single rank never loads NCCL)
+            NcclApi &api = nccl();
+            if (api.GetVersion) api.GetVersion(nccl_version);
+        }
     }
     if (comm_nranks) *comm_nranks = m->comm ? m->world : 1;
     return PCP_OK;

@@ -40,15 +40,24 @@ float exact_d2_threshold(float r) {
 
 namespace {
 
+// launch radius_kernel<FILL, LIST, EXACT> with EXACT chosen at run time
+#define PCP_RADIUS_LAUNCH(FILL_, LIST_, rt_, grid_, ...)                                                           \
+    do {                                                                                                          \
+        if ((rt_).lo != (rt_).hi || (rt_).p64)                                                                    \
+            radius_kernel<FILL_, LIST_, true><<<grid_, kWarpsPerCta * 32, 0, ctx->stream>>>(__VA_ARGS__);           \
+        else                                                                                                      \
+            radius_kernel<FILL_, LIST_, false><<<grid_, kWarpsPerCta * 32, 0, ctx->stream>>>(__VA_ARGS__);          \
+    } while (0)
+
 constexpr int kWarpsPerCta = 8;
 constexpr int kStack = kMaxLevels * kFan;
 
 // LIST = false: warp w of the grid takes query w.
 // LIST = true:  persistent warps drain the hand-over list of the tiled kernel (pcp_radius_tile.cu): list[0] =
 //               number of groups, list[1..] = group ids; item w -> regrouped position list[1 + w / 32] * 32 + w % 32.
-template <bool FILL, bool LIST>
+template <bool FILL, bool LIST, bool EXACT>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-radius_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, float d2max,
+radius_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, const RadiusTest rt,
               long long *__restrict__ counts, const long long *__restrict__ offsets, int *__restrict__ out_idx,
               float *__restrict__ out_dist, unsigned long long *__restrict__ ctr, const unsigned *__restrict__ list,
               const unsigned *__restrict__ perm) {
@@ -75,7 +84,8 @@ radius_kernel(const IndexView ix, const float *__restrict__ queries, long long n
         ++n_scan;
         const float4 p = __ldg(ix.pts + leaf * kLeaf + lane);
         const float d2 = ref_d2(qx, qy, qz, p.x, p.y, p.z);
-        const bool hit = d2 <= d2max;                       // NaN pads never hit
+        // NaN pads never hit.  EXACT: borderline pairs are decided in float64 (RadiusTest, pcp_device.cuh)
+        const bool hit = EXACT ? radius_hit(rt, d2, qx, qy, qz, p.x, p.y, p.z, qi, __float_as_uint(p.w)) : d2 <= rt.hi;
         const unsigned m = __ballot_sync(kFullMask, hit);
         if (FILL && hit) {
             const long long o = base + total + __popc(m & lt_mask);
@@ -104,7 +114,7 @@ radius_kernel(const IndexView ix, const float *__restrict__ queries, long long n
             bool hit = false;
             if (c < ix.level_cnt[lv - 1]) {
                 const long long b = ix.level_off[lv - 1] + c;
-                hit = box_lb2(qx, qy, qz, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)) <= d2max;
+                hit = box_lb2(qx, qy, qz, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)) <= rt.hi;
             }
             unsigned m = __ballot_sync(kFullMask, hit);
             if (lv == 1) {
@@ -171,24 +181,48 @@ int radius_query_perm(pcp_index *ix, const float *d_q, int64_t nq, int64_t strid
 
 // Groups the tiled kernel handed over (its stragglers), one warp per query, persistent grid.
 int radius_warp_list_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
-                            const uint32_t *d_list, float d2max, long long *d_counts, const long long *d_offsets,
+                            const uint32_t *d_list, const RadiusTest &d2max, long long *d_counts, const long long *d_offsets,
                             int32_t *d_idx, float *d_dist) {
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
     const unsigned grid = (unsigned)ctx->sm_count * 8;
     if (d_counts)
-        radius_kernel<false, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, d_counts, nullptr,
+        PCP_RADIUS_LAUNCH(false, true, d2max, grid, v, d_q, nq, stride, d2max, d_counts, nullptr,
                                                                                nullptr, nullptr, ctx->ctr(), d_list, d_perm);
     else
-        radius_kernel<true, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, nullptr, d_offsets,
+        PCP_RADIUS_LAUNCH(true, true, d2max, grid, v, d_q, nq, stride, d2max, nullptr, d_offsets,
                                                                               d_idx, d_dist, ctx->ctr(), d_list, d_perm);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
 }
 
+// exact64: decide borderline pairs in float64 (RadiusTest, pcp_device.cuh); the float64 rows attached to the index
+// are used when the queries ARE the indexed cloud (the ISS / DBSCAN case).
+RadiusTest make_radius_test(const pcp_index *ix, const float *d_q, int64_t nq, float radius, bool exact64, double radius64) {
+    RadiusTest t;
+    t.lo = t.hi = exact_d2_threshold(radius);
+    t.r2 = (double)radius * (double)radius;
+    t.q64 = t.p64 = nullptr;
+    if (!exact64 || !(radius >= 0.f) || std::isinf(radius)) return t;
+    double E = 0.0;                                     // float32 rounding of attached float64 coordinates
+    const bool same = d_q == ix->built_from && nq == ix->n;
+    if (ix->xyz64.p && ix->xyz64_n == ix->n) {
+        t.p64 = ix->xyz64.as<double>();
+        if (same) t.q64 = t.p64;
+        E = std::sqrt(3.0) * ix->xyz64_max_abs * 1.2e-7 * (same ? 2.0 : 1.0);
+    }
+    const double r = radius64 >= 0.0 ? radius64 : (double)radius, rel = 1.0e-6;
+    t.r2 = r * r;      // > 8 x 2^-24: the float32 evaluation's own rounding
+    const double lo = r > E ? (r - E) * (r - E) * (1.0 - rel) : -1.0, hi = (r + E) * (r + E) * (1.0 + rel);
+    t.lo = lo < 0.0 ? -1.f : nextafterf((float)lo, -1.f);
+    t.hi = nextafterf((float)hi, INFINITY);
+    if (!(t.hi < 3.0e38f)) t.hi = 3.0e38f;
+    return t;
+}
+
 int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
-                        int64_t *d_offsets) {
+                        int64_t *d_offsets, bool exact64, double radius64) {
     pcp_ctx *ctx = ix->ctx;
     set_zero_kernel<<<1, 1, 0, ctx->stream>>>(reinterpret_cast<long long *>(d_offsets));
     ctx->launches += 1;
@@ -199,7 +233,7 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
         PCP_CUDA(cudaMemsetAsync(d_offsets, 0, sizeof(int64_t) * (size_t)(nq + 1), ctx->stream));
         return PCP_OK;
     }
-    const float d2max = exact_d2_threshold(radius);
+    const RadiusTest d2max = make_radius_test(ix, d_q, nq, radius, exact64, radius64);
     const IndexView v = make_view(ix);
     if (use_tile(nq)) {
         const uint32_t *perm = nullptr;
@@ -207,7 +241,7 @@ int radius_count_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t str
         PCP_TRY(radius_tile_device(ix, d_q, nq, stride, perm, d2max, counts, nullptr, nullptr, nullptr));
     } else {
         const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-        radius_kernel<false, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, d2max, counts, nullptr,
+        PCP_RADIUS_LAUNCH(false, false, d2max, grid, v, d_q, nq, stride, d2max, counts, nullptr,
                                                                                 nullptr, nullptr, ctx->ctr(), nullptr,
                                                                                 nullptr);
         ctx->launches += 1;
@@ -240,10 +274,10 @@ __global__ void __launch_bounds__(256) unpack_pairs_kernel(const unsigned long l
 }  // namespace
 
 int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float radius,
-                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted) {
+                       const int64_t *d_offsets, int32_t *d_idx, float *d_dist, int sorted, bool exact64, double radius64) {
     pcp_ctx *ctx = ix->ctx;
     if (nq == 0 || ix->n == 0) return PCP_OK;
-    const float d2max = exact_d2_threshold(radius);
+    const RadiusTest d2max = make_radius_test(ix, d_q, nq, radius, exact64, radius64);
     const IndexView v = make_view(ix);
     // FILL kernel choice.  The tiled FILL stages hits in shared memory and writes 64-byte runs; it walks the
     // hierarchy once per 32 queries and wins on large query sets at every result density (1 M uniform queries:
@@ -262,8 +296,7 @@ int radius_fill_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
                                    d_idx, d_dist));
     } else {
         const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
-        radius_kernel<true, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(
-            v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr(),
+        PCP_RADIUS_LAUNCH(true, false, d2max, grid, v, d_q, nq, stride, d2max, nullptr, reinterpret_cast<const long long *>(d_offsets), d_idx, d_dist, ctx->ctr(),
             nullptr, nullptr);
         ctx->launches += 1;
     }

@@ -30,10 +30,11 @@ constexpr int kRtChunk = 8;
 constexpr int kRtCap = 16;
 template <bool FILL> struct RtCfg { static constexpr int kWarps = FILL ? 4 : 8; };
 
-template <bool FILL>
+// EXACT: borderline pairs are decided in float64 (RadiusTest); else the plain float32 compare d2 <= rt.hi (== rt.lo)
+template <bool FILL, bool EXACT>
 __global__ void __launch_bounds__(RtCfg<FILL>::kWarps * 32)
 radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const unsigned *__restrict__ perm,
-                   long long nq, long long stride, float d2max, long long *__restrict__ counts,
+                   long long nq, long long stride, const RadiusTest rt, long long *__restrict__ counts,
                    const long long *__restrict__ offsets, int *__restrict__ out_idx, float *__restrict__ out_dist,
                    unsigned long long *__restrict__ ctr, unsigned *__restrict__ sched, unsigned *__restrict__ handover,
                    unsigned n_groups, unsigned tail_slots) {
@@ -70,7 +71,7 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
             qx = __ldg(q); qy = __ldg(q + 1); qz = __ldg(q + 2);
         }
         const bool active = qid >= 0;
-        const float gate = active ? d2max : -1.f;       // inactive lanes: nothing passes
+        const float gate = active ? rt.hi : -1.f;       // inactive lanes: nothing passes (box tests; points: radius_hit)
         float3 glo, ghi;
         glo.x = warp_min(active ? qx : FLT_MAX); glo.y = warp_min(active ? qy : FLT_MAX); glo.z = warp_min(active ? qz : FLT_MAX);
         ghi.x = warp_max(active ? qx : -FLT_MAX); ghi.y = warp_max(active ? qy : -FLT_MAX); ghi.z = warp_max(active ? qz : -FLT_MAX);
@@ -125,7 +126,7 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
                 bool hit = false;
                 if (present) {
                     const long long b = ix.level_off[lv - 1] + c;
-                    hit = boxbox_lb2(glo, ghi, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)) <= d2max;
+                    hit = boxbox_lb2(glo, ghi, __ldg(ix.box_lo + b), __ldg(ix.box_hi + b)) <= rt.hi;
                 }
                 const unsigned m = __ballot_sync(kFullMask, hit);
                 if (hit) stack[sp + __popc(m & lt_mask)] = ((unsigned)(lv - 1) << 27) | (unsigned)c;
@@ -139,8 +140,8 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
                 const float4 *h = ix.half + c * 4;
                 const float4 alo = __ldg(h), ahi = __ldg(h + 1), blo = __ldg(h + 2), bhi = __ldg(h + 3);
                 boxes[4 * lane] = alo; boxes[4 * lane + 1] = ahi; boxes[4 * lane + 2] = blo; boxes[4 * lane + 3] = bhi;
-                ha = boxbox_lb2(glo, ghi, alo, ahi) <= d2max;
-                hb = boxbox_lb2(glo, ghi, blo, bhi) <= d2max;
+                ha = boxbox_lb2(glo, ghi, alo, ahi) <= rt.hi;
+                hb = boxbox_lb2(glo, ghi, blo, bhi) <= rt.hi;
             }
             const unsigned ma = __ballot_sync(kFullMask, ha), mb = __ballot_sync(kFullMask, hb);
             unsigned m = ma | mb;
@@ -171,7 +172,9 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
 #pragma unroll
                     for (int i = 0; i < kRtChunk; ++i) {
                         const float d2 = ref_d2(qx, qy, qz, p[i].x, p[i].y, p[i].z);
-                        if (d2 <= gate) {                            // NaN pads never hit
+                        const bool hit = EXACT ? (active && radius_hit(rt, d2, qx, qy, qz, p[i].x, p[i].y, p[i].z, qid, __float_as_uint(p[i].w)))
+                                               : d2 <= gate;                 // NaN pads never hit
+                        if (hit) {
                             if (FILL) {
                                 asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(waddr), "f"(p[i].w), "f"(d2) : "memory");
                                 waddr += 8;
@@ -205,7 +208,7 @@ radius_tile_kernel(const IndexView ix, const float *__restrict__ queries, const 
 }  // namespace
 
 // COUNT (counts != nullptr) or FILL (offsets/out_* != nullptr) over queries regrouped by d_perm.
-int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, float d2max,
+int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, const RadiusTest &d2max,
                        long long *d_counts, const long long *d_offsets, int32_t *d_idx, float *d_dist) {
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
@@ -219,14 +222,19 @@ int radius_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stri
     const unsigned grid = (unsigned)std::min<long long>((n_groups + warps - 1) / warps, (long long)ctx->sm_count * 6);
     static const char *e_tail = getenv("PCP_TILE_TAIL");   // developer override (share of the warp slots; 0 = off)
     const unsigned tail_slots = (unsigned)((e_tail ? atof(e_tail) : 0.05) * (double)grid * warps);
-    if (d_counts)
-        radius_tile_kernel<false><<<grid, warps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, d_counts,
-                                                                          nullptr, nullptr, nullptr, ctx->ctr(), sched,
-                                                                          handover, (unsigned)n_groups, tail_slots);
-    else
-        radius_tile_kernel<true><<<grid, warps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, nullptr,
-                                                                         d_offsets, d_idx, d_dist, ctx->ctr(), sched,
-                                                                         handover, (unsigned)n_groups, tail_slots);
+    const bool exact = d2max.lo != d2max.hi || d2max.p64 != nullptr;
+#define PCP_RT(FILL_, EXACT_, counts_, offs_, idx_, dist_)                                                              \
+    radius_tile_kernel<FILL_, EXACT_><<<grid, warps * 32, 0, ctx->stream>>>(v, d_q, d_perm, nq, stride, d2max, counts_, \
+                                                                            offs_, idx_, dist_, ctx->ctr(), sched,       \
+                                                                            handover, (unsigned)n_groups, tail_slots)
+    if (d_counts) {
+        if (exact) PCP_RT(false, true, d_counts, nullptr, nullptr, nullptr);
+        else PCP_RT(false, false, d_counts, nullptr, nullptr, nullptr);
+    } else {
+        if (exact) PCP_RT(true, true, nullptr, d_offsets, d_idx, d_dist);
+        else PCP_RT(true, false, nullptr, d_offsets, d_idx, d_dist);
+    }
+#undef PCP_RT
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return radius_warp_list_device(ix, d_q, nq, stride, d_perm, handover, d2max, d_counts, d_offsets, d_idx, d_dist);

@@ -27,7 +27,11 @@ class DBSCAN(object):
         if data.shape[1] == 2:
             data = np.concatenate([data, np.zeros((len(data), 1), data.dtype)], axis=1)
         ix = SearchIndex(data, device=self._device, ctx=self._ctx)
-        labels, self.n_clusters_ = ix._ix.dbscan(float(np.float32(self.radius)), int(self.Min_Pts))
+        if data.dtype == np.float64:
+            # the reference searches the float64 rows with scipy's KDTree (dbscan.py:13): the float32 search structure
+            # finds the candidates, borderline pairs are decided on these originals (pcp_index_attach_f64)
+            ix._ix.attach_f64(np.ascontiguousarray(data))
+        labels, self.n_clusters_ = ix._ix.dbscan(float(self.radius), int(self.Min_Pts))
         self.labels_ = np.asarray(labels, dtype=np.int32)
 
     def predict(self):

@@ -86,11 +86,31 @@ def exchange_bytes(payload, rank, world, addr=None, port=None, timeout=120.0):
             time.sleep(0.05)
 
 
+def prefer_bundled_nccl():
+    """Point the library's run-time NCCL binding (PCP_NCCL_LIB) at the NCCL wheel installed beside torch, when there
+    is one and nothing was chosen: a process that later imports torch then finds ITS libnccl.so.2 already loaded
+    instead of an older system copy under the same soname.  No torch import here."""
+    if os.environ.get("PCP_NCCL_LIB"):
+        return os.environ["PCP_NCCL_LIB"]
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            p = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(p):
+                os.environ["PCP_NCCL_LIB"] = p
+                return p
+    except Exception:   # noqa: BLE001
+        pass
+    return None
+
+
 def exchange_unique_id(rank, world, addr=None, port=None):
     """The NCCL unique id of rank 0 (pcp_multi_unique_id) on every rank; None for a single rank."""
     if world == 1:
         return None
     from . import native
+    prefer_bundled_nccl()
     uid = native.Multi.unique_id() if rank == 0 else b""
     return exchange_bytes(uid, rank, world, addr, port)
 
@@ -105,6 +125,8 @@ def create(rank=None, world=None, device=None, unique_id=None, ctx=None, addr=No
     world = e_world if world is None else world
     device = e_local if device is None else device
     ctx = ctx or default_context(device)
+    if world > 1:
+        prefer_bundled_nccl()
     if world > 1 and unique_id is None:
         unique_id = exchange_unique_id(rank, world, addr, port)
     return native.Multi(ctx, rank, world, unique_id)

@@ -295,3 +295,45 @@ def test_dbscan_kitti_properties(pcp, kitti):
     # cluster numbers follow the seeds' descending index: the first cluster contains the last seedable point
     seedable = np.flatnonzero(cnt >= 10)
     assert lab[seedable[-1]] == 0
+
+
+def test_float64_neighbourhoods_match_scipy_on_the_full_kitti_scan(pcp, kitti):
+    """ISS.py:38-40 and dbscan.py:13 search with scipy's float64 cKDTree.  On the full scan (r = 1.0, 80.2 M pairs) the
+    float32 predicate of the lesson2 search (result_set.py:80) and the float64 one differ for a few dozen pairs that
+    sit within float32 rounding of the radius; the neighbourhood sizes ISS and DBSCAN are built on must equal scipy's."""
+    from scipy.spatial import cKDTree
+    ix = pcp.SearchIndex(kitti)
+    got = ix._ix.neighbor_counts_f64(1.0)
+    p64 = kitti.astype(np.float64)
+    want = cKDTree(p64).query_ball_point(p64, 1.0, return_length=True, workers=-1)
+    assert np.array_equal(got, want)
+    off, _, _ = ix.radius(kitti, 1.0)
+    f32 = np.diff(off)
+    assert int(np.abs(f32 - want).sum()) > 0        # the test bites: the float32 predicate is NOT scipy's on this scan
+
+
+def test_float64_clouds_keep_their_float64_neighbourhoods(pcp):
+    """A cloud that is not representable in float32 (ModelNet40 .txt rows are decimal fractions): the float64
+    originals are attached to the float32 search structure and decide the borderline pairs, for a radius that is
+    not a float32 either."""
+    from scipy.spatial import cKDTree
+    from oracle import front_oracle
+    from point_cloud_process_b200.dbscan import DBSCAN
+    rng = np.random.default_rng(41)
+    r = 0.3
+    pts = rng.random((30000, 3)) * 6.0
+    # planted borderline pairs: neighbours at r (1 -+ 1e-12) along x, far below float32 resolution
+    pts[:200, 0] = 100.0 + np.arange(200) * 3.0
+    pts[:200, 1:] = 0.0
+    pts[200:400] = pts[:200] + [r * (1 - 1e-12), 0, 0]
+    pts[400:600] = pts[:200] - [r * (1 + 1e-12), 0, 0]
+    want = cKDTree(pts).query_ball_point(pts, r, return_length=True, workers=-1)
+    assert (want[:200] == 2).all()                                   # itself + the neighbour just inside
+    ix = pcp.SearchIndex(pts)
+    ix._ix.attach_f64(pts)
+    assert np.array_equal(ix._ix.neighbor_counts_f64(r), want)
+    # DBSCAN end to end on float64 rows (the class attaches them itself): labels of the reference's sequential loop
+    blobs = rng.normal(0, 0.35, (4000, 3)) + rng.integers(0, 5, (4000, 1)) * np.array([2.5, 0, 0])
+    d = DBSCAN(radius=0.2, Min_Pts=6)
+    d.fit(blobs)
+    assert np.array_equal(d.predict(), front_oracle.dbscan_labels(blobs, 0.2, 6))

@@ -20,6 +20,7 @@ def timeit(stream, fn, reps=10, warm=2):
 
 
 def search_config(name, pts, k, r, ctx, stream):
+    """Timed passes run with the work counters OFF; the evaluations come from ONE separate counted pass each."""
     n = len(pts)
     d = torch.from_numpy(pts).cuda()
     ix = native.Index(ctx, d.data_ptr(), n, 3)
@@ -32,18 +33,23 @@ def search_config(name, pts, k, r, ctx, stream):
     ctx.enable_counters(True)
     ix.knn_device(d.data_ptr(), n, 3, k, idx.data_ptr(), dist.data_ptr(), cnt.data_ptr())
     c = ctx.read_counters()
+    ctx.enable_counters(False)
     out["knn_evals_per_query"] = c[0] / n
-    out["knn_fp32_frac"] = 8.0 * c[0] / (out["knn_ms"] * 1e-3) / (148 * 128 * 1.965e9)
+    out["knn_fp32_frac_whole_search"] = 8.0 * c[0] / (out["knn_ms"] * 1e-3) / (148 * 128 * 1.965e9)
     out["radius_count_ms"] = timeit(stream, lambda: ix.radius_count_device(d.data_ptr(), n, 3, r, off.data_ptr()), reps=5)
     ctx.synchronize()
     m = int(off[-1].item())
-    ix.radius_count_device(d.data_ptr(), n, 3, r, off.data_ptr())
-    c = ctx.read_counters(); ctx.enable_counters(False)
     ridx = torch.empty(m, dtype=torch.int32, device="cuda"); rdist = torch.empty(m, dtype=torch.float32, device="cuda")
     out["radius_fill_ms"] = timeit(stream, lambda: ix.radius_fill_device(d.data_ptr(), n, 3, r, off.data_ptr(), ridx.data_ptr(), rdist.data_ptr(), False), reps=5)
+    ctx.enable_counters(True)
+    ix.radius_count_device(d.data_ptr(), n, 3, r, off.data_ptr())
+    c = ctx.read_counters()
+    ctx.enable_counters(False)
     out["radius_pairs"] = m
     out["radius_evals_per_query"] = c[0] / n
+    out["radius_count_fp32_frac"] = 8.0 * c[0] / (out["radius_count_ms"] * 1e-3) / (148 * 128 * 1.965e9)
     out["radius_fill_out_gbs"] = m * 8 / (out["radius_fill_ms"] * 1e-3) / 1e9
+    out["radius_fill_hbm_frac"] = (28 * n + 8 * (n + 1) + 8 * m) / (out["radius_fill_ms"] * 1e-3) / 1e9 / 6557.4
     out["knn_queries_per_s"] = n / (out["knn_ms"] * 1e-3)
     out["radius_queries_per_s"] = n / ((out["radius_count_ms"] + out["radius_fill_ms"]) * 1e-3)
     return out
@@ -62,7 +68,9 @@ def main():
     res.append(search_config("C3 uniform 1M in [0,25.4)^3: build + radius r=0.5 + kNN k=16", uni, 16, 0.5, ctx, stream))
     if not a.skip_icp:
         for mode in ("A", "B"):
-            r = bench.measure_icp(torch, native, ctx, stream, 0, a.pairs, 20000, mode, steps=2, warmup=1, e2e=(mode == "A"))
+            h_src, h_tgt = bench.make_pairs(0, a.pairs, 20000, os.cpu_count() or 1) if mode == "A" else (h_src, h_tgt)
+            r = bench.measure_icp(torch, pcp, ctx, stream, h_src, h_tgt, 0, a.pairs, 20000, mode, steps=2, warmup=1,
+                                  peaks=bench.load_peaks()[0], sm_count=148)
             r["config"] = f"C4 {a.pairs} synthetic pairs x 20000 pts, mode {mode} {bench.ICP_MODES[mode]}"
             r["pairs_per_s"] = a.pairs / (r["device_ms_per_batch"] * 1e-3)
             r["pair_iterations_per_s"] = sum(i * c for i, c in enumerate(r["iterations_hist"])) / (r["device_ms_per_batch"] * 1e-3)
