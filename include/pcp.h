@@ -336,6 +336,20 @@ PCP_API int pcp_multi_icp_batch(pcp_multi *m, const pcp_icp_params *params, int6
                                 int32_t *iterations, int32_t *status, double *diff_log, int64_t *first_pair,
                                 int64_t *last_pair);
 
+/* ---- PointNet++ neighbourhood layouts ----------------------------------------------------------
+ * The two search ops of the reference's own CUDA extension, same layouts and selection rules, packed float32 rows:
+ * pcp_ball_query replaces query_ball_point_kernel        _ext-src/src/ball_query_gpu.cu:9-46 (ball_query.cpp:9-34)
+ *   new_xyz (b, m, 3) centres, xyz (b, n, 3) points -> idx (b, m, nsample) int32: the FIRST nsample points in index
+ *   order with d2 < radius * radius; the tail of a short row repeats its first hit; a centre without a hit keeps 0s.
+ * pcp_three_nn replaces three_nn_kernel                  _ext-src/src/interpolate_gpu.cu:9-60
+ *   unknown (b, n, 3), known (b, m, 3) -> dist2 (b, n, 3) SQUARED distances ascending, idx (b, n, 3); strict '<',
+ *   the lowest index wins a tie; slots without a point hold (+inf, 0).
+ * d2 is the reference's float32 expression as nvcc compiles it: fma(dz, dz, fma(dx, dx, dy * dy)). */
+PCP_API int pcp_ball_query(pcp_ctx *ctx, int b, int n, int m, float radius, int nsample, const float *new_xyz,
+                           const float *xyz, int mem, int32_t *idx);
+PCP_API int pcp_three_nn(pcp_ctx *ctx, int b, int n, int m, const float *unknown, const float *known, int mem,
+                         float *dist2, int32_t *idx);
+
 /* Pose helpers (host side, no GPU): rotmat2quaternion / homo2tq of main.py:158-174.
  * homo: 16 row-major doubles; tq: tx,ty,tz,qw,qx,qy,qz. */
 PCP_API int pcp_homo2tq(const double *homo, double *tq);

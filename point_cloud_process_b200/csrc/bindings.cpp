@@ -431,6 +431,29 @@ py::tuple multi_pair_range(const i64_array &src_off, const i64_array &tgt_off, i
     return py::make_tuple(lo, hi);
 }
 
+// PointNet++ layouts: (b, m, 3) / (b, n, 3) float32 arrays
+py::array_t<int32_t> ball_query(std::shared_ptr<Context> ctx, double radius, int nsample, const f32_array &xyz,
+                                const f32_array &new_xyz) {
+    if (xyz.ndim() != 3 || new_xyz.ndim() != 3 || xyz.shape(2) != 3 || new_xyz.shape(2) != 3 || xyz.shape(0) != new_xyz.shape(0))
+        throw py::value_error("ball_query: expected xyz (B, N, 3) and new_xyz (B, npoint, 3)");
+    if (nsample < 0) throw py::value_error("ball_query: nsample must be >= 0");
+    const int b = (int)xyz.shape(0), n = (int)xyz.shape(1), m = (int)new_xyz.shape(1);
+    py::array_t<int32_t> idx({(py::ssize_t)b, (py::ssize_t)m, (py::ssize_t)nsample});
+    check(pcp_ball_query(ctx->get(), b, n, m, (float)radius, nsample, new_xyz.data(), xyz.data(), PCP_HOST, idx.mutable_data()),
+          "pcp_ball_query");
+    return idx;
+}
+py::tuple three_nn(std::shared_ptr<Context> ctx, const f32_array &unknown, const f32_array &known) {
+    if (unknown.ndim() != 3 || known.ndim() != 3 || unknown.shape(2) != 3 || known.shape(2) != 3 || unknown.shape(0) != known.shape(0))
+        throw py::value_error("three_nn: expected unknown (B, n, 3) and known (B, m, 3)");
+    const int b = (int)unknown.shape(0), n = (int)unknown.shape(1), m = (int)known.shape(1);
+    py::array_t<float> d2({(py::ssize_t)b, (py::ssize_t)n, (py::ssize_t)3});
+    py::array_t<int32_t> idx({(py::ssize_t)b, (py::ssize_t)n, (py::ssize_t)3});
+    check(pcp_three_nn(ctx->get(), b, n, m, unknown.data(), known.data(), PCP_HOST, d2.mutable_data(), idx.mutable_data()),
+          "pcp_three_nn");
+    return py::make_tuple(d2, idx);
+}
+
 // icp_batch: packed clouds + offsets -> dict(T_last, T_total, iterations, status[, diff_log])
 py::dict icp_batch(std::shared_ptr<Context> ctx, const py::object &src, const i64_array &src_off, const py::object &tgt,
                    const i64_array &tgt_off, const f64_array &T_init, int max_iteration, double R_diff_thres,
@@ -631,6 +654,8 @@ PYBIND11_MODULE(_pcp, m) {
     m.def("multi_pair_range", &multi_pair_range, py::arg("source_offsets"), py::arg("target_offsets"), py::arg("rank"),
           py::arg("world"));
 
+    m.def("ball_query", &ball_query, py::arg("ctx"), py::arg("radius"), py::arg("nsample"), py::arg("xyz"), py::arg("new_xyz"));
+    m.def("three_nn", &three_nn, py::arg("ctx"), py::arg("unknown"), py::arg("known"));
     m.def("icp_batch", &icp_batch, py::arg("ctx"), py::arg("source"), py::arg("source_offsets"), py::arg("target"),
           py::arg("target_offsets"), py::arg("T_init"), py::arg("max_iteration") = 100, py::arg("R_diff_thres") = 0.5,
           py::arg("t_diff_thres") = 0.5, py::arg("dist_thres") = 5.0, py::arg("first_iter_broadcast") = true,

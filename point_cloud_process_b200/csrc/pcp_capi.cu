@@ -877,6 +877,65 @@ int pcp_iss_keypoints(pcp_index *ix, double radius, double lambda21, double lamb
     return PCP_OK;
 }
 
+int pcp_ball_query(pcp_ctx *ctx, int b, int n, int m, float radius, int nsample, const float *new_xyz, const float *xyz,
+                   int mem, int32_t *idx) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ball_query: ctx is NULL");
+    if (b < 0 || n < 0 || m < 0 || nsample < 0) return fail(PCP_ERR_INVALID, "pcp_ball_query: negative size");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_ball_query: mem must be PCP_HOST or PCP_DEVICE");
+    const size_t nc = (size_t)b * (size_t)m * 3, np = (size_t)b * (size_t)n * 3, ni = (size_t)b * (size_t)m * (size_t)nsample;
+    if ((nc && !new_xyz) || (np && !xyz) || (ni && !idx)) return fail(PCP_ERR_INVALID, "pcp_ball_query: NULL array");
+    if (ni == 0) return PCP_OK;
+    DeviceGuard g(ctx->device);
+    const float *d_c = new_xyz, *d_p = xyz;
+    int32_t *d_i = idx;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], new_xyz, sizeof(float) * nc));
+        if (np) PCP_TRY(upload(ctx, 2, ctx->scratch[5], xyz, sizeof(float) * np));
+        else PCP_TRY(ctx->scratch[5].ensure(16));
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(int32_t) * ni));
+        d_c = ctx->scratch[6].as<float>();
+        d_p = ctx->scratch[5].as<float>();
+        d_i = ctx->scratch[7].as<int32_t>();
+    }
+    PCP_TRY(ball_query_device(ctx, b, n, m, radius, nsample, d_c, d_p, d_i));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, idx, d_i, sizeof(int32_t) * ni));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_three_nn(pcp_ctx *ctx, int b, int n, int m, const float *unknown, const float *known, int mem, float *dist2,
+                 int32_t *idx) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_three_nn: ctx is NULL");
+    if (b < 0 || n < 0 || m < 0) return fail(PCP_ERR_INVALID, "pcp_three_nn: negative size");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_three_nn: mem must be PCP_HOST or PCP_DEVICE");
+    const size_t nu = (size_t)b * (size_t)n * 3, nk = (size_t)b * (size_t)m * 3;
+    if ((nu && (!unknown || !dist2 || !idx)) || (nk && !known)) return fail(PCP_ERR_INVALID, "pcp_three_nn: NULL array");
+    if (nu == 0) return PCP_OK;
+    DeviceGuard g(ctx->device);
+    const float *d_u = unknown, *d_k = known;
+    float *d_d = dist2;
+    int32_t *d_i = idx;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], unknown, sizeof(float) * nu));
+        if (nk) PCP_TRY(upload(ctx, 2, ctx->scratch[5], known, sizeof(float) * nk));
+        else PCP_TRY(ctx->scratch[5].ensure(16));
+        PCP_TRY(ctx->scratch[7].ensure(nu * 8));
+        d_u = ctx->scratch[6].as<float>();
+        d_k = ctx->scratch[5].as<float>();
+        d_d = ctx->scratch[7].as<float>();
+        d_i = reinterpret_cast<int32_t *>(d_d + nu);
+    }
+    PCP_TRY(three_nn_device(ctx, b, n, m, d_u, d_k, d_d, d_i));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, dist2, d_d, sizeof(float) * nu));
+        PCP_TRY(download(ctx, idx, d_i, sizeof(int32_t) * nu));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
 int pcp_neighbor_counts_f64(pcp_index *ix, double radius, int64_t *counts) {
     if (!ix) return fail(PCP_ERR_INVALID, "pcp_neighbor_counts_f64: index is NULL");
     if (!(radius >= 0.0)) return fail(PCP_ERR_INVALID, "pcp_neighbor_counts_f64: radius must be >= 0");

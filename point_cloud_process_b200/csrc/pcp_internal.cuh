@@ -211,6 +211,12 @@ int knn_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride
                      int32_t *d_count);
 int radius_count_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float d2max, long long *d_counts);
 
+// PointNet++ neighbourhood layouts (pcp_pointnet.cu)
+int ball_query_device(pcp_ctx *ctx, int b, int n, int m, float radius, int nsample, const float *d_new_xyz,
+                      const float *d_xyz, int32_t *d_idx);
+int three_nn_device(pcp_ctx *ctx, int b, int n, int m, const float *d_unknown, const float *d_known, float *d_dist2,
+                    int32_t *d_idx);
+
 // icp (pcp_icp.cu)
 int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t n_pairs, const float *d_src,
                      const int64_t *h_src_off, const float *d_tgt, const int64_t *h_tgt_off, int64_t stride,
