@@ -9,7 +9,7 @@
 // The squared distance is the reference's float32 expression AS nvcc COMPILES IT (default -fmad=true):
 //   (a-x)*(a-x) + (b-y)*(b-y) + (c-z)*(c-z)  ->  fma(dz, dz, fma(dx, dx, dy * dy))
 // written with explicit intrinsics here so that the hit sets and orders are identical to the reference build
-// (oracle/_ref, compiled from the reference's own sources, is the judge of that).
+// (the test-suite compares with the reference sources compiled as they are).
 //
 // The reference gives one CTA a whole batch element and lets every thread stream all n points from global memory.
 // Here a CTA of 128 threads owns 128 centres of one batch element; the points pass through shared memory in tiles
