@@ -336,6 +336,39 @@ PCP_API int pcp_multi_icp_batch(pcp_multi *m, const pcp_icp_params *params, int6
                                 int32_t *iterations, int32_t *status, double *diff_log, int64_t *first_pair,
                                 int64_t *last_pair);
 
+/* ---- global initialisation in front of ICP: normals, FPFH, feature matching, RANSAC ---------------
+ * The Open3D calls of Registration/main.py:33-47,68-84 and the contract of icp_template.py:20-41,56-111.  Open3D is
+ * absent and unpinned in the reference: these restate its published algorithms; parity "unpinned".
+ * pcp_normals_hybrid   estimate_normals(KDTreeSearchParamHybrid(radius, max_nn))             main.py:37-39
+ *     neighbourhood = the up-to-max_nn nearest indexed points within radius (self included); normal = eigenvector of
+ *     the smallest eigenvalue of its covariance, (0,0,1) below 3 neighbours; sign: largest component positive.
+ * pcp_fpfh             compute_fpfh_feature(pcd, KDTreeSearchParamHybrid(radius, max_nn))    main.py:43-46
+ *     normals: n x 3 float64 of the indexed cloud; features: n x 33 float64 (row per point; Open3D stores 33 x n).
+ * pcp_feature_match    nearest target feature of every source feature (exhaustive, float64, lowest index wins):
+ *     the search inside registration_ransac_based_on_feature_matching / find_matchings      icp_template.py:20-41
+ * pcp_ransac_init      registration_ransac_based_on_feature_matching(..., ransac_n = 3, [EdgeLength, Distance],
+ *     RANSACConvergenceCriteria(max_iteration, confidence))                                  main.py:74-83
+ *     correspondences: m x 2 int32 (source row, target row); target_index: the index over the target cloud (its
+ *     cloud must still be alive); T: 16 doubles row-major source -> target; fitness = inliers / n_src with
+ *     inlier = nearest target point within max_correspondence_distance; inlier_rmse over the inliers.
+ *     Hypotheses are drawn from a counter hash of (seed, iteration): the result is reproducible. */
+typedef struct pcp_ransac_params {
+    double max_correspondence_distance;   /* main.py:71   voxel_size * 1.5 */
+    double edge_length_threshold;         /* main.py:78   0.9 */
+    double confidence;                    /* main.py:83   0.999 */
+    int32_t max_iteration;                /* main.py:83   100000 */
+    int32_t ransac_n;                     /* main.py:77   3 (the only supported value) */
+    uint64_t seed;
+} pcp_ransac_params;
+PCP_API int pcp_normals_hybrid(pcp_index *index, double radius, int max_nn, int mem, double *normals);
+PCP_API int pcp_fpfh(pcp_index *index, const double *normals, double radius, int max_nn, int mem, double *features);
+PCP_API int pcp_feature_match(pcp_ctx *ctx, const double *src_features, int64_t n_src, const double *tgt_features,
+                              int64_t n_tgt, int dim, int mem, int32_t *nearest, double *dist2);
+PCP_API int pcp_ransac_init(pcp_ctx *ctx, const pcp_ransac_params *params, const float *src_xyz, int64_t n_src,
+                            int64_t stride_floats, pcp_index *target_index, const int32_t *correspondences,
+                            int64_t n_corr, int mem, double *T, double *fitness, double *inlier_rmse,
+                            int64_t *iterations, int64_t *hypotheses_evaluated);
+
 /* ---- PointNet++ neighbourhood layouts ----------------------------------------------------------
  * The two search ops of the reference's own CUDA extension, same layouts and selection rules, packed float32 rows:
  * pcp_ball_query replaces query_ball_point_kernel        _ext-src/src/ball_query_gpu.cu:9-46 (ball_query.cpp:9-34)

@@ -137,6 +137,20 @@ class Index {
         check(pcp_index_rebuild(ix_, reinterpret_cast<const float *>(dptr), n, stride, PCP_DEVICE), "pcp_index_rebuild");
     }
     int64_t size() const { return pcp_index_size(ix_); }
+    // global initialisation: normals / FPFH over hybrid neighbourhoods (main.py:33-47)
+    py::array_t<double> normals_hybrid(double radius, int max_nn) {
+        py::array_t<double> nrm({(py::ssize_t)size(), (py::ssize_t)3});
+        check(pcp_normals_hybrid(ix_, radius, max_nn, PCP_HOST, nrm.mutable_data()), "pcp_normals_hybrid");
+        return nrm;
+    }
+    py::array_t<double> fpfh(const f64_array &normals, double radius, int max_nn) {
+        if (normals.ndim() != 2 || normals.shape(0) != size() || normals.shape(1) != 3)
+            throw py::value_error("fpfh: normals must be (N, 3) float64 rows of the indexed cloud");
+        py::array_t<double> f({(py::ssize_t)size(), (py::ssize_t)33});
+        check(pcp_fpfh(ix_, normals.data(), radius, max_nn, PCP_HOST, f.mutable_data()), "pcp_fpfh");
+        return f;
+    }
+    pcp_index *raw() const { return ix_; }
     py::array_t<int64_t> neighbor_counts_f64(double radius) {
         py::array_t<int64_t> c((py::ssize_t)size());
         check(pcp_neighbor_counts_f64(ix_, radius, c.mutable_data()), "pcp_neighbor_counts_f64");
@@ -431,6 +445,39 @@ py::tuple multi_pair_range(const i64_array &src_off, const i64_array &tgt_off, i
     return py::make_tuple(lo, hi);
 }
 
+// nearest target feature of every source feature: rows = points, columns = feature dimensions
+py::tuple feature_match(std::shared_ptr<Context> ctx, const f64_array &src, const f64_array &tgt) {
+    if (src.ndim() != 2 || tgt.ndim() != 2 || src.shape(1) != tgt.shape(1))
+        throw py::value_error("feature_match: expected (Ns, D) and (Nt, D) float64 arrays");
+    py::array_t<int32_t> idx((py::ssize_t)src.shape(0));
+    py::array_t<double> d2((py::ssize_t)src.shape(0));
+    check(pcp_feature_match(ctx->get(), src.data(), src.shape(0), tgt.data(), tgt.shape(0), (int)src.shape(1), PCP_HOST,
+                            idx.mutable_data(), d2.mutable_data()), "pcp_feature_match");
+    return py::make_tuple(idx, d2);
+}
+// feature-matching RANSAC (main.py:68-84) -> dict(transformation 4x4, fitness, inlier_rmse, iterations, evaluated)
+py::dict ransac_init(std::shared_ptr<Context> ctx, const py::object &src_points, const Index &target,
+                     const py::array_t<int32_t, py::array::c_style | py::array::forcecast> &corr, double max_corr_dist,
+                     double edge_ratio, int max_iteration, double confidence, uint64_t seed) {
+    Cloud s(src_points, "source");
+    if (corr.ndim() != 2 || corr.shape(1) != 2) throw py::value_error("ransac_init: correspondences must be (M, 2) int32");
+    pcp_ransac_params prm;
+    prm.max_correspondence_distance = max_corr_dist;
+    prm.edge_length_threshold = edge_ratio;
+    prm.confidence = confidence;
+    prm.max_iteration = max_iteration;
+    prm.ransac_n = 3;
+    prm.seed = seed;
+    py::array_t<double> T({(py::ssize_t)4, (py::ssize_t)4});
+    double fit = 0, rmse = 0;
+    int64_t it = 0, ev = 0;
+    check(pcp_ransac_init(ctx->get(), &prm, s.data(), s.n, s.stride, target.raw(), corr.data(), corr.shape(0), PCP_HOST,
+                          T.mutable_data(), &fit, &rmse, &it, &ev), "pcp_ransac_init");
+    py::dict d;
+    d["transformation"] = T; d["fitness"] = fit; d["inlier_rmse"] = rmse; d["iterations"] = it; d["evaluated"] = ev;
+    return d;
+}
+
 // PointNet++ layouts: (b, m, 3) / (b, n, 3) float32 arrays
 py::array_t<int32_t> ball_query(std::shared_ptr<Context> ctx, double radius, int nsample, const f32_array &xyz,
                                 const f32_array &new_xyz) {
@@ -616,6 +663,8 @@ PYBIND11_MODULE(_pcp, m) {
         .def("rebuild_device", &Index::rebuild_device, py::arg("device_ptr"), py::arg("n"), py::arg("stride_floats") = 3)
         .def("size", &Index::size)
         .def("attach_f64", &Index::attach_f64, py::arg("xyz"))
+        .def("normals_hybrid", &Index::normals_hybrid, py::arg("radius"), py::arg("max_nn"))
+        .def("fpfh", &Index::fpfh, py::arg("normals"), py::arg("radius"), py::arg("max_nn"))
         .def("neighbor_counts_f64", &Index::neighbor_counts_f64, py::arg("radius"))
         .def("stats", &Index::stats)
         .def("knn", &Index::knn, py::arg("queries"), py::arg("k"))
@@ -654,6 +703,10 @@ PYBIND11_MODULE(_pcp, m) {
     m.def("multi_pair_range", &multi_pair_range, py::arg("source_offsets"), py::arg("target_offsets"), py::arg("rank"),
           py::arg("world"));
 
+    m.def("feature_match", &feature_match, py::arg("ctx"), py::arg("src_features"), py::arg("tgt_features"));
+    m.def("ransac_init", &ransac_init, py::arg("ctx"), py::arg("source"), py::arg("target_index"), py::arg("correspondences"),
+          py::arg("max_correspondence_distance"), py::arg("edge_length_threshold") = 0.9, py::arg("max_iteration") = 100000,
+          py::arg("confidence") = 0.999, py::arg("seed") = 0);
     m.def("ball_query", &ball_query, py::arg("ctx"), py::arg("radius"), py::arg("nsample"), py::arg("xyz"), py::arg("new_xyz"));
     m.def("three_nn", &three_nn, py::arg("ctx"), py::arg("unknown"), py::arg("known"));
     m.def("icp_batch", &icp_batch, py::arg("ctx"), py::arg("source"), py::arg("source_offsets"), py::arg("target"),

@@ -877,6 +877,111 @@ int pcp_iss_keypoints(pcp_index *ix, double radius, double lambda21, double lamb
     return PCP_OK;
 }
 
+int pcp_normals_hybrid(pcp_index *ix, double radius, int max_nn, int mem, double *normals) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_normals_hybrid: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_normals_hybrid: mem must be PCP_HOST or PCP_DEVICE");
+    if (!(radius > 0.0) || max_nn < 1) return fail(PCP_ERR_INVALID, "pcp_normals_hybrid: radius > 0 and max_nn >= 1 required");
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    if (!normals) return fail(PCP_ERR_INVALID, "pcp_normals_hybrid: normals is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    double *d_n = normals;
+    if (mem == PCP_HOST) {
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(double) * 3 * (size_t)n));
+        d_n = ctx->scratch[7].as<double>();
+    }
+    PCP_TRY(normals_hybrid_device(ix, radius, max_nn, d_n));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, normals, d_n, sizeof(double) * 3 * (size_t)n));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_fpfh(pcp_index *ix, const double *normals, double radius, int max_nn, int mem, double *features) {
+    if (!ix) return fail(PCP_ERR_INVALID, "pcp_fpfh: index is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_fpfh: mem must be PCP_HOST or PCP_DEVICE");
+    if (!(radius > 0.0) || max_nn < 1) return fail(PCP_ERR_INVALID, "pcp_fpfh: radius > 0 and max_nn >= 1 required");
+    const int64_t n = ix->n;
+    if (n == 0) return PCP_OK;
+    if (!normals || !features) return fail(PCP_ERR_INVALID, "pcp_fpfh: normals/features is NULL");
+    pcp_ctx *ctx = ix->ctx;
+    DeviceGuard g(ctx->device);
+    const double *d_n = normals;
+    double *d_f = features;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], normals, sizeof(double) * 3 * (size_t)n));
+        PCP_TRY(ctx->scratch[7].ensure(sizeof(double) * 33 * (size_t)n));
+        d_n = ctx->scratch[6].as<double>();
+        d_f = ctx->scratch[7].as<double>();
+    }
+    PCP_TRY(fpfh_device(ix, d_n, radius, max_nn, d_f));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, features, d_f, sizeof(double) * 33 * (size_t)n));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_feature_match(pcp_ctx *ctx, const double *src, int64_t ns, const double *tgt, int64_t nt, int dim, int mem,
+                      int32_t *nearest, double *dist2) {
+    if (!ctx) return fail(PCP_ERR_INVALID, "pcp_feature_match: ctx is NULL");
+    if (bad_mem(mem)) return fail(PCP_ERR_INVALID, "pcp_feature_match: mem must be PCP_HOST or PCP_DEVICE");
+    if (ns < 0 || nt < 0 || dim < 1) return fail(PCP_ERR_INVALID, "pcp_feature_match: bad sizes");
+    if (ns == 0) return PCP_OK;
+    if (!src || !nearest || (nt > 0 && !tgt)) return fail(PCP_ERR_INVALID, "pcp_feature_match: NULL array");
+    DeviceGuard g(ctx->device);
+    const double *d_s = src, *d_t = tgt;
+    int32_t *d_i = nearest;
+    double *d_d = dist2;
+    if (mem == PCP_HOST) {
+        PCP_TRY(upload(ctx, 1, ctx->scratch[6], src, sizeof(double) * (size_t)ns * (size_t)dim));
+        if (nt) PCP_TRY(upload(ctx, 2, ctx->scratch[5], tgt, sizeof(double) * (size_t)nt * (size_t)dim));
+        else PCP_TRY(ctx->scratch[5].ensure(16));
+        PCP_TRY(ctx->scratch[7].ensure((size_t)ns * 16));
+        d_s = ctx->scratch[6].as<double>();
+        d_t = ctx->scratch[5].as<double>();
+        d_d = ctx->scratch[7].as<double>();
+        d_i = reinterpret_cast<int32_t *>(d_d + ns);
+    }
+    PCP_TRY(feature_match_device(ctx, d_s, ns, d_t, nt, dim, d_i, d_d));
+    if (mem == PCP_HOST) {
+        PCP_TRY(download(ctx, nearest, d_i, sizeof(int32_t) * (size_t)ns));
+        if (dist2) PCP_TRY(download(ctx, dist2, d_d, sizeof(double) * (size_t)ns));
+        PCP_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCP_OK;
+}
+
+int pcp_ransac_init(pcp_ctx *ctx, const pcp_ransac_params *prm, const float *src, int64_t ns, int64_t stride,
+                    pcp_index *tgt, const int32_t *corr, int64_t n_corr, int mem, double *T, double *fitness,
+                    double *rmse, int64_t *iterations, int64_t *evaluated) {
+    if (!ctx || !prm || !tgt || !T) return fail(PCP_ERR_INVALID, "pcp_ransac_init: NULL argument");
+    if (tgt->ctx != ctx) return fail(PCP_ERR_INVALID, "pcp_ransac_init: the target index belongs to another context");
+    PCP_TRY(check_cloud("pcp_ransac_init", src, ns, stride, mem));
+    if (n_corr < 0 || (n_corr > 0 && !corr)) return fail(PCP_ERR_INVALID, "pcp_ransac_init: bad correspondences");
+    if (prm->ransac_n != 3) return fail(PCP_ERR_UNSUPPORTED, "pcp_ransac_init: ransac_n must be 3");
+    if (!(prm->max_correspondence_distance > 0.0)) return fail(PCP_ERR_INVALID, "pcp_ransac_init: max_correspondence_distance must be > 0");
+    DeviceGuard g(ctx->device);
+    const float *d_s = src;
+    const int32_t *d_c = corr;
+    if (mem == PCP_HOST) {
+        if (ns) PCP_TRY(upload(ctx, 1, ctx->scratch[6], src, sizeof(float) * (size_t)ns * (size_t)stride));
+        if (n_corr) PCP_TRY(upload(ctx, 2, ctx->scratch[7], corr, sizeof(int32_t) * 2 * (size_t)n_corr));
+        d_s = ctx->scratch[6].as<float>();
+        d_c = ctx->scratch[7].as<int32_t>();
+    }
+    double fit = 0, rm = 0;
+    int64_t it = 0, ev = 0;
+    PCP_TRY(ransac_device(ctx, *prm, d_s, ns, stride, tgt, d_c, n_corr, T, &fit, &rm, &it, &ev));
+    if (fitness) *fitness = fit;
+    if (rmse) *rmse = rm;
+    if (iterations) *iterations = it;
+    if (evaluated) *evaluated = ev;
+    return PCP_OK;
+}
+
 int pcp_ball_query(pcp_ctx *ctx, int b, int n, int m, float radius, int nsample, const float *new_xyz, const float *xyz,
                    int mem, int32_t *idx) {
     if (!ctx) return fail(PCP_ERR_INVALID, "pcp_ball_query: ctx is NULL");

@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "pcp_internal.cuh"
+#include "pcp_linalg.cuh"
 
 namespace pcp {
 namespace {
@@ -358,51 +359,6 @@ int voxel_filter_device(pcp_ctx *ctx, const float *d_xyz, int64_t n, int64_t str
 // ================================================================================================ normals
 
 namespace {
-
-// cyclic Jacobi on a symmetric 3x3 (float64): eigenvalues w[3], eigenvectors as the COLUMNS of V (row-major 3x3)
-__device__ void sym_eig3(double a00, double a01, double a02, double a11, double a12, double a22, double w[3],
-                         double V[9]) {
-    double A[3][3] = {{a00, a01, a02}, {a01, a11, a12}, {a02, a12, a22}};
-    double E[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
-    for (int sweep = 0; sweep < 24; ++sweep) {
-        const double off = fabs(A[0][1]) + fabs(A[0][2]) + fabs(A[1][2]);
-        const double diag = fabs(A[0][0]) + fabs(A[1][1]) + fabs(A[2][2]);
-        if (off <= 1e-300 || off <= 1e-18 * diag) break;
-#pragma unroll
-        for (int pq = 0; pq < 3; ++pq) {
-            const int p = pq == 2 ? 1 : 0, q = pq == 0 ? 1 : 2;
-            const double apq = A[p][q];
-            if (apq == 0.0) continue;
-            const double theta = (A[q][q] - A[p][p]) / (2.0 * apq);
-            const double t = copysign(1.0, theta) / (fabs(theta) + sqrt(theta * theta + 1.0));
-            const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {   // A <- A J
-                const double arp = A[r][p], arq = A[r][q];
-                A[r][p] = c * arp - s * arq;
-                A[r][q] = s * arp + c * arq;
-            }
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {   // A <- J^T A
-                const double apr = A[p][r], aqr = A[q][r];
-                A[p][r] = c * apr - s * aqr;
-                A[q][r] = s * apr + c * aqr;
-            }
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {
-                const double erp = E[r][p], erq = E[r][q];
-                E[r][p] = c * erp - s * erq;
-                E[r][q] = s * erp + c * erq;
-            }
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        w[i] = A[i][i];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) V[i * 3 + j] = E[i][j];
-    }
-}
 
 // One thread per point: PCA(pc_array[idx, :]) of pca_normal.py:10-36 on the point's k nearest neighbours
 // (self included, pca_normal.py:88) -- mean (np.mean: left-to-right below 8 values, pairwise above: k <= 32 uses

@@ -29,6 +29,7 @@
 
 #include "pcp_device.cuh"
 #include "pcp_internal.cuh"
+#include "pcp_linalg.cuh"
 
 namespace pcp {
 
@@ -441,69 +442,6 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
         for (int w = 0; w < kTileAssocWarps; ++w) s += s_sum[w][threadIdx.x];
         partials[((long long)pair * chunks_per_pair + chunk) * kSums + threadIdx.x] = s;
     }
-}
-
-// One-sided (Hestenes) Jacobi SVD of a 3x3 float64 matrix: A V = U S.  Returns R = U V^T, the
-// orthogonal polar factor u @ vt of main.py:138-139 (independent of the SVD's sign conventions
-// whenever the smallest singular value is > 0).
-__device__ void polar_uvt(const double H[9], double R[9]) {
-    double A[9], V[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-#pragma unroll
-    for (int i = 0; i < 9; ++i) A[i] = H[i];
-    for (int sweep = 0; sweep < 30; ++sweep) {
-        double off = 0.0;
-#pragma unroll
-        for (int pq = 0; pq < 3; ++pq) {
-            const int p = pq == 2 ? 1 : 0, q = pq == 0 ? 1 : 2;
-            double alpha = 0, beta = 0, gamma = 0;
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {
-                alpha += A[r * 3 + p] * A[r * 3 + p];
-                beta += A[r * 3 + q] * A[r * 3 + q];
-                gamma += A[r * 3 + p] * A[r * 3 + q];
-            }
-            const double lim = 1e-15 * sqrt(alpha * beta);
-            if (fabs(gamma) <= lim || gamma == 0.0) continue;
-            off = fmax(off, fabs(gamma) / fmax(sqrt(alpha * beta), 1e-300));
-            const double zeta = (beta - alpha) / (2.0 * gamma);
-            const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-            const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
-#pragma unroll
-            for (int r = 0; r < 3; ++r) {
-                const double ap = A[r * 3 + p], aq = A[r * 3 + q];
-                A[r * 3 + p] = c * ap - s * aq;
-                A[r * 3 + q] = s * ap + c * aq;
-                const double vp = V[r * 3 + p], vq = V[r * 3 + q];
-                V[r * 3 + p] = c * vp - s * vq;
-                V[r * 3 + q] = s * vp + c * vq;
-            }
-        }
-        if (off < 1e-15) break;
-    }
-    // U columns = normalised A columns; a vanishing column (rank-deficient H: collinear / planar
-    // correspondences) is completed by the cross product of the other two, as any SVD would pick
-    // some unit vector orthogonal to them.
-    double U[9], nrm[3];
-#pragma unroll
-    for (int j = 0; j < 3; ++j) nrm[j] = sqrt(A[j] * A[j] + A[3 + j] * A[3 + j] + A[6 + j] * A[6 + j]);
-    const double big = fmax(nrm[0], fmax(nrm[1], nrm[2]));
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-        const double inv = nrm[j] > 1e-14 * big && nrm[j] > 0.0 ? 1.0 / nrm[j] : 0.0;
-        U[j] = A[j] * inv; U[3 + j] = A[3 + j] * inv; U[6 + j] = A[6 + j] * inv;
-    }
-    for (int j = 0; j < 3; ++j) {
-        if (nrm[j] > 1e-14 * big && nrm[j] > 0.0) continue;
-        const int a = (j + 1) % 3, b = (j + 2) % 3;
-        U[j] = U[3 + a] * U[6 + b] - U[6 + a] * U[3 + b];
-        U[3 + j] = U[6 + a] * U[b] - U[a] * U[6 + b];
-        U[6 + j] = U[a] * U[3 + b] - U[3 + a] * U[b];
-    }
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-            R[i * 3 + j] = U[i * 3 + 0] * V[j * 3 + 0] + U[i * 3 + 1] * V[j * 3 + 1] + U[i * 3 + 2] * V[j * 3 + 2];
 }
 
 // out = inc o prev for 3x4 row-major rigid transforms

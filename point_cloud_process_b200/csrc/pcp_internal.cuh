@@ -140,6 +140,7 @@ struct pcp_ctx {
     // ICP front end (pcp_front.cu): result of the last pcp_voxel_filter (read by pcp_voxel_filter_read), its run
     // count / bounding-box accumulators, and the neighbour lists of pcp_normals
     pcp::DevBuf voxel_out, voxel_meta, normals_nn;
+    pcp::DevBuf ransac_buf[4];     // pcp_ransac_init: hypotheses, counter, transformed queries, per-query results
     pcp::DevBuf iss_buf[4];        // pcp_iss_keypoints: CSR of the radius search (offsets, indices, distances) and its work arrays
     int64_t voxel_n_out = -1;
     bool count_work = false;
@@ -210,6 +211,15 @@ float exact_d2_threshold(float r);
 int knn_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, int k, int32_t *d_idx, float *d_dist,
                      int32_t *d_count);
 int radius_count_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, float d2max, long long *d_counts);
+
+// global initialisation (pcp_global.cu, pcp_global_ransac.cu)
+int normals_hybrid_device(pcp_index *ix, double radius, int max_nn, double *d_normals);
+int fpfh_device(pcp_index *ix, const double *d_normals, double radius, int max_nn, double *d_fpfh);
+int feature_match_device(pcp_ctx *ctx, const double *d_src, int64_t ns, const double *d_tgt, int64_t nt, int dim,
+                         int32_t *d_idx, double *d_d2);
+int ransac_device(pcp_ctx *ctx, const pcp_ransac_params &prm, const float *d_src, int64_t ns, int64_t stride,
+                  pcp_index *tgt, const int32_t *d_corr, int64_t n_corr, double *h_T, double *h_fitness, double *h_rmse,
+                  int64_t *h_iterations, int64_t *h_evaluated);
 
 // PointNet++ neighbourhood layouts (pcp_pointnet.cu)
 int ball_query_device(pcp_ctx *ctx, int b, int n, int m, float radius, int nsample, const float *d_new_xyz,
