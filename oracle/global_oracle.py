@@ -56,7 +56,7 @@ def pair_features(p1, n1, p2, n2):
     if ln == 0:
         return f
     a1, a2 = n1 @ d / ln, n2 @ d / ln
-    if np.arccos(min(1.0, abs(a1))) > np.arccos(min(1.0, abs(a2))):
+    if np.arccos(min(1.0, abs(a1))) > np.arccos(min(1.0, abs(a2))) + 1e-9:      # (a clear win only: see pcp_global.cu)
         u, t, d, f[2] = n2, n1, -d, -a2
     else:
         u, t, f[2] = n1, n2, a1

@@ -89,7 +89,9 @@ __device__ __forceinline__ void pair_features(const double p1[3], const double n
     const double a1 = (n1[0] * d[0] + n1[1] * d[1] + n1[2] * d[2]) / len;
     const double a2 = (n2[0] * d[0] + n2[1] * d[1] + n2[2] * d[2]) / len;
     double u[3], t[3];                        // u = frame normal (n1 or n2), t = the other one
-    if (acos(fabs(a1)) > acos(fabs(a2))) {
+    // (Open3D compares the two angles exactly; on a symmetric pair -- |a1| == |a2| up to rounding, e.g. two points of a
+    // sphere -- the outcome then hangs on the last bit.  Here the frame moves to the second point only for a clear win.)
+    if (acos(fmin(fabs(a1), 1.0)) > acos(fmin(fabs(a2), 1.0)) + 1e-9) {
         u[0] = n2[0]; u[1] = n2[1]; u[2] = n2[2];
         t[0] = n1[0]; t[1] = n1[1]; t[2] = n1[2];
         d[0] = -d[0]; d[1] = -d[1]; d[2] = -d[2];

@@ -39,11 +39,21 @@ def write_synthetic_dataset(pair_ids, cloud_dir, make_pair, n_points=20000):
             rows.tofile(os.path.join(cloud_dir, "%03d_%s_%d.bin" % (j, role, idx)))
 
 
-def run(pair_list_path, cloud_dir, out_path, inits=None, **icp_kw):
-    """-> (rows (P, 9), raw icp_batch output).  Writes out_path in the reference's reg_result.txt format."""
+def run(pair_list_path, cloud_dir, out_path, inits=None, init="identity", voxel_size=2.0, seed=0, **icp_kw):
+    """-> (rows (P, 9), raw icp_batch output).  Writes out_path in the reference's reg_result.txt format.
+    init = "ransac": the global initialisation of main.py:196-209 (voxel down-sample, normals, FPFH, feature-matching
+    RANSAC; global_registration.py) is computed per pair on the GPU -- raw clouds in, reg_result.txt out, no
+    caller-supplied transformation; "identity" (or explicit `inits`): ICP alone."""
     pair_ids = icp.read_pair_list(pair_list_path)
     sources = [icp.read_bin_velodyne(cloud_path(cloud_dir, s, j, "src")) for j, (t, s) in enumerate(pair_ids)]
     targets = [icp.read_bin_velodyne(cloud_path(cloud_dir, t, j, "trg")) for j, (t, s) in enumerate(pair_ids)]
-    if inits is None:
+    if inits is None and init == "ransac":
+        from . import global_registration as gr
+        inits = np.zeros((len(pair_ids), 4, 4))
+        for j, (src, tgt) in enumerate(zip(sources, targets)):
+            sd, sf = gr.preprocess_point_cloud(src, voxel_size)                       # main.py:63-64
+            td, tf = gr.preprocess_point_cloud(tgt, voxel_size)
+            inits[j] = gr.execute_global_registration(sd, td, sf, tf, voxel_size, seed=seed + j).transformation   # main.py:205-209
+    elif inits is None:
         inits = np.tile(np.eye(4), (len(pair_ids), 1, 1))
     return icp.register_pairs(sources, targets, inits, pair_ids, out_path=out_path, **icp_kw)

@@ -43,8 +43,8 @@ def test_normals_and_fpfh_vs_oracle(pcp):
     assert np.allclose(f_gpu.sum(1), f_ref.sum(1), atol=1e-6)
     # a pair feature that sits on a bin edge may fall either way under different summation orders: rows must agree
     # except for isolated single-bin moves
-    bad = (np.abs(f_gpu - f_ref) > 1e-6).any(1)
-    assert bad.mean() < 0.02
+    l1 = np.abs(f_gpu - f_ref).sum(1)
+    assert (l1 > 1e-6).mean() < 0.02 and (l1 > 60.0).mean() < 0.002, ((l1 > 1e-6).mean(), np.percentile(l1, [50, 90, 99, 100]))
 
 
 def test_feature_match_vs_bruteforce(pcp):
@@ -98,3 +98,28 @@ def test_global_init_then_icp_end_to_end(pcp):
     T_last, info = icp.icp_point2point(src, tgt, init, max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6, return_info=True)
     ok, rte, rre = evaluate_rt.is_registration_successful(info["total"], T_gt)
     assert ok and rte < 0.05 and rre < 0.1, (rte, rre)
+
+
+def test_c2_from_raw_clouds_without_a_supplied_transformation(pcp, tmp_path):
+    """main.py:183-222 end to end: pair list -> Oxford-layout files -> global initialisation (FPFH + RANSAC) -> ICP ->
+    reg_result.txt, nothing supplied by the caller.  The written rows are icp_point2point's return value (the LAST
+    increment, main.py:156,211-218 -- as built); the composed poses recover the planted transformations."""
+    from oracle import global_oracle as go
+    from point_cloud_process_b200 import evaluate_rt, icp, registration
+    pair_ids = [(643, 456), (0, 456), (645, 189)]
+    gts = []
+
+    def make(seed, n):
+        tgt, src, T = go.planted_pair(seed, n=n, max_rot_deg=15.0, max_t=4.0)
+        gts.append(T)
+        return tgt, src
+    (tmp_path / "pairs.txt").write_text("idx1,idx2\n" + "".join("%d,%d\n" % p for p in pair_ids))
+    registration.write_synthetic_dataset(pair_ids, str(tmp_path / "pc"), make, 30000)
+    rows, out = registration.run(str(tmp_path / "pairs.txt"), str(tmp_path / "pc"), str(tmp_path / "reg_result.txt"),
+                                 init="ransac", max_iteration=50, R_diff_thres=1e-6, t_diff_thres=1e-6)
+    lines = (tmp_path / "reg_result.txt").read_text().splitlines()
+    assert len(lines) == 4 and lines[0] == "# idx1,idx2,t_x,t_y,t_z,q_w,q_x,q_y,q_z" and lines[1].startswith("643,456,")
+    for j in range(3):
+        ok, rte, rre = evaluate_rt.is_registration_successful(out["T_total"][j], gts[j])
+        assert ok and rte < 0.1 and rre < 0.2, (j, rte, rre)
+        assert np.allclose(rows[j, 2:], icp.homo2tq(out["T_last"][j]))
