@@ -123,180 +123,271 @@ __global__ void __launch_bounds__(256) key_kernel(const float *__restrict__ xyz,
 // exchange by warp shuffle, larger ones through shared memory.  Pad slots (beyond the cloud) carry
 // the largest key on every axis (no finite float maps to it), so real points always stay at the front of their segment and
 // bucket b of the node holds sorted positions [32b, 32b+32) exactly as the hierarchy expects.
-constexpr int kRefine = 1024;                 // points per block == threads per CTA
+constexpr int kRefine = 1024;                 // points per block (one level-1 node)
+constexpr int kRefineE = 8;                   // points per thread: slot s of the block lives in thread s / 8, register s % 8
+constexpr int kRefineT = kRefine / kRefineE;  // threads per CTA
 constexpr unsigned kPadKey = 0xffffffffu;
 
 struct RefineSmem {
-    float x[kRefine], y[kRefine], z[kRefine];
+    unsigned ox[kRefine], oy[kRefine], oz[kRefine];   // coordinates as ordered integers, addressed by element id
     unsigned key[2][kRefine];                  // double-buffered exchange: one barrier per cross-warp stage
-    unsigned box[32][6];                       // per segment: ordered-uint min xyz, max xyz
+    unsigned box[2][6];                        // segments of 512 / 1024 slots span warps: ordered-uint min xyz, max xyz
 };
 
-// One compare-exchange stage of the direction-free bitonic network: slot t against slot t ^ MASK, the slot
-// whose BIT is clear keeps the smaller key.  Masks below 32 exchange by shuffle, larger ones through shared memory.
+// One compare-exchange stage of the direction-free bitonic network: slot s against slot s ^ MASK, the slot whose
+// BIT is clear keeps the smaller key.  With eight consecutive slots per thread the strides 1, 2, 4 (and the mirror
+// masks 1, 3, 7) stay inside the thread -- one min and one max per pair, no select, no exchange: 117 of the 200
+// stages of a block.  Strides up to 128 exchange registers by warp shuffle, 256 and 512 through shared memory
+// (4 stages of a block).
 template <unsigned MASK, unsigned BIT>
-__device__ __forceinline__ void refine_stage(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
-    unsigned other;
-    if (MASK >= 32) {
-        sm.key[phase][t] = key;
-        __syncthreads();
-        other = sm.key[phase][t ^ MASK];
-        phase ^= 1u;                           // the next exchange writes the other buffer: no second barrier
+__device__ __forceinline__ void refine_stage(RefineSmem &sm, unsigned (&k)[kRefineE], unsigned t, unsigned &phase) {
+    if (MASK < kRefineE) {
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r) {
+            const int p = r ^ (int)MASK;
+            if (p > r) {
+                const unsigned lo = min(k[r], k[p]), hi = max(k[r], k[p]);
+                const bool first_low = (r & (int)BIT) == 0;
+                k[r] = first_low ? lo : hi;
+                k[p] = first_low ? hi : lo;
+            }
+        }
     } else {
-        other = __shfl_xor_sync(kFullMask, key, MASK);
+        constexpr unsigned TM = MASK / kRefineE, RM = MASK % kRefineE;   // partner thread, partner register
+        unsigned o[kRefineE];
+        if (TM >= 32) {
+            uint4 *mine = reinterpret_cast<uint4 *>(sm.key[phase] + t * kRefineE);
+            mine[0] = make_uint4(k[0], k[1], k[2], k[3]);
+            mine[1] = make_uint4(k[4], k[5], k[6], k[7]);
+            __syncthreads();
+            const uint4 *theirs = reinterpret_cast<const uint4 *>(sm.key[phase] + (t ^ TM) * kRefineE);
+            const uint4 a = theirs[0], b = theirs[1];
+            const unsigned v[kRefineE] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int r = 0; r < kRefineE; ++r) o[r] = v[r ^ (int)RM];
+            phase ^= 1u;                       // the next exchange writes the other buffer: no second barrier
+        } else {
+#pragma unroll
+            for (int r = 0; r < kRefineE; ++r) o[r] = __shfl_xor_sync(kFullMask, k[r ^ (int)RM], TM);
+        }
+        const bool keep_low = (t & (BIT / kRefineE)) == 0;
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r) k[r] = keep_low ? min(k[r], o[r]) : max(k[r], o[r]);
     }
-    key = (t & BIT) == 0 ? min(key, other) : max(key, other);
 }
 
 // merge step K of the network (blocks of K become sorted): mirror stage, then strides K/4 ... 1
 template <unsigned K, unsigned J>
 struct RefineMerge {
-    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
-        refine_stage<J, J>(sm, key, t, phase);
-        RefineMerge<K, J / 2>::run(sm, key, t, phase);
+    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned (&k)[kRefineE], unsigned t, unsigned &phase) {
+        refine_stage<J, J>(sm, k, t, phase);
+        RefineMerge<K, J / 2>::run(sm, k, t, phase);
     }
 };
 template <unsigned K>
 struct RefineMerge<K, 0> {
-    static __device__ __forceinline__ void run(RefineSmem &, unsigned &, unsigned, unsigned &) {}
+    static __device__ __forceinline__ void run(RefineSmem &, unsigned (&)[kRefineE], unsigned, unsigned &) {}
 };
 // ascending sort of every aligned segment of S slots, fully unrolled: K = 2, 4, ..., S
 template <unsigned S, unsigned K = 2>
 struct RefineSort {
-    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned &key, unsigned t, unsigned &phase) {
-        refine_stage<K - 1, K / 2>(sm, key, t, phase);          // slot i of a block against slot K-1-i
-        RefineMerge<K, K / 4>::run(sm, key, t, phase);
-        RefineSort<S, K * 2>::run(sm, key, t, phase);
+    static __device__ __forceinline__ void run(RefineSmem &sm, unsigned (&k)[kRefineE], unsigned t, unsigned &phase) {
+        refine_stage<K - 1, K / 2>(sm, k, t, phase);            // slot i of a block against slot K-1-i
+        RefineMerge<K, K / 4>::run(sm, k, t, phase);
+        RefineSort<S, K * 2>::run(sm, k, t, phase);
     }
 };
 template <unsigned S>
 struct RefineSort<S, 2 * S> {
-    static __device__ __forceinline__ void run(RefineSmem &, unsigned &, unsigned, unsigned &) {}
+    static __device__ __forceinline__ void run(RefineSmem &, unsigned (&)[kRefineE], unsigned, unsigned &) {}
 };
 
 // One level of the kd refinement: every aligned segment of S slots is sorted along its widest axis, which splits
-// it at the median into two segments of S/2.
+// it at the median into two segments of S/2.  id[r]: the element in slot 8 t + r; bit r of realm: it is a real point
+// (pad elements carry the coordinates of a real one, so they never widen a box).
 template <unsigned S>
-__device__ __forceinline__ void refine_level(RefineSmem &sm, unsigned &id, bool &real, unsigned &phase) {
+__device__ __forceinline__ void refine_level(RefineSmem &sm, unsigned (&id)[kRefineE], unsigned &realm, unsigned &phase) {
     const unsigned t = threadIdx.x;
-    const unsigned seg = t / S;
+    constexpr unsigned TS = S / kRefineE;      // threads per segment: 4 .. 128
     // ---- widest axis of every segment
-    if (t < 32 * 6) sm.box[t / 6][t % 6] = (t % 6) < 3 ? 0xffffffffu : 0u;
-    __syncthreads();                           // also orders the sm.x/y/z stores before the first gather
-    const unsigned ox = float_to_ordered(sm.x[id]), oy = float_to_ordered(sm.y[id]), oz = float_to_ordered(sm.z[id]);
-    {
-        // a warp never straddles segments (S >= 32)
-        const unsigned mnx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), mxx = __reduce_max_sync(kFullMask, real ? ox : 0u);
-        const unsigned mny = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), mxy = __reduce_max_sync(kFullMask, real ? oy : 0u);
-        const unsigned mnz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), mxz = __reduce_max_sync(kFullMask, real ? oz : 0u);
-        if ((t & 31) == 0) {
-            if (S > 32) {
-                atomicMin(&sm.box[seg][0], mnx); atomicMin(&sm.box[seg][1], mny); atomicMin(&sm.box[seg][2], mnz);
-                atomicMax(&sm.box[seg][3], mxx); atomicMax(&sm.box[seg][4], mxy); atomicMax(&sm.box[seg][5], mxz);
-            } else {
-                sm.box[seg][0] = mnx; sm.box[seg][1] = mny; sm.box[seg][2] = mnz;
-                sm.box[seg][3] = mxx; sm.box[seg][4] = mxy; sm.box[seg][5] = mxz;
+    unsigned mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r) {
+        const unsigned ox = sm.ox[id[r]], oy = sm.oy[id[r]], oz = sm.oz[id[r]];
+        mn[0] = min(mn[0], ox); mn[1] = min(mn[1], oy); mn[2] = min(mn[2], oz);
+        mx[0] = max(mx[0], ox); mx[1] = max(mx[1], oy); mx[2] = max(mx[2], oz);
+    }
+    if (TS == 32) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { mn[a] = __reduce_min_sync(kFullMask, mn[a]); mx[a] = __reduce_max_sync(kFullMask, mx[a]); }
+    } else if (TS < 32) {                      // the segment's threads are an aligned group of lanes: butterfly
+#pragma unroll
+        for (unsigned d = 1; d < TS; d *= 2) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                mn[a] = min(mn[a], __shfl_xor_sync(kFullMask, mn[a], d));
+                mx[a] = max(mx[a], __shfl_xor_sync(kFullMask, mx[a], d));
             }
         }
+    } else {
+        const unsigned seg = t / TS;
+        if (t < 12) sm.box[t / 6][t % 6] = (t % 6) < 3 ? 0xffffffffu : 0u;
+        __syncthreads();
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { mn[a] = __reduce_min_sync(kFullMask, mn[a]); mx[a] = __reduce_max_sync(kFullMask, mx[a]); }
+        if ((t & 31u) == 0) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { atomicMin(&sm.box[seg][a], mn[a]); atomicMax(&sm.box[seg][3 + a], mx[a]); }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { mn[a] = sm.box[seg][a]; mx[a] = sm.box[seg][3 + a]; }
     }
-    __syncthreads();
-    const float wx = ordered_to_float(sm.box[seg][3]) - ordered_to_float(sm.box[seg][0]);
-    const float wy = ordered_to_float(sm.box[seg][4]) - ordered_to_float(sm.box[seg][1]);
-    const float wz = ordered_to_float(sm.box[seg][5]) - ordered_to_float(sm.box[seg][2]);
-    // empty segments give NaN / negative widths: any axis will do
-    const unsigned okey = (wx >= wy && wx >= wz) ? ox : (wy >= wz ? oy : oz);
-    // 22 coordinate bits + 10 slot bits in one word: the split is a partition heuristic, the slot makes keys
+    const float wx = ordered_to_float(mx[0]) - ordered_to_float(mn[0]);
+    const float wy = ordered_to_float(mx[1]) - ordered_to_float(mn[1]);
+    const float wz = ordered_to_float(mx[2]) - ordered_to_float(mn[2]);
+    const unsigned *c = sm.ox + ((wx >= wy && wx >= wz) ? 0 : (wy >= wz ? kRefine : 2 * kRefine));   // ox, oy, oz are contiguous
+    // 22 coordinate bits + 10 element bits in one word: the split is a partition heuristic, the element id makes keys
     // unique and the order deterministic; pads carry the largest key
-    unsigned key = ((real ? okey : kPadKey) & ~(kRefine - 1u)) | id;
-    RefineSort<S>::run(sm, key, t, phase);
-    id = key & (kRefine - 1u);
-    real = (key | (kRefine - 1u)) != kPadKey;
+    unsigned k[kRefineE];
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r)
+        k[r] = ((((realm >> r) & 1u) ? c[id[r]] : kPadKey) & ~(kRefine - 1u)) | id[r];
+    RefineSort<S>::run(sm, k, t, phase);
+    realm = 0;
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r) {
+        id[r] = k[r] & (kRefine - 1u);
+        realm |= ((k[r] | (kRefine - 1u)) != kPadKey ? 1u : 0u) << r;
+    }
 }
 
-// Thread t owns slot t.  In: its element's coordinates (valid = real point).  Out: the element id (0..1023,
-// the slot that loaded it) that ends up in slot t; coordinates stay addressable by id in sm.x/y/z.
+// Loads done (sm.ox/oy/oz and the caller's per-element payload filled for all 1024 slots, barrier NOT yet passed):
+// gives pad elements the coordinates of the block's first point (always real), then runs the levels.
+// Out: id[r] = the element (0..1023, the slot that loaded it) that ends up in slot 8 t + r.
 // HALVES: a sixth level splits the 32-slot segments (buckets) into halves of 16.
 template <bool HALVES>
-__device__ __forceinline__ unsigned refine_block(RefineSmem &sm, float x, float y, float z, bool valid) {
+__device__ __forceinline__ void refine_block(RefineSmem &sm, unsigned (&id)[kRefineE], unsigned &realm) {
     const unsigned t = threadIdx.x;
-    sm.x[t] = x; sm.y[t] = y; sm.z[t] = z;
-    unsigned id = t, phase = 0;
-    bool real = valid;
-    refine_level<1024>(sm, id, real, phase);
-    refine_level<512>(sm, id, real, phase);
-    refine_level<256>(sm, id, real, phase);
-    refine_level<128>(sm, id, real, phase);
-    refine_level<64>(sm, id, real, phase);
-    if (HALVES) refine_level<32>(sm, id, real, phase);
-    return id;
+    __syncthreads();
+    if (realm != 0xffu) {
+        const unsigned x0 = sm.ox[0], y0 = sm.oy[0], z0 = sm.oz[0];
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r)
+            if (!((realm >> r) & 1u)) { sm.ox[t * kRefineE + r] = x0; sm.oy[t * kRefineE + r] = y0; sm.oz[t * kRefineE + r] = z0; }
+    }
+    __syncthreads();
+    unsigned phase = 0;
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r) id[r] = t * kRefineE + r;
+    refine_level<1024>(sm, id, realm, phase);
+    refine_level<512>(sm, id, realm, phase);
+    refine_level<256>(sm, id, realm, phase);
+    refine_level<128>(sm, id, realm, phase);
+    refine_level<64>(sm, id, realm, phase);
+    if (HALVES) refine_level<32>(sm, id, realm, phase);
+}
+
+__device__ __forceinline__ void refine_store8(unsigned *dst, const unsigned (&v)[kRefineE]) {
+    reinterpret_cast<uint4 *>(dst)[0] = make_uint4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<uint4 *>(dst)[1] = make_uint4(v[4], v[5], v[6], v[7]);
 }
 
 // One CTA per level-1 node: gather the node's points through the Morton order, refine, write the float4
 // bucket rows (pad lanes NaN / index -1, so that every distance against them is NaN and fails every "<="
-// gate) and the bucket AABBs.
-__global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__restrict__ xyz, long long stride,
-                                                               const IndexView *__restrict__ views,
-                                                               const unsigned *__restrict__ sorted_rows) {
-    __shared__ RefineSmem sm;
-    __shared__ unsigned s_idx[kRefine];
+// gate), their pair-layout copy, and the bucket / half-bucket AABBs.
+__global__ void __launch_bounds__(kRefineT) refine_leaf_kernel(const float *__restrict__ xyz, long long stride,
+                                                                const IndexView *__restrict__ views,
+                                                                const unsigned *__restrict__ sorted_rows) {
+    __shared__ __align__(16) RefineSmem sm;
+    __shared__ __align__(16) unsigned s_idx[kRefine];
     __shared__ unsigned s_node[6];                               // AABB of the whole block = the level-1 node
     const IndexView &v = views[blockIdx.y];
     const long long node = blockIdx.x;
     if (node * kFan >= v.n_leaf) return;
     const unsigned t = threadIdx.x;
     if (t < 6) s_node[t] = t < 3 ? 0xffffffffu : 0u;             // (ordered by the barriers inside refine_block)
-    const long long pos = node * kRefine + t;
-    float x = nanf(""), y = x, z = x;
-    unsigned idx = 0xffffffffu;
-    const bool valid = pos < v.n;
-    if (valid) {
-        const unsigned row = sorted_rows[v.src_off + pos];       // sorted by (segment, morton): rows of this segment
-        const float *p = xyz + (long long)row * stride;
-        x = p[0]; y = p[1]; z = p[2];
-        idx = row - static_cast<unsigned>(v.src_off);
-    }
-    s_idx[t] = idx;
-    const unsigned id = refine_block<true>(sm, x, y, z, valid);
-    const long long leaf = pos >> 5;
-    if (leaf < v.n_leaf) {                                       // (whole warp) else: bucket beyond the cloud
-    x = sm.x[id]; y = sm.y[id]; z = sm.z[id];
-    idx = s_idx[id];
-    const_cast<float4 *>(v.pts)[pos] = make_float4(x, y, z, __uint_as_float(idx));
-    const bool real = idx != 0xffffffffu;
+    const long long pos0 = node * kRefine + t * kRefineE;
+    unsigned id[kRefineE], realm = 0;
     {
-        // pair layout (IndexView::pts2): the even lane of a pair writes (x0, x1, y0, y1), the odd one (z0, z1, w0, w1)
-        const bool odd = (t & 1u) != 0u;
-        const float px = real ? x : __uint_as_float(0x7f800000u), py = real ? y : 0.f, pz = real ? z : 0.f;
-        const float pw = __uint_as_float(idx);
-        const float a = __shfl_xor_sync(kFullMask, odd ? px : pz, 1);
-        const float b = __shfl_xor_sync(kFullMask, odd ? py : pw, 1);
-        const_cast<float4 *>(v.pts2)[pos] = odd ? make_float4(a, pz, b, pw) : make_float4(px, a, py, b);
+        unsigned ox[kRefineE], oy[kRefineE], oz[kRefineE], idx[kRefineE];
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r) {
+            ox[r] = oy[r] = oz[r] = 0u;
+            idx[r] = 0xffffffffu;
+            if (pos0 + r < v.n) {
+                const unsigned row = sorted_rows[v.src_off + pos0 + r];   // sorted by (segment, morton): rows of this segment
+                const float *p = xyz + (long long)row * stride;
+                ox[r] = float_to_ordered(p[0]); oy[r] = float_to_ordered(p[1]); oz[r] = float_to_ordered(p[2]);
+                idx[r] = row - static_cast<unsigned>(v.src_off);
+                realm |= 1u << r;
+            }
+        }
+        refine_store8(sm.ox + t * kRefineE, ox);
+        refine_store8(sm.oy + t * kRefineE, oy);
+        refine_store8(sm.oz + t * kRefineE, oz);
+        refine_store8(s_idx + t * kRefineE, idx);
     }
-    const unsigned ox = float_to_ordered(x), oy = float_to_ordered(y), oz = float_to_ordered(z);
-    const unsigned lx = __reduce_min_sync(kFullMask, real ? ox : 0xffffffffu), hx = __reduce_max_sync(kFullMask, real ? ox : 0u);
-    const unsigned ly = __reduce_min_sync(kFullMask, real ? oy : 0xffffffffu), hy = __reduce_max_sync(kFullMask, real ? oy : 0u);
-    const unsigned lz = __reduce_min_sync(kFullMask, real ? oz : 0xffffffffu), hz = __reduce_max_sync(kFullMask, real ? oz : 0u);
-    if ((t & 31) == 0) {
-        const_cast<float4 *>(v.box_lo)[leaf] = make_float4(ordered_to_float(lx), ordered_to_float(ly), ordered_to_float(lz), 0.f);
-        const_cast<float4 *>(v.box_hi)[leaf] = make_float4(ordered_to_float(hx), ordered_to_float(hy), ordered_to_float(hz), 0.f);
-        atomicMin(&s_node[0], lx); atomicMin(&s_node[1], ly); atomicMin(&s_node[2], lz);
-        atomicMax(&s_node[3], hx); atomicMax(&s_node[4], hy); atomicMax(&s_node[5], hz);
+    refine_block<true>(sm, id, realm);
+
+    // slots 8 t .. 8 t + 7: a quarter of bucket t / 4, half of its 16-point half (t / 2) & 1
+    const long long leaf = pos0 >> 5;
+    const bool store = leaf < v.n_leaf;                          // else: bucket beyond the cloud
+    const float nan = __uint_as_float(0x7fc00000u), inf = __uint_as_float(0x7f800000u);
+    unsigned mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
+    float4 P[kRefineE];
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r) {
+        const bool real = (realm >> r) & 1u;
+        const unsigned ox = sm.ox[id[r]], oy = sm.oy[id[r]], oz = sm.oz[id[r]];
+        mn[0] = min(mn[0], real ? ox : 0xffffffffu); mn[1] = min(mn[1], real ? oy : 0xffffffffu); mn[2] = min(mn[2], real ? oz : 0xffffffffu);
+        mx[0] = max(mx[0], real ? ox : 0u); mx[1] = max(mx[1], real ? oy : 0u); mx[2] = max(mx[2], real ? oz : 0u);
+        P[r] = real ? make_float4(ordered_to_float(ox), ordered_to_float(oy), ordered_to_float(oz), __uint_as_float(s_idx[id[r]]))
+                    : make_float4(nan, nan, nan, __uint_as_float(0xffffffffu));
+    }
+    if (store) {
+        float4 *dst = const_cast<float4 *>(v.pts) + pos0;
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r) dst[r] = P[r];
+        // pair layout (IndexView::pts2): entries 2m / 2m+1 = (x0, x1, y0, y1) / (z0, z1, w0, w1) of points 2m, 2m+1
+        float4 *dst2 = const_cast<float4 *>(v.pts2) + pos0;
+#pragma unroll
+        for (int m = 0; m < kRefineE / 2; ++m) {
+            const bool ra = (realm >> (2 * m)) & 1u, rb = (realm >> (2 * m + 1)) & 1u;
+            const float4 a = P[2 * m], b = P[2 * m + 1];
+            dst2[2 * m] = make_float4(ra ? a.x : inf, rb ? b.x : inf, ra ? a.y : 0.f, rb ? b.y : 0.f);
+            dst2[2 * m + 1] = make_float4(ra ? a.z : 0.f, rb ? b.z : 0.f, a.w, b.w);
+        }
     }
     // AABBs of the two 16-point halves (the sixth split): an empty half gets (+inf, -inf), infinitely far from everything
-    const unsigned hm = (t & 16) ? 0xffff0000u : 0x0000ffffu;
-    const unsigned alx = __reduce_min_sync(hm, real ? ox : 0xffffffffu), ahx = __reduce_max_sync(hm, real ? ox : 0u);
-    const unsigned aly = __reduce_min_sync(hm, real ? oy : 0xffffffffu), ahy = __reduce_max_sync(hm, real ? oy : 0u);
-    const unsigned alz = __reduce_min_sync(hm, real ? oz : 0xffffffffu), ahz = __reduce_max_sync(hm, real ? oz : 0u);
-    if ((t & 15) == 0) {
-        const bool any = alx != 0xffffffffu;
-        const float inf = __uint_as_float(0x7f800000u);
-        float4 *h = const_cast<float4 *>(v.half) + leaf * 4 + ((t & 16) ? 2 : 0);
-        h[0] = any ? make_float4(ordered_to_float(alx), ordered_to_float(aly), ordered_to_float(alz), 0.f) : make_float4(inf, inf, inf, 0.f);
-        h[1] = any ? make_float4(ordered_to_float(ahx), ordered_to_float(ahy), ordered_to_float(ahz), 0.f) : make_float4(-inf, -inf, -inf, 0.f);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        mn[a] = min(mn[a], __shfl_xor_sync(kFullMask, mn[a], 1));
+        mx[a] = max(mx[a], __shfl_xor_sync(kFullMask, mx[a], 1));
     }
+    if (store && (t & 1u) == 0) {
+        const bool any = mn[0] != 0xffffffffu;
+        float4 *h = const_cast<float4 *>(v.half) + leaf * 4 + ((t & 2u) ? 2 : 0);
+        h[0] = any ? make_float4(ordered_to_float(mn[0]), ordered_to_float(mn[1]), ordered_to_float(mn[2]), 0.f) : make_float4(inf, inf, inf, 0.f);
+        h[1] = any ? make_float4(ordered_to_float(mx[0]), ordered_to_float(mx[1]), ordered_to_float(mx[2]), 0.f) : make_float4(-inf, -inf, -inf, 0.f);
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        mn[a] = min(mn[a], __shfl_xor_sync(kFullMask, mn[a], 2));
+        mx[a] = max(mx[a], __shfl_xor_sync(kFullMask, mx[a], 2));
+    }
+    if (store && (t & 3u) == 0) {
+        const_cast<float4 *>(v.box_lo)[leaf] = make_float4(ordered_to_float(mn[0]), ordered_to_float(mn[1]), ordered_to_float(mn[2]), 0.f);
+        const_cast<float4 *>(v.box_hi)[leaf] = make_float4(ordered_to_float(mx[0]), ordered_to_float(mx[1]), ordered_to_float(mx[2]), 0.f);
     }
     // the block is one level-1 node: its box is the union of the bucket boxes (same values node_box_kernel
     // would compute: min / max of the same floats)
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = __reduce_min_sync(kFullMask, mn[a]); mx[a] = __reduce_max_sync(kFullMask, mx[a]); }
+    if ((t & 31u) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { atomicMin(&s_node[a], mn[a]); atomicMax(&s_node[3 + a], mx[a]); }
+    }
     __syncthreads();
     if (t == 0 && v.n_levels > 1) {
         const long long at = v.level_off[1] + node;
@@ -307,23 +398,36 @@ __global__ void __launch_bounds__(kRefine) refine_leaf_kernel(const float *__res
 
 // Same refinement for a sorted QUERY set: blocks of 1024 Morton-consecutive queries are re-grouped into 32
 // tight groups of 32 (one group = one warp of the tiled kNN kernel).  In place on the permutation.
-__global__ void __launch_bounds__(kRefine) refine_queries_kernel(const float *__restrict__ q, long long nq, long long stride,
-                                                                  unsigned *__restrict__ perm) {
-    __shared__ RefineSmem sm;
-    __shared__ unsigned s_idx[kRefine];
+__global__ void __launch_bounds__(kRefineT) refine_queries_kernel(const float *__restrict__ q, long long nq, long long stride,
+                                                                   unsigned *__restrict__ perm) {
+    __shared__ __align__(16) RefineSmem sm;
+    __shared__ __align__(16) unsigned s_idx[kRefine];
     const unsigned t = threadIdx.x;
-    const long long pos = blockIdx.x * (long long)kRefine + t;
-    float x = 0.f, y = 0.f, z = 0.f;
-    unsigned row = 0xffffffffu;
-    const bool valid = pos < nq;
-    if (valid) {
-        row = perm[pos];
-        const float *p = q + (long long)row * stride;
-        x = p[0]; y = p[1]; z = p[2];
+    const long long pos0 = blockIdx.x * (long long)kRefine + t * kRefineE;
+    unsigned id[kRefineE], realm = 0;
+    {
+        unsigned ox[kRefineE], oy[kRefineE], oz[kRefineE], idx[kRefineE];
+#pragma unroll
+        for (int r = 0; r < kRefineE; ++r) {
+            ox[r] = oy[r] = oz[r] = 0u;
+            idx[r] = 0xffffffffu;
+            if (pos0 + r < nq) {
+                idx[r] = perm[pos0 + r];
+                const float *p = q + (long long)idx[r] * stride;
+                ox[r] = float_to_ordered(p[0]); oy[r] = float_to_ordered(p[1]); oz[r] = float_to_ordered(p[2]);
+                realm |= 1u << r;
+            }
+        }
+        refine_store8(sm.ox + t * kRefineE, ox);
+        refine_store8(sm.oy + t * kRefineE, oy);
+        refine_store8(sm.oz + t * kRefineE, oz);
+        refine_store8(s_idx + t * kRefineE, idx);
     }
-    s_idx[t] = row;
-    const unsigned id = refine_block<false>(sm, x, y, z, valid);
-    if (valid) perm[pos] = s_idx[id];          // real queries stay at the front of the block: slot t < nq - base is real
+    refine_block<false>(sm, id, realm);
+    // real queries stay at the front of the block: slot s < nq - base is real
+#pragma unroll
+    for (int r = 0; r < kRefineE; ++r)
+        if (pos0 + r < nq) perm[pos0 + r] = s_idx[id[r]];
 }
 
 __global__ void __launch_bounds__(256) node_box_kernel(const IndexView *__restrict__ views, int level) {
@@ -543,7 +647,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
-        refine_leaf_kernel<<<dim3((unsigned)((b->max_leaf + kFan - 1) / kFan), gy), kRefine, 0, st>>>(
+        refine_leaf_kernel<<<dim3((unsigned)((b->max_leaf + kFan - 1) / kFan), gy), kRefineT, 0, st>>>(
             d_xyz, stride, dv + p0, b->vals_b.as<unsigned>());
         ctx->launches += 1;
         // level 1 came out of refine_leaf_kernel; wide levels get a launch each, the small ones above share one
@@ -584,7 +688,7 @@ int sort_queries_on(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride,
     query_key_kernel<<<grid_for(nq, 256), 256, 0, st>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
     ctx->launches += 1;
     PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30, st, &cub_tmp));
-    refine_queries_kernel<<<grid_for(nq, kRefine), kRefine, 0, st>>>(d_q, nq, stride, d_perm);
+    refine_queries_kernel<<<grid_for(nq, kRefine), kRefineT, 0, st>>>(d_q, nq, stride, d_perm);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;

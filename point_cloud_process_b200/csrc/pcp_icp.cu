@@ -280,42 +280,50 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
         };
         float m32 = __int_as_float(0x7f800000);                // smallest float32 d^2 this lane has seen
         unsigned n_pts = 0;                                    // work counter: points evaluated per lane
+        const f32x2 qx2 = pk2(qx, qx), qy2 = pk2(qy, qy), qz2 = pk2(qz, qz);
+        // pv: this lane's float4 of the bucket in the PAIR layout (IndexView::pts2): entries 2m / 2m+1 hold
+        // (x0, x1, y0, y1) / (z0, z1, w0, w1) of points 2m, 2m+1; pad points have x = +inf (d^2 = +inf)
         auto scan_bucket = [&](const float4 pv, unsigned halves) {
             n_pts += 16u * __popc(halves);
             __syncwarp();
             tile[lane] = pv;
             __syncwarp();
             unsigned mask = 0;
-            // 8 points at a time.  The gate is tightened INSIDE the scan from the running float32 minimum: a point
-            // whose float32 d^2 is m has a true d^2 <= (sqrt(m) + 2.5 E)^2 (1 + 6 eps), and whatever beats or ties it
-            // has a float32 d^2 <= (sqrt(m) + 3.5 E)^2 (1 + 12 eps) -- bounded here by (sqrt(m)(1 + 2e-6) + 4 E)^2
-            // rounded up.  Only "record setters" of the float32 scan reach the float64 evaluation below (a handful
-            // per bucket instead of every point inside the initial dist_thres ball).
+            // 8 points at a time, two per packed FP32 instruction (bit-equal to ref_d2).  The gate is tightened INSIDE
+            // the scan from the running float32 minimum: a point whose float32 d^2 is m has a true d^2 <=
+            // (sqrt(m) + 2.5 E)^2 (1 + 6 eps), and whatever beats or ties it has a float32 d^2 <=
+            // (sqrt(m) + 3.5 E)^2 (1 + 12 eps) -- bounded here by (sqrt(m)(1 + 2e-6) + 4 E)^2 rounded up.  Only "record
+            // setters" of the float32 scan reach the float64 evaluation below (a handful per bucket instead of every
+            // point inside the initial dist_thres ball); a chunk whose minimum misses the gate costs no mask work.
 #pragma unroll
             for (int j0 = 0; j0 < 32; j0 += 8) {
                 if (!((halves >> (j0 >> 4)) & 1u)) continue;
                 float d2[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float4 p = tile[j0 + j];
-                    d2[j] = ref_d2(qx, qy, qz, p.x, p.y, p.z);
+                for (int m = 0; m < 4; ++m) {
+                    const float4 a = tile[j0 + 2 * m];
+                    const float2 b = *reinterpret_cast<const float2 *>(tile + j0 + 2 * m + 1);
+                    ref_d2_pair(qx2, qy2, qz2, pk2(a.x, a.y), pk2(a.z, a.w), pk2(b.x, b.y), d2[2 * m], d2[2 * m + 1]);
                 }
-                float cm = fminf(fminf(fminf(d2[0], d2[1]), fminf(d2[2], d2[3])), fminf(fminf(d2[4], d2[5]), fminf(d2[6], d2[7])));
-                if (cm < m32) {                                  // NaN pads never lower the minimum
-                    m32 = cm;
-                    const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(cm), 1.000002f), __fmul_ru(4.f, E));
-                    gate = fminf(gate, __fmul_ru(r, r));
-                }
+                const float cm = min3f(min3f(d2[0], d2[1], d2[2]), min3f(d2[3], d2[4], d2[5]), fminf(d2[6], d2[7]));
+                if (cm <= gate) {
+                    if (cm < m32) {
+                        m32 = cm;
+                        const float r = __fadd_ru(__fmul_ru(__fsqrt_ru(cm), 1.000002f), __fmul_ru(4.f, E));
+                        gate = fminf(gate, __fmul_ru(r, r));
+                    }
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (d2[j] <= gate) mask |= 1u << (j0 + j);   // NaN pads never pass
+                    for (int j = 0; j < 8; ++j)
+                        if (d2[j] <= gate) mask |= 1u << (j0 + j);
+                }
             }
             bool changed = false;
             while (__any_sync(kFullMask, mask != 0)) {
                 if (mask) {
                     const int j = __ffs(mask) - 1;
                     mask &= mask - 1;
-                    const float4 p = tile[j];
+                    const float *e = reinterpret_cast<const float *>(tile) + (j >> 1) * 8 + (j & 1);
+                    const float4 p = make_float4(e[0], e[2], e[4], e[6]);
                     const double dx = ax - (double)p.x, dy = ay - (double)p.y, dz = az - (double)p.z;
                     const double d2 = dx * dx + dy * dy + dz * dz;
                     const unsigned id = __float_as_uint(p.w);
@@ -390,7 +398,7 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
                     open_node(level, child);
                     continue;
                 }
-                const float4 *base = ix.pts + (long long)nodes[1] * kFan * kLeaf + lane;
+                const float4 *base = ix.pts2 + (long long)nodes[1] * kFan * kLeaf + lane;
                 unsigned halves = 0;
                 while (sel >= 0 && !(halves = bucket_needed(sel))) sel = pick(1);
                 if (sel < 0) continue;
