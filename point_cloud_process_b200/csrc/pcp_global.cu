@@ -7,7 +7,7 @@
 // restate its PUBLISHED algorithms (Rusu et al. FPFH with Open3D's pair-feature / binning / 1 / d^2 weighting
 // conventions; RANSAC over 3-correspondence Kabsch hypotheses with the edge-length and distance checkers,
 // fitness / RMSE evaluation and confidence-based termination), with a seeded counter-hash random stream instead of
-// Open3D's global generator.  Parity is "unpinned"; the tests pin the restatement (oracle/global_oracle.py) and
+// Open3D's global generator.  Parity is "unpinned"; the tests pin a CPU restatement of the same conventions and
 // planted-pose properties.
 //
 //   hybrid neighbourhoods  radius CSR of the cloud against itself, rows sorted by (distance, index); a row's first
