@@ -158,6 +158,21 @@ PCP_API int pcp_knn_self(pcp_index *index, int k, int mem, int32_t *idx, float *
  * the search kernels: the test-suite uses it as the on-device second oracle for full-size query sets. */
 PCP_API int pcp_knn_bruteforce(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats, int k, int mem,
                                int32_t *idx, float *dist, int32_t *count);
+
+/* pcp_knn_bruteforce for callers that cannot allocate device memory (code under stream capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * No context and no index: points, queries and results are DEVICE pointers of the caller; the kernel's
+ * scratch (the pair-layout copy of the cloud) is a static device array of PCP_NOALLOC_MAX_POINTS x 16 B = 4 MiB that
+ * every GPU loading the library holds until exit.  The call performs no cudaMalloc / cudaFree and enqueues two
+ * kernels on `stream` (a cudaStream_t, NULL = the default stream) without synchronising.  n > PCP_NOALLOC_MAX_POINTS
+ * fails with PCP_ERR_UNSUPPORTED.  Outputs are identical to pcp_knn_bruteforce (canonical (distance, index) order,
+ * unfilled slots (PCP_KNN_EMPTY_DIST, 0)); count may be NULL.  All calls on a device share the array, which keeps
+ * the last call's contents (every slot read is rewritten first, nothing has to be cleared): calls that overlap on
+ * the GPU -- different streams or host threads -- race and must be serialised by the caller. */
+#define PCP_NOALLOC_MAX_POINTS 262144
+PCP_API int pcp_knn_bruteforce_noalloc(int device, const float *d_points, int64_t n, int64_t point_stride_floats,
+                                       const float *d_queries, int64_t nq, int64_t query_stride_floats, int k,
+                                       int32_t *d_idx, float *d_dist, int32_t *d_count, void *stream);
 /* counts[i] = number of indexed points with float32 dist <= radius, by the same exhaustive kernel (the count
  * RadiusNNResultSet.size() reports, result_set.py:72-73). */
 PCP_API int pcp_radius_count_bruteforce(pcp_index *index, const float *queries, int64_t nq, int64_t stride_floats,

@@ -14,6 +14,8 @@
 // issue slots, its share of the two loads, and a compare.
 #include <cfloat>
 #include <cstdlib>
+#include <mutex>
+#include <string>
 
 #include "pcp_device.cuh"
 #include "pcp_internal.cuh"
@@ -211,4 +213,106 @@ int radius_count_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64
     return PCP_OK;
 }
 
+
+// ---- brute-force kNN without any allocation (pcp_knn_bruteforce_noalloc, include/pcp.h) -------------------------
+// For callers that cannot call cudaMalloc (stream capture, serving loops, harnesses that forbid it).  The one piece of
+// scratch memory the brute-force kernel needs -- the pair-layout copy of the cloud that the TMA tiles are cut from --
+// lives in a file-scope device array of fixed size instead of a context buffer: every GPU that loads the library holds
+// PCP_NOALLOC_MAX_POINTS x 16 B = 4 MiB until the process exits.  No context, no index, no stream of its own.
+// The array is SHARED by every call on a device and keeps the last call's contents: the pack kernel rewrites every
+// slot the search kernel reads (pads included), nothing accumulates, so nothing has to start at zero; calls that
+// overlap on the GPU (two streams, two host threads) race on it.
+namespace {
+
+constexpr long long kNoAllocMaxPoints = PCP_NOALLOC_MAX_POINTS;
+static_assert(kNoAllocMaxPoints % kLeaf == 0, "the scratch holds whole groups of 32 slots");
+static __device__ __align__(256) float4 g_noalloc_pairs[kNoAllocMaxPoints];
+
+// raw rows -> pair layout in input order: entries 2m / 2m+1 = (x0, x1, y0, y1) / (z0, z1, w0, w1) of points 2m, 2m+1,
+// w = the row number; slots beyond the cloud are pads (x = +inf: d2 = +inf passes no gate; index -1)
+__global__ void __launch_bounds__(256) noalloc_pack_kernel(const float *__restrict__ xyz, long long n, long long stride,
+                                                            long long n_slots, float4 *__restrict__ pairs) {
+    const long long m = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (2 * m >= n_slots) return;
+    const float inf = __uint_as_float(0x7f800000u);
+    float x[2] = {inf, inf}, y[2] = {0.f, 0.f}, z[2] = {0.f, 0.f};
+    unsigned w[2] = {0xffffffffu, 0xffffffffu};
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const long long i = 2 * m + j;
+        if (i < n) {
+            const float *p = xyz + i * stride;
+            x[j] = __ldg(p); y[j] = __ldg(p + 1); z[j] = __ldg(p + 2);
+            w[j] = (unsigned)i;
+        }
+    }
+    pairs[2 * m] = make_float4(x[0], x[1], y[0], y[1]);
+    pairs[2 * m + 1] = make_float4(z[0], z[1], __uint_as_float(w[0]), __uint_as_float(w[1]));
+}
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+float4 *g_noalloc_addr[kNoAllocMaxDevices] = {nullptr};
+
+// Once per device, with that device current: the DEVICE address of the array (in host code its name is only a
+// host-side stand-in) and the shared-memory opt-in of the three kernel widths.  None of these calls allocates.
+int noalloc_setup(int device, float4 **out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_addr[device]) {
+        void *ptr = nullptr;
+        PCP_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_pairs));
+        if (!ptr) return fail(PCP_ERR_CUDA, "pcp_knn_bruteforce_noalloc: cudaGetSymbolAddress returned NULL");
+        const int smem = (int)(2 * kTileBytes + 16);
+        PCP_CUDA(cudaFuncSetAttribute(brute_kernel<8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        PCP_CUDA(cudaFuncSetAttribute(brute_kernel<16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        PCP_CUDA(cudaFuncSetAttribute(brute_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        g_noalloc_addr[device] = static_cast<float4 *>(ptr);
+    }
+    *out = g_noalloc_addr[device];
+    return PCP_OK;
+}
+
+}  // namespace
+
 }  // namespace pcp
+
+extern "C" PCP_API int pcp_knn_bruteforce_noalloc(int device, const float *d_points, int64_t n, int64_t point_stride,
+                                                  const float *d_queries, int64_t nq, int64_t query_stride, int k,
+                                                  int32_t *d_idx, float *d_dist, int32_t *d_count, void *stream) {
+    using namespace pcp;
+    if (n < 0 || nq < 0) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce_noalloc: negative size");
+    if (k < 1 || k > PCP_MAX_K) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce_noalloc: k must be in 1.." + std::to_string(PCP_MAX_K));
+    if (n > kNoAllocMaxPoints)
+        return fail(PCP_ERR_UNSUPPORTED, "pcp_knn_bruteforce_noalloc: " + std::to_string(n) + " points exceed the static scratch of " +
+                                             std::to_string(kNoAllocMaxPoints) + " points (PCP_NOALLOC_MAX_POINTS); use pcp_knn_bruteforce");
+    if ((n > 0 && (!d_points || point_stride < 3)) || (nq > 0 && (!d_queries || query_stride < 3)))
+        return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce_noalloc: NULL cloud or stride < 3");
+    if (nq > 0 && (!d_idx || !d_dist)) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce_noalloc: idx/dist is NULL");
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(PCP_ERR_INVALID, "pcp_knn_bruteforce_noalloc: bad device");
+    if (nq == 0) return PCP_OK;
+    int prev = -1;
+    PCP_CUDA(cudaGetDevice(&prev));
+    if (prev != device) PCP_CUDA(cudaSetDevice(device));
+    struct Restore {
+        int prev, device;
+        ~Restore() { if (prev != device) cudaSetDevice(prev); }
+    } restore{prev, device};
+    float4 *pairs = nullptr;
+    PCP_TRY(noalloc_setup(device, &pairs));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long n_slots = (n + kLeaf - 1) / kLeaf * kLeaf;
+    if (n_slots > 0) {
+        noalloc_pack_kernel<<<(unsigned)((n_slots / 2 + 255) / 256), 256, 0, st>>>(d_points, n, point_stride, n_slots, pairs);
+        PCP_CUDA(cudaGetLastError());
+    }
+    const unsigned grid = (unsigned)((nq + kBruteThreads - 1) / kBruteThreads);
+    const size_t smem = 2 * kTileBytes + 16;
+    if (k <= 8)
+        brute_kernel<8, 0><<<grid, kBruteThreads, smem, st>>>(pairs, n_slots, d_queries, nq, query_stride, k, 0.f, d_idx, d_dist, d_count, nullptr);
+    else if (k <= 16)
+        brute_kernel<16, 0><<<grid, kBruteThreads, smem, st>>>(pairs, n_slots, d_queries, nq, query_stride, k, 0.f, d_idx, d_dist, d_count, nullptr);
+    else
+        brute_kernel<32, 0><<<grid, kBruteThreads, smem, st>>>(pairs, n_slots, d_queries, nq, query_stride, k, 0.f, d_idx, d_dist, d_count, nullptr);
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
