@@ -18,7 +18,7 @@ OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libpcp_b200.so")
 MOD = os.path.join(HERE, "_pcp" + sysconfig.get_config_var("EXT_SUFFIX"))
 
-CU_SOURCES = ["pcp_capi.cu", "pcp_build.cu", "pcp_knn.cu", "pcp_knn_tile.cu", "pcp_knn_tile_v1.cu", "pcp_brute.cu", "pcp_multi.cu", "pcp_pointnet.cu", "pcp_global.cu", "pcp_global_ransac.cu", "pcp_radius.cu", "pcp_radius_tile.cu", "pcp_icp.cu", "pcp_front.cu", "pcp_dbscan.cu"]
+CU_SOURCES = ["pcp_capi.cu", "pcp_build.cu", "pcp_knn.cu", "pcp_knn_tile.cu", "pcp_brute.cu", "pcp_multi.cu", "pcp_pointnet.cu", "pcp_global.cu", "pcp_global_ransac.cu", "pcp_radius.cu", "pcp_radius_tile.cu", "pcp_icp.cu", "pcp_front.cu", "pcp_dbscan.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr",
               "-Xptxas", "-v", "-I", os.path.join(ROOT, "include"), "-I", CSRC]

@@ -12,6 +12,7 @@
 //                      memory (the kd-tree's split rule, kdtree.py:74-97, applied below the Morton order)
 //                      -> float4 bucket rows + bucket AABBs                    (Node / Octant objects)
 //   node_box_kernel    32 child AABBs -> parent AABB, once per upper level
+#include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
@@ -430,6 +431,83 @@ __global__ void __launch_bounds__(kRefineT) refine_queries_kernel(const float *_
         if (pos0 + r < nq) perm[pos0 + r] = s_idx[id[r]];
 }
 
+// ---- small clouds (<= 20 480 points each, e.g. the 20 000-point registration clouds): ONE CTA per cloud does
+// what bbox_kernel + key_kernel + the device-wide radix sort do for a batch -- bounding box, Morton keys, stable
+// sort by the significant Morton bits -- with the keys in registers / shared memory instead of three radix passes
+// over 16 B per point in HBM.  The word that is sorted is (key << 15 | index in the cloud); only the key bits take
+// part and cub's block sort is stable on the blocked arrangement (= index order), so the permutation is the one
+// the device-wide sort of (segment | key) produces and the index that comes out is bit-identical.
+constexpr int kCsThreads = 512, kCsItems = 40, kCsMaxPoints = kCsThreads * kCsItems, kCsIdxBits = 15;
+using CloudSort = cub::BlockRadixSort<unsigned, kCsThreads, kCsItems, cub::NullType, 5>;
+
+__global__ void __launch_bounds__(kCsThreads) cloud_sort_kernel(const float *__restrict__ xyz, long long stride,
+                                                                 const IndexView *__restrict__ views, int skip,
+                                                                 int key_bits, unsigned *__restrict__ sorted_rows) {
+    extern __shared__ __align__(16) unsigned char s_cs[];
+    CloudSort::TempStorage &temp = *reinterpret_cast<CloudSort::TempStorage *>(s_cs);
+    __shared__ float s_lo[kCsThreads / 32][3], s_hi[kCsThreads / 32][3];
+    __shared__ float s_bbox[4];
+    const IndexView &v = views[blockIdx.x];
+    const int n = (int)v.n;
+    const int t = threadIdx.x;
+    const float *base = xyz + v.src_off * stride;
+    // bounding box (the record bbox_kernel writes)
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = t; i < n; i += kCsThreads) {
+        const float *p = base + (long long)i * stride;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float x = p[a];
+            lo[a] = fminf(lo[a], x);
+            hi[a] = fmaxf(hi[a], x);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = warp_min(lo[a]);
+        hi[a] = warp_max(hi[a]);
+    }
+    if ((t & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { s_lo[t >> 5][a] = lo[a]; s_hi[t >> 5][a] = hi[a]; }
+    }
+    __syncthreads();
+    if (t == 0) {
+        float l[3], h[3];
+        for (int a = 0; a < 3; ++a) {
+            l[a] = s_lo[0][a]; h[a] = s_hi[0][a];
+            for (int w = 1; w < kCsThreads / 32; ++w) { l[a] = fminf(l[a], s_lo[w][a]); h[a] = fmaxf(h[a], s_hi[w][a]); }
+            if (n == 0) { l[a] = ordered_to_float(0xffffffffu); h[a] = ordered_to_float(0u); }   // (what bbox_kernel leaves)
+            else { l[a] = ordered_to_float(float_to_ordered(l[a])); h[a] = ordered_to_float(float_to_ordered(h[a])); }
+        }
+        const float ext = fmaxf(fmaxf(h[0] - l[0], h[1] - l[1]), h[2] - l[2]);
+        const float scale = (ext > 0.f && isfinite(ext)) ? 1024.f / (ext * 1.0001f) : 0.f;
+        float *bbox = const_cast<float *>(v.bbox);
+        bbox[0] = l[0]; bbox[1] = l[1]; bbox[2] = l[2]; bbox[3] = scale;
+        bbox[4] = h[0]; bbox[5] = h[1]; bbox[6] = h[2]; bbox[7] = ext;
+        s_bbox[0] = l[0]; s_bbox[1] = l[1]; s_bbox[2] = l[2]; s_bbox[3] = scale;
+    }
+    __syncthreads();
+    // keys, blocked arrangement: thread t holds points 40 t .. 40 t + 39 (pads: the largest word, they stay last)
+    unsigned key[kCsItems];
+#pragma unroll
+    for (int j = 0; j < kCsItems; ++j) {
+        const int i = t * kCsItems + j;
+        key[j] = 0xffffffffu;
+        if (i < n) {
+            const float *p = base + (long long)i * stride;
+            key[j] = ((morton30(p[0], p[1], p[2], s_bbox) >> skip) << kCsIdxBits) | (unsigned)i;
+        }
+    }
+    CloudSort(temp).SortBlockedToStriped(key, kCsIdxBits, kCsIdxBits + key_bits);
+    const unsigned off = (unsigned)v.src_off;
+#pragma unroll
+    for (int j = 0; j < kCsItems; ++j) {
+        const int r = j * kCsThreads + t;
+        if (r < n) sorted_rows[v.src_off + r] = off + (key[j] & ((1u << kCsIdxBits) - 1u));
+    }
+}
+
 __global__ void __launch_bounds__(256) node_box_kernel(const IndexView *__restrict__ views, int level) {
     const IndexView &v = views[blockIdx.y];
     if (level >= v.n_levels) return;
@@ -613,37 +691,52 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     PCP_TRY(b->vals_b.ensure(sizeof(unsigned) * (size_t)b->total_n));
     const IndexView *dv = b->d_views();
 
-    const unsigned bx = (unsigned)std::min<long long>(grid_for(b->max_n, 256),
-                                                      P == 1 ? (long long)ctx->sm_count * 2 : 16);
-    for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
-        const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
-        bbox_kernel<<<dim3(bx, gy), 256, 0, st>>>(d_xyz, stride, dv + p0);
+    static const bool no_cloud_sort = getenv("PCP_BUILD_CLOUD_SORT") && atoi(getenv("PCP_BUILD_CLOUD_SORT")) == 0;   // developer A/B
+    const bool cloud_sort = wide && !force64 && !no_cloud_sort && b->max_n <= kCsMaxPoints && mbits + kCsIdxBits <= 32;
+    if (cloud_sort) {
+        static bool attr = false;
+        if (!attr) {
+            PCP_CUDA(cudaFuncSetAttribute(cloud_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(CloudSort::TempStorage)));
+            attr = true;
+        }
+        cloud_sort_kernel<<<(unsigned)P, kCsThreads, sizeof(CloudSort::TempStorage), st>>>(d_xyz, stride, dv, 30 - mbits, mbits,
+                                                                                          b->vals_b.as<unsigned>());
         ctx->launches += 1;
-    }
-    if (b->ev_bbox_record) PCP_CUDA(cudaEventRecord(b->ev_bbox_record, st));   // query keys only need the boxes, not the sorted cloud
-    for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
-        const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
-        if (wide64)
-            key_kernel<unsigned long long><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
-                d_xyz, stride, dv + p0, p0, 30 - mbits, mbits, b->keys_a.as<unsigned long long>(), b->vals_a.as<unsigned>());
-        else
-            key_kernel<unsigned><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
-                d_xyz, stride, dv + p0, p0, wide ? 30 - mbits : 0, wide ? mbits : 0, b->keys_a.as<unsigned>(),
-                b->vals_a.as<unsigned>());
-        ctx->launches += 1;
-    }
-    if (wide64) {
-        PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
-                                                     b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
-                                                     b->vals_b.as<unsigned>(), b->total_n, 0, mbits + seg_bits));
-    } else if (wide) {
-        PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
-                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n, 0,
-                                           mbits + seg_bits));
+        if (b->ev_bbox_record) PCP_CUDA(cudaEventRecord(b->ev_bbox_record, st));
     } else {
-        PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
-                                           b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n,
-                                           30 - mbits, 30));
+        const unsigned bx = (unsigned)std::min<long long>(grid_for(b->max_n, 256),
+                                                          P == 1 ? (long long)ctx->sm_count * 2 : 16);
+        for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+            const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+            bbox_kernel<<<dim3(bx, gy), 256, 0, st>>>(d_xyz, stride, dv + p0);
+            ctx->launches += 1;
+        }
+        if (b->ev_bbox_record) PCP_CUDA(cudaEventRecord(b->ev_bbox_record, st));   // query keys only need the boxes, not the sorted cloud
+        for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+            const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+            if (wide64)
+                key_kernel<unsigned long long><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
+                    d_xyz, stride, dv + p0, p0, 30 - mbits, mbits, b->keys_a.as<unsigned long long>(), b->vals_a.as<unsigned>());
+            else
+                key_kernel<unsigned><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
+                    d_xyz, stride, dv + p0, p0, wide ? 30 - mbits : 0, wide ? mbits : 0, b->keys_a.as<unsigned>(),
+                    b->vals_a.as<unsigned>());
+            ctx->launches += 1;
+        }
+        if (wide64) {
+            PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
+                                                         b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
+                                                         b->vals_b.as<unsigned>(), b->total_n, 0, mbits + seg_bits));
+        } else if (wide) {
+            PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
+                                               b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n, 0,
+                                               mbits + seg_bits));
+        } else {
+            PCP_TRY(radix_sort_pairs<unsigned>(ctx, b->keys_a.as<unsigned>(), b->keys_b.as<unsigned>(),
+                                               b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), b->total_n,
+                                               30 - mbits, 30));
+        }
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);

@@ -216,7 +216,7 @@ icp_assoc_kernel(const IndexView *__restrict__ views, const float *__restrict__ 
 // Same structure as knn_tile_kernel (pcp_knn_tile.cu) with K = 1: the group walks the pair's TARGET hierarchy once,
 // buckets are staged in shared memory and every lane evaluates its own (transformed) point against the 32 staged
 // points in float32; survivors of the proven-margin filter are re-evaluated in float64 (nn1 semantics above).
-constexpr int kTileAssocWarps = 2;
+constexpr int kTileAssocWarps = 8;
 
 __device__ __forceinline__ float nn1_gate_fast(double best, float E) {
     // upper bound of best (1 + 2^-20) + 2 sqrt(best) E + E^2 in float, every step rounded up
@@ -435,13 +435,25 @@ icp_assoc_tile_kernel(const IndexView *__restrict__ tgt_views, const IndexView *
         acc[10] = ty * ax; acc[11] = ty * ay; acc[12] = ty * az;
         acc[13] = tz * ax; acc[14] = tz * ay; acc[15] = tz * az;
     }
-    // fixed-shape reductions: xor-shuffle tree inside the warp, warps in order inside the CTA -> deterministic
+    // fixed-shape reductions -> deterministic.  Inside the warp a halving butterfly: at distance 16 a lane keeps the
+    // 8 sums of its half and hands the other 8 over, at distance 8 it keeps 4, ... -- 16 double shuffles instead of
+    // the 80 of sixteen separate trees; sum i ends up in lanes 2 i and 2 i + 1.  Then the warps in order.
+    {
+        static_assert(kSums == 16, "butterfly below is written for 16 sums");
+        const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+        double v8[8], v4[4], v2[2], v1;
 #pragma unroll
-    for (int i = 0; i < kSums; ++i) {
-        double v = acc[i];
+        for (int i = 0; i < 8; ++i)
+            v8[i] = (b4 ? acc[8 + i] : acc[i]) + __shfl_xor_sync(kFullMask, b4 ? acc[i] : acc[8 + i], 16);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
-        if (lane == 0) s_sum[warp][i] = v;
+        for (int i = 0; i < 4; ++i)
+            v4[i] = (b3 ? v8[4 + i] : v8[i]) + __shfl_xor_sync(kFullMask, b3 ? v8[i] : v8[4 + i], 8);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+            v2[i] = (b2 ? v4[2 + i] : v4[i]) + __shfl_xor_sync(kFullMask, b2 ? v4[i] : v4[2 + i], 4);
+        v1 = (b1 ? v2[1] : v2[0]) + __shfl_xor_sync(kFullMask, b1 ? v2[0] : v2[1], 2);
+        v1 += __shfl_xor_sync(kFullMask, v1, 1);
+        if ((lane & 1) == 0) s_sum[warp][lane >> 1] = v1;
     }
     __syncthreads();
     if (threadIdx.x < kSums) {

@@ -189,8 +189,8 @@ int knn_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride,
                     int32_t *d_idx, float *d_dist, int32_t *d_count);
 int knn_tile_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count);
 int knn_warp_list_device(pcp_index *ix, bool self, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
-                         const uint32_t *d_list, const float *d_hints, uint32_t hint_groups, int k, int32_t *d_idx,
-                         float *d_dist, int32_t *d_count);
+                         const uint32_t *d_list, const uint32_t *d_sched, uint32_t n_groups, const float *d_hints,
+                         uint32_t hint_groups, int k, int32_t *d_idx, float *d_dist, int32_t *d_count, bool overlap);
 // 0 = choose by query count, 1 = warp-per-query kernel, 2 = tiled kernel (PCP_KNN_KERNEL=warp|tile, for tests)
 int knn_kernel_choice();
 // exact64: borderline pairs are decided in float64 (RadiusTest, pcp_device.cuh) -- scipy's semantics for ISS / DBSCAN

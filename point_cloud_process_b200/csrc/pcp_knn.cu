@@ -26,24 +26,56 @@ namespace {
 constexpr int kWarpsPerCta = 8;
 
 // LIST = false: warp w of the grid takes query w (SELF: sorted slot w).
-// LIST = true:  persistent warps drain the overflow list of the tiled kernel (pcp_knn_tile.cu): list[0] = number
-//               of groups, list[1..] = group ids; warp item w -> query lane (w % 32) of group list[1 + w / 32].
+// LIST = true:  persistent warps drain the overflow list of the tiled kernel (pcp_knn_tile.cu) WHILE that kernel may
+//               still be running (launched as its programmatic dependent): list[1 + e] = group id + 1 once entry e is
+//               published (0 before), sched[1] = groups the tiled kernel has finished (handed-over ones included).
+//               Warp item w -> query lane (w % 32) of entry w / 32; a warp waits for its entry until it appears or
+//               until all n_groups groups are accounted for without it.
 template <bool SELF, bool LIST>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long nq, long long stride, int k,
                 int *__restrict__ out_idx, float *__restrict__ out_dist, int *__restrict__ out_cnt,
-                unsigned long long *__restrict__ ctr, const unsigned *__restrict__ list,
-                const unsigned *__restrict__ perm, const float *__restrict__ hints, unsigned hint_groups) {
+                unsigned long long *__restrict__ ctr, const unsigned *list, const unsigned *sched, unsigned n_groups,
+                const unsigned *__restrict__ perm, const float *hints, unsigned hint_groups) {
     // per-level traversal state: lane j keeps the pending lower bound of child j of the open node
     __shared__ unsigned s_lb[kWarpsPerCta][kMaxLevels][32];
     __shared__ unsigned s_cd[kWarpsPerCta][kMaxLevels][32];   // squared distance to the child's box centre
     __shared__ unsigned s_node[kWarpsPerCta][kMaxLevels];
+    __shared__ unsigned s_entry;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long long n_work = LIST ? (long long)list[0] * 32 : (SELF ? ix.n_leaf * kLeaf : nq);
+    const long long n_work = LIST ? (long long)n_groups * 32 : (SELF ? ix.n_leaf * kLeaf : nq);
     for (long long item = blockIdx.x * (long long)kWarpsPerCta + warp; item < n_work;
          item += LIST ? gridDim.x * (long long)kWarpsPerCta : n_work) {
     long long wid = item;
-    if (LIST) wid = (long long)list[1 + (item >> 5)] * 32 + (item & 31);    // slot (SELF) / sorted position
+    if (LIST) {
+        // the 8 items of a CTA belong to one entry: ONE thread polls for it (thousands of warps polling the words
+        // the tiled kernel's scheduler lives on would starve that kernel's own atomics), the others wait at the barrier
+        __syncthreads();                         // (everyone has read s_entry of the previous round)
+        if (threadIdx.x == 0) {
+            const unsigned *entry = list + 1 + (item >> 5);
+            unsigned g1 = 0, spins = 0;
+            for (;;) {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(g1) : "l"(entry) : "memory");
+                if (g1) break;
+                if ((spins++ & 3u) == 0u) {
+                    unsigned done;
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(done) : "l"(sched + 1) : "memory");
+                    if (done >= n_groups) {      // every publication precedes its group's count: look once more
+                        __threadfence();
+                        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(g1) : "l"(entry) : "memory");
+                        break;
+                    }
+                }
+                __nanosleep(2000);
+            }
+            __threadfence();                     // acquire: the entry's gates are read below
+            s_entry = g1;
+        }
+        __syncthreads();
+        const unsigned g1 = s_entry;
+        if (!g1) break;                          // no such entry (whole CTA): neither will any later one exist
+        wid = (long long)(g1 - 1u) * 32 + (item & 31);                       // slot (SELF) / sorted position
+    }
     warpq::QueryState st;
     long long qid = wid;
     if (SELF) {
@@ -61,7 +93,7 @@ knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long
     }
     // LIST: the gate the tiled kernel had reached for this query when it gave the group up (first hint_groups entries)
     float gate0 = __int_as_float(0x7f800000);
-    if (LIST && (item >> 5) < (long long)hint_groups) gate0 = hints[item];
+    if (LIST && (item >> 5) < (long long)hint_groups) gate0 = __ldcg(hints + item);
     warpq::search(ix, st, lane, k, s_lb[warp], s_cd[warp], s_node[warp], gate0);
 
     if (ctr && lane == 0) {
@@ -89,6 +121,8 @@ knn_warp_kernel(const IndexView ix, const float *__restrict__ queries, long long
     }
     __syncwarp();
     }
+    // completion of this grid must imply completion of the tiled kernel (whose last groups may still be writing results)
+    if (LIST) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, int *cnt) {
@@ -99,21 +133,35 @@ __global__ void fill_empty_kernel(long long nq, int k, int *idx, float *dist, in
 
 }  // namespace
 
-// Overflow groups of the tiled kernel, one warp per query, persistent grid.
+// Overflow groups of the tiled kernel, one warp per query, persistent grid.  overlap: launched with programmatic
+// stream serialisation -- the grid may start once every CTA of the tiled kernel in front of it on the stream has
+// executed griddepcontrol.launch_dependents (all of them are resident by then, so this grid can only take what
+// they leave or free) and consumes the list as it is published.  PCP_KNN_OVERLAP=0 keeps the two kernels serial.
 int knn_warp_list_device(pcp_index *ix, bool self, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm,
-                         const uint32_t *d_list, const float *d_hints, uint32_t hint_groups, int k, int32_t *d_idx,
-                         float *d_dist, int32_t *d_count) {
+                         const uint32_t *d_list, const uint32_t *d_sched, uint32_t n_groups, const float *d_hints,
+                         uint32_t hint_groups, int k, int32_t *d_idx, float *d_dist, int32_t *d_count, bool overlap) {
     pcp_ctx *ctx = ix->ctx;
     const IndexView v = make_view(ix);
-    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    static const bool allow = !(getenv("PCP_KNN_OVERLAP") && atoi(getenv("PCP_KNN_OVERLAP")) == 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)ctx->sm_count * 8);
+    cfg.blockDim = dim3(kWarpsPerCta * 32);
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap && allow ? 1 : 0;
+    unsigned long long *ctr = ctx->ctr();
+    const long long n = self ? ix->n : nq, st = self ? 3 : stride;
+    const float *q = self ? nullptr : d_q;
+    const unsigned *perm = self ? nullptr : d_perm;
     if (self)
-        knn_warp_kernel<true, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
-                                                                                d_count, ctx->ctr(), d_list, nullptr, d_hints,
-                                                                                hint_groups);
+        PCP_CUDA(cudaLaunchKernelEx(&cfg, knn_warp_kernel<true, true>, v, q, n, st, k, d_idx, d_dist, d_count, ctr,
+                                    (const unsigned *)d_list, (const unsigned *)d_sched, n_groups, perm, d_hints, hint_groups));
     else
-        knn_warp_kernel<false, true><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
-                                                                                 d_count, ctx->ctr(), d_list, d_perm, d_hints,
-                                                                                 hint_groups);
+        PCP_CUDA(cudaLaunchKernelEx(&cfg, knn_warp_kernel<false, true>, v, q, n, st, k, d_idx, d_dist, d_count, ctr,
+                                    (const unsigned *)d_list, (const unsigned *)d_sched, n_groups, perm, d_hints, hint_groups));
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
@@ -177,7 +225,7 @@ int knn_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, cons
     const IndexView v = make_view(ix);
     const unsigned grid = (unsigned)((nq + kWarpsPerCta - 1) / kWarpsPerCta);
     knn_warp_kernel<false, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, d_q, nq, stride, k, d_idx, d_dist,
-                                                                               d_count, ctx->ctr(), nullptr, nullptr, nullptr, 0u);
+                                                                               d_count, ctx->ctr(), nullptr, nullptr, 0u, nullptr, nullptr, 0u);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;
@@ -192,7 +240,7 @@ int knn_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t
     const long long n_work = v.n_leaf * kLeaf;
     const unsigned grid = (unsigned)((n_work + kWarpsPerCta - 1) / kWarpsPerCta);
     knn_warp_kernel<true, false><<<grid, kWarpsPerCta * 32, 0, ctx->stream>>>(v, nullptr, ix->n, 3, k, d_idx, d_dist,
-                                                                              d_count, ctx->ctr(), nullptr, nullptr, nullptr, 0u);
+                                                                              d_count, ctx->ctr(), nullptr, nullptr, 0u, nullptr, nullptr, 0u);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());
     return PCP_OK;

@@ -37,10 +37,6 @@
 
 namespace pcp {
 
-int knn_tile_device_v1(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
-                       int32_t *d_idx, float *d_dist, int32_t *d_count);
-int knn_tile_self_device_v1(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count);
-
 namespace {
 
 constexpr unsigned kDone = 0xffffffffu;
@@ -165,6 +161,10 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
 #define NODE_A(lv) (wb + kNodeOff + (unsigned)(lv) * 4u)
 #define LBS_A(lv, j) (wb + kLbsOff + (unsigned)(lv) * 128u + (unsigned)(j) * 4u)
     const float inf = __uint_as_float(kInfBits);
+    // The overflow kernel is launched as a PROGRAMMATIC DEPENDENT of this grid (knn_warp_list_device): it may start
+    // as soon as every CTA of this grid has passed this point -- i.e. is resident, the grid being one wave -- and
+    // then takes whatever the finishing CTAs free, draining the overflow list while the stragglers still run.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     // Persistent warps: groups are handed out dynamically (sched[0]); sched[1] counts finished groups.  Tail
     // hand-over (tail_slots != 0): once the queue is dry and fewer than tail_slots groups are still in flight, the
@@ -534,14 +534,18 @@ knn_tile_kernel(const IndexView ix, const float *__restrict__ queries, const uns
         // work budget exceeded (a sparse group whose box is much larger than its neighbourhoods) or a mass of
         // tied distances: hand the group's queries to the warp-per-query kernel, which re-does them in parallel
         unsigned pos = 0;
-        if (lane == 0) {
-            pos = atomicAdd(overflow, 1u);
-            overflow[1 + pos] = group;
-            atomicAdd(sched + 1, 1u);
-        }
+        if (lane == 0) pos = atomicAdd(overflow, 1u);
         // the gates reached so far seed the searches of the warp-per-query kernel
         pos = __shfl_sync(kFullMask, pos, 0);
         if (pos < hint_groups) hints[(size_t)pos * 32 + lane] = active ? gate : inf;
+        // publish: the consumer may be running already (it polls the entry, then the finished count)
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+            atomicExch(overflow + 1 + pos, group + 1u);
+            __threadfence();
+            atomicAdd(sched + 1, 1u);
+        }
         if (ctr && lane == 0) {
             atomicAdd(ctr + 0, (unsigned long long)n_half * (kLeaf / 2) * n_active);
             atomicAdd(ctr + 6, 1ull);
@@ -609,7 +613,7 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     const IndexView v = make_view(ix);
     const long long n_groups = SELF ? v.n_leaf : (nq + 31) / 32;
     unsigned long long *ctr = ctx->ctr();
-    // overflow list: [0] = count, [1..] = group ids
+    // overflow list: [0] = count, [1..] = group ids + 1
     // behind the list, 8-byte aligned: next group of the persistent tile warps, number of finished groups
     // and the gates of the first kHintGroups overflow groups (32 floats each)
     const long long sched_at = (n_groups + 2) & ~1LL, hints_at = (sched_at + 2 + 31) & ~31LL;
@@ -617,8 +621,8 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
     PCP_TRY(ctx->scratch[5].ensure(sizeof(unsigned) * (size_t)(hints_at + 32LL * hint_groups)));
     unsigned *overflow = ctx->scratch[5].as<unsigned>();
     float *hints = reinterpret_cast<float *>(overflow + hints_at);
-    PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned), ctx->stream));
-    PCP_CUDA(cudaMemsetAsync(overflow + sched_at, 0, 2 * sizeof(unsigned), ctx->stream));
+    // count, entries (0 = not published yet; group + 1 otherwise) and the two scheduler words in one clear
+    PCP_CUDA(cudaMemsetAsync(overflow, 0, sizeof(unsigned) * (size_t)(sched_at + 2), ctx->stream));
     const int K = k <= 2 ? k : k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32;
     const bool small_grid = n_groups < 2LL * ctx->sm_count * 32;
     static const char *e_scans = getenv("PCP_TILE_MAX_SCANS"), *e_tests = getenv("PCP_TILE_MAX_TESTS"),
@@ -688,25 +692,20 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
         if (FILE *f = fopen(dump, "wb")) { fwrite(h.data(), sizeof(unsigned), h.size(), f); fclose(f); }
     }
-    // groups that ran out of budget: one warp per query, persistent grid sized by the device-side count
-    return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, hints, hint_groups, k, d_idx, d_dist, d_count);
-}
-
-bool use_v1() {
-    static const bool v1 = getenv("PCP_TILE_V1") != nullptr;   // developer A/B switch: the round-1 kernel
-    return v1;
+    // groups that ran out of budget or were handed over in the tail: one warp per query, persistent grid that runs
+    // BESIDE the tail of the tiled kernel (not when its launches are being timed: the event sits in between)
+    return knn_warp_list_device(ix, SELF, d_q, nq, stride, d_perm, overflow, overflow + sched_at, (uint32_t)n_groups, hints,
+                                hint_groups, k, d_idx, d_dist, d_count, /*overlap=*/ev_end == nullptr && !dump);
 }
 
 }  // namespace
 
 int knn_tile_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride, const uint32_t *d_perm, int k,
                     int32_t *d_idx, float *d_dist, int32_t *d_count) {
-    if (use_v1()) return knn_tile_device_v1(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_count);
     return launch_tile<false>(ix, d_q, d_perm, nq, stride, k, d_idx, d_dist, d_count);
 }
 
 int knn_tile_self_device(pcp_index *ix, int k, int32_t *d_idx, float *d_dist, int32_t *d_count) {
-    if (use_v1()) return knn_tile_self_device_v1(ix, k, d_idx, d_dist, d_count);
     return launch_tile<true>(ix, nullptr, nullptr, ix->n, 3, k, d_idx, d_dist, d_count);
 }
 
