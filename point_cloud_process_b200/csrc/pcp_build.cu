@@ -591,6 +591,31 @@ inline unsigned grid_for(long long n, int block) { return static_cast<unsigned>(
 
 }  // namespace
 
+namespace {
+__global__ void small_copy_kernel(unsigned *__restrict__ dst, const unsigned *__restrict__ src, size_t words) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < words) dst[i] = src[i];
+}
+}  // namespace
+
+int small_h2d(pcp_ctx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return PCP_OK;
+    const size_t at = (ctx->small_used + 15) & ~(size_t)15;
+    if (!ctx->h2d_by_kernel || (bytes & 3) || at + bytes > ctx->small_stage.cap) {
+        PCP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+        return PCP_OK;
+    }
+    unsigned char *stage = static_cast<unsigned char *>(ctx->small_stage.p) + at;
+    memcpy(stage, src, bytes);
+    ctx->small_used = at + bytes;
+    const size_t words = bytes / 4;
+    small_copy_kernel<<<(unsigned)((words + 255) / 256), 256, 0, st>>>(static_cast<unsigned *>(dst),
+                                                                      reinterpret_cast<const unsigned *>(stage), words);
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
 void BatchIndex::release() {
     if (ev_bbox) { cudaEventDestroy(ev_bbox); ev_bbox = nullptr; }
     for (DevBuf *d : {&pts, &pts2, &box_lo, &box_hi, &half, &bbox, &views, &keys_a, &keys_b, &vals_a, &vals_b}) d->release();
@@ -667,7 +692,7 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
         v.bbox = b->bbox.as<float>() + p * kBboxWords;
     }
     // views are small (184 B per segment): pageable copy, staged by the driver before it returns
-    PCP_CUDA(cudaMemcpyAsync(b->views.p, b->h_views.data(), sizeof(IndexView) * (size_t)P, cudaMemcpyHostToDevice, st));
+    PCP_TRY(small_h2d(ctx, b->views.p, b->h_views.data(), sizeof(IndexView) * (size_t)P, st));
     if (b->total_n == 0) return PCP_OK;
 
     // Key layout.  Batch: segment id above the significant Morton bits -- per cloud one bit fewer than

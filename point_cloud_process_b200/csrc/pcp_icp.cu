@@ -734,10 +734,10 @@ int icp_batch_device(pcp_ctx *ctx, const pcp_icp_params &prm, int64_t P, const f
         d_log = b_log.as<double>();
         PCP_CUDA(cudaMemsetAsync(d_log, 0xff, sizeof(double) * 2 * (size_t)P * (size_t)max_it, st));   // NaN fill
     }
-    PCP_CUDA(cudaMemcpyAsync(b_states.p, h_states.data(), sizeof(IcpState) * (size_t)P, cudaMemcpyHostToDevice, st));
-    PCP_CUDA(cudaMemcpyAsync(b_off.p, h_src_off, sizeof(long long) * (size_t)(P + 1), cudaMemcpyHostToDevice, st));
+    PCP_TRY(small_h2d(ctx, b_states.p, h_states.data(), sizeof(IcpState) * (size_t)P, st));
+    PCP_TRY(small_h2d(ctx, b_off.p, h_src_off, sizeof(long long) * (size_t)(P + 1), st));
     int h_active = max_it > 0 ? (int)P : 0;
-    PCP_CUDA(cudaMemcpyAsync(b_act.p, &h_active, sizeof(int), cudaMemcpyHostToDevice, st));
+    PCP_TRY(small_h2d(ctx, b_act.p, &h_active, sizeof(int), st));
 
     // No host round trip inside an iteration, and none between the iterations of a block: blocks of 4, 8, 16, ...
     // iterations are enqueued back to back (a pair that has stopped makes its CTAs return at once, so the

@@ -104,6 +104,13 @@ struct BatchIndex {
     void release();
 };
 
+// Host -> device copy of a small host structure, ordered on st.  Normally a cudaMemcpyAsync from pageable memory.
+// While pcp_icp_batch(PCP_HOST) streams the next run of clouds over the copy engine (ctx->h2d_by_kernel) such a copy
+// would queue behind hundreds of MB on that engine and stall the kernels after it: the bytes are then placed in a
+// page-locked ring (ctx->small_stage; the caller sizes it and resets small_used between synchronised calls) and a
+// kernel fetches them over PCIe itself.  bytes must be a multiple of 4.
+int small_h2d(pcp_ctx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st);
+
 // Build over rows [offsets[p], offsets[p+1]) of d_xyz for p < P (offsets: P+1 host values).
 int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_t P, const int64_t *h_offsets);
 
@@ -127,6 +134,11 @@ struct pcp_ctx {
     int64_t launches = 0;
     // last pcp_icp_batch: kernels launched in its iteration loop, host synchronisations, iterations enqueued
     int64_t icp_last_launches = 0, icp_last_syncs = 0, icp_last_enqueued = 0;
+    pcp::DevBuf icp_up[4];                // pcp_icp_batch(PCP_HOST): two staging sets {targets, sources}
+    cudaEvent_t ev_icp_up[4] = {nullptr, nullptr, nullptr, nullptr};
+    pcp::PinBuf small_stage;              // small_h2d(): page-locked ring the copy kernel reads from
+    size_t small_used = 0;
+    bool h2d_by_kernel = false;           // a large upload occupies the copy engine: small structures go by kernel
     pcp::DevBuf cub_tmp;           // CUB temporary storage
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
     pcp::PinBuf pin[4];            // pinned staging for host<->device copies

@@ -230,3 +230,37 @@ def test_c4_64_pairs_of_20000_points_vs_oracle(pcp, mode):
         assert max(a1, a2) <= 1e-4 and max(t1, t2) <= 1e-4, (i, a1, t1, a2, t2)
     if mode == "A":
         assert set(np.unique(out["iterations"]).tolist()) <= {1, 2}      # 1 iteration on ~80 %, 2 on the rest
+
+
+def test_icp_batch_pinned_host_pipeline_same_results(pcp, monkeypatch):
+    """pcp_icp_batch(PCP_HOST) with page-locked clouds copies and registers the batch in runs of pairs (copy of run
+    c + 1 beside the registration of run c): same iterations, poses and log (1e-9) as the single-shot pageable path.
+    Ragged batch, large enough for several runs (kIcpChunkPoints = 12 Mi points)."""
+    import torch
+    from oracle import icp_oracle
+    native = pcp.native
+    rng = np.random.default_rng(5)
+    sizes = [int(s) for s in rng.integers(150_000, 420_000, 48)] + [0, 17]
+    srcs, tgts = [], []
+    for i, n in enumerate(sizes):
+        if n == 0:
+            srcs.append(np.zeros((0, 3), np.float32)), tgts.append(np.zeros((0, 3), np.float32))
+            continue
+        tgt, src, _ = icp_oracle.make_pair(4000 + i, n=n, box=(60.0, 60.0, 8.0))
+        srcs.append(src), tgts.append(tgt)
+    so = np.concatenate([[0], np.cumsum([len(s) for s in srcs])]).astype(np.int64)
+    to = np.concatenate([[0], np.cumsum([len(t) for t in tgts])]).astype(np.int64)
+    assert so[-1] + to[-1] > 2 * (12 << 20)                       # at least three runs
+    sp, tp = np.concatenate(srcs), np.concatenate(tgts)
+    T0 = np.tile(np.eye(4), (len(srcs), 1, 1))
+    ctx = native.Context(0)
+    args = (T0, 30, 1e-5, 1e-5, 5.0, True, True)
+    ref = native.icp_batch(ctx, sp, so, tp, to, *args)            # pageable: one shot
+    pin_s, pin_t = torch.from_numpy(sp).pin_memory().numpy(), torch.from_numpy(tp).pin_memory().numpy()
+    got = native.icp_batch(ctx, pin_s, so, pin_t, to, *args)      # page-locked: pipelined
+    for key in ("iterations", "status"):
+        assert np.array_equal(ref[key], got[key]), key
+    # (the Morton key width of a build follows its largest cloud, so a run may bucket a cloud differently from the
+    # whole batch: float64 sums in another order)
+    for key in ("T_last", "T_total", "diff_log"):
+        assert np.allclose(np.asarray(ref[key]), np.asarray(got[key]), rtol=0, atol=1e-9, equal_nan=True), key
