@@ -340,8 +340,8 @@ def measure_knn(torch, pcp, ctx, stream, w, args, dist, rank, world, local_rank,
         "bound": "fp32", "kernel": "knn_tile_kernel", "achieved": achieved, "peak": fp32_peak,
         "unit": "TFLOP/s (unfused FP32 ops; 8 per distance evaluation: 3 sub + 3 mul + 2 add, issued as 3 FADD2 + 3 FMUL2 + 4 FADD per pair of evaluations)",
         "frac": achieved / fp32_peak, "frac_fma2_convention": achieved / fp32_peak / 2.0,
-        "traffic": None,
-        "traffic_note": "not measured inside this run (needs ncu); the ncu --set full capture of this kernel is summarised under profiles/ (dram__bytes_read + write per launch: r2_ncu_knn_tile_kitti_k8.txt)",
+        "traffic": ncu_traffic_bytes(args.workload),
+        "traffic_note": "bytes per launch, dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture of this kernel on this workload (profiles/r2_ncu_knn_tile_*.txt); not re-measured inside this run (needs ncu); null when there is no capture for the workload",
         "peak_source": f"{sm_count} SMs x 128 FP32 lanes x sm_max_mhz ({peaks_kind} MEASURED_PEAKS.json clock); no FP32 peak is measured by the driver",
         "distance_evaluations_per_launch": evals, "evals_per_query": evals / n,
         "kernel_ms": tile_s * 1e3, "kernel_launches_timed": int(tile_launches),
@@ -573,7 +573,7 @@ def run_reference(args):
                              "sample": f"{n_pairs} pairs per step on a pool of {threads} processes; float64 numpy + cKDTree restatement of "
                                        f"main.py:97-156 (the reference needs Open3D: absent); iterations {sorted(set(its_all))}"},
             "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-        print(json.dumps(line))
+        emit_line(line)
         return
     w = make_workload(args.workload, 0)
     pts, k = w["pts"], w["k"]
@@ -599,12 +599,48 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_line(line)
 
 
 # ---------------------------------------------------------------------------------------------- main
 
+def ncu_traffic_bytes(workload):
+    """DRAM bytes per launch of the tiled kNN kernel from the committed ncu capture of that workload (MB in the file)."""
+    name = {"kitti_knn8": "r2_ncu_knn_tile_kitti_k8.txt"}.get(workload)
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", name) if name else None
+    if not path or not os.path.exists(path):
+        return None
+    total = 0.0
+    for line in open(path):
+        if line.startswith("dram__bytes_read.sum") or line.startswith("dram__bytes_write.sum"):
+            total += float(line.split("=")[1])
+    return int(total * 1e6)
+
+
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """Libraries below us (NCCL prints its version banner on stdout) must not add lines to the one-JSON-line contract:
+    everything written to fd 1 from here on goes to stderr, the JSON line goes to the saved descriptor."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_STDOUT_FD, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
@@ -748,7 +784,7 @@ def main():
         if "cpu_baseline" in icp:
             line["cpu_baseline"] = icp["cpu_baseline"]
     if rank == 0:
-        print(json.dumps(line))
+        emit_line(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
