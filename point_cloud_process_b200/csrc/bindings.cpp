@@ -45,6 +45,30 @@ py::array_t<T> result_array(std::vector<py::ssize_t> shape) {
     return py::array_t<T>(shape, static_cast<T *>(p), owner);
 }
 
+// The three result arrays of a kNN call as views of ONE page-locked slab (idx | dist | count): the library then
+// brings them back with a single device -> host copy.
+struct KnnResult {
+    py::array_t<int32_t> idx, cnt;
+    py::array_t<float> dist;
+    KnnResult(int64_t n, int k) {
+        const size_t nres = (size_t)n * (size_t)k, bytes = nres * 8 + (size_t)n * 4;
+        if (bytes < (64u << 10)) {
+            idx = py::array_t<int32_t>({(py::ssize_t)n, (py::ssize_t)k});
+            dist = py::array_t<float>({(py::ssize_t)n, (py::ssize_t)k});
+            cnt = py::array_t<int32_t>((py::ssize_t)n);
+            return;
+        }
+        void *p = nullptr;
+        check(pcp_host_alloc(bytes, &p), "pcp_host_alloc");
+        py::capsule owner(p, [](void *q) { pcp_host_free(q); });
+        char *c = static_cast<char *>(p);
+        idx = py::array_t<int32_t>({(py::ssize_t)n, (py::ssize_t)k}, reinterpret_cast<int32_t *>(c), owner);
+        dist = py::array_t<float>({(py::ssize_t)n, (py::ssize_t)k}, reinterpret_cast<float *>(c + nres * 4), owner);
+        cnt = py::array_t<int32_t>({(py::ssize_t)n}, reinterpret_cast<int32_t *>(c + nres * 8), owner);
+    }
+    py::tuple tuple() const { return py::make_tuple(idx, dist, cnt); }
+};
+
 // rows x cols float32 view; the reference's clouds are (N, 3) (benchmark.py:19); (N, >=3) rows with
 // extra columns (KITTI intensity, Oxford normals) are accepted and only x,y,z are read.
 struct Cloud {
@@ -170,16 +194,14 @@ class Index {
     py::tuple knn(const py::object &queries, int k) {
         Cloud q(queries, "queries");
         if (k < 1) throw py::value_error("k must be >= 1");
-        auto idx = result_array<int32_t>({(py::ssize_t)q.n, (py::ssize_t)k});
-        auto dist = result_array<float>({(py::ssize_t)q.n, (py::ssize_t)k});
-        auto cnt = result_array<int32_t>({(py::ssize_t)q.n});
+        KnnResult r(q.n, k);
         {
             py::gil_scoped_release rel;
-            check_nogil(pcp_knn(ix_, q.data(), q.n, q.stride, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(),
-                                cnt.mutable_data()), "pcp_knn");
+            check_nogil(pcp_knn(ix_, q.data(), q.n, q.stride, k, PCP_HOST, r.idx.mutable_data(), r.dist.mutable_data(),
+                                r.cnt.mutable_data()), "pcp_knn");
         }
         rethrow();
-        return py::make_tuple(idx, dist, cnt);
+        return r.tuple();
     }
     // exhaustive kernel (kdtree.py:234-238 as a device kernel): the exhaustive cross-check
     py::tuple knn_bruteforce(const py::object &queries, int k) {
@@ -215,16 +237,14 @@ class Index {
     py::tuple knn_self(int k) {
         if (k < 1) throw py::value_error("k must be >= 1");
         const int64_t n = size();
-        auto idx = result_array<int32_t>({(py::ssize_t)n, (py::ssize_t)k});
-        auto dist = result_array<float>({(py::ssize_t)n, (py::ssize_t)k});
-        auto cnt = result_array<int32_t>({(py::ssize_t)n});
+        KnnResult r(n, k);
         {
             py::gil_scoped_release rel;
-            check_nogil(pcp_knn_self(ix_, k, PCP_HOST, idx.mutable_data(), dist.mutable_data(), cnt.mutable_data()),
+            check_nogil(pcp_knn_self(ix_, k, PCP_HOST, r.idx.mutable_data(), r.dist.mutable_data(), r.cnt.mutable_data()),
                         "pcp_knn_self");
         }
         rethrow();
-        return py::make_tuple(idx, dist, cnt);
+        return r.tuple();
     }
     // normals by k-NN PCA (pca_normal.py:85-90): (normals (N,3) f64, eigenvalues (N,3) f64 descending)
     py::tuple normals(int k) {

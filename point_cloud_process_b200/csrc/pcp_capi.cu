@@ -142,6 +142,20 @@ int download(pcp_ctx *ctx, void *dst, const void *src, size_t bytes) {
     return PCP_OK;
 }
 
+// kNN results device slab (idx | dist | count, contiguous) -> host.  One copy when the caller's three arrays are laid
+// out the same way (the pybind11 layer allocates them as one page-locked slab): every separate copy costs ~10 us of
+// fixed latency on top of its bytes.
+int download_knn(pcp_ctx *ctx, int32_t *idx, float *dist, int32_t *count, const int32_t *d_idx, size_t nres, size_t nq) {
+    const char *d = reinterpret_cast<const char *>(d_idx);
+    const bool slab = reinterpret_cast<char *>(dist) == reinterpret_cast<char *>(idx) + nres * 4 &&
+                      (!count || reinterpret_cast<char *>(count) == reinterpret_cast<char *>(dist) + nres * 4);
+    if (slab) return download(ctx, idx, d, nres * 8 + (count ? nq * 4 : 0));
+    PCP_TRY(download(ctx, idx, d, nres * 4));
+    PCP_TRY(download(ctx, dist, d + nres * 4, nres * 4));
+    if (count) PCP_TRY(download(ctx, count, d + nres * 8, nq * 4));
+    return PCP_OK;
+}
+
 bool bad_mem(int mem) { return mem != PCP_HOST && mem != PCP_DEVICE; }
 
 }  // namespace
@@ -496,13 +510,10 @@ int pcp_knn(pcp_index *ix, const float *queries, int64_t nq, int64_t stride, int
         d_dist = reinterpret_cast<float *>(d_idx + nres);
         d_cnt = reinterpret_cast<int32_t *>(d_dist + nres);
     }
-    // one warp per query: queries are independent, no reordering pass is needed
     const uint32_t *d_perm = nullptr;
     PCP_TRY(knn_device(ix, d_q, nq, stride, d_perm, k, d_idx, d_dist, d_cnt, side_ok));
     if (mem == PCP_HOST) {
-        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
-        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
-        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_TRY(download_knn(ctx, idx, dist, count, d_idx, nres, (size_t)nq));
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
     }
     return PCP_OK;
@@ -531,9 +542,7 @@ int pcp_knn_bruteforce(pcp_index *ix, const float *queries, int64_t nq, int64_t 
     }
     PCP_TRY(knn_brute_device(ix, d_q, nq, stride, k, d_idx, d_dist, d_cnt));
     if (mem == PCP_HOST) {
-        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
-        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
-        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_TRY(download_knn(ctx, idx, dist, count, d_idx, nres, (size_t)nq));
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
     }
     return PCP_OK;
@@ -584,9 +593,7 @@ int pcp_knn_self(pcp_index *ix, int k, int mem, int32_t *idx, float *dist, int32
     }
     PCP_TRY(knn_self_device(ix, k, d_idx, d_dist, d_cnt));
     if (mem == PCP_HOST) {
-        PCP_TRY(download(ctx, idx, d_idx, nres * 4));
-        PCP_TRY(download(ctx, dist, d_dist, nres * 4));
-        if (count) PCP_TRY(download(ctx, count, d_cnt, sizeof(int32_t) * (size_t)nq));
+        PCP_TRY(download_knn(ctx, idx, dist, count, d_idx, nres, (size_t)nq));
         PCP_CUDA(cudaStreamSynchronize(ctx->stream));
     }
     return PCP_OK;
