@@ -177,7 +177,8 @@ int knn_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride
     const size_t smem = 2 * kTileBytes + 16;
 #define PCP_BRUTE(KK)                                                                                                  \
     do {                                                                                                               \
-        static bool attr = false;                                                                                      \
+        static bool attr_dev[kMaxDevices] = {false};   /* function attributes are per device */                          \
+        bool &attr = attr_dev[ctx->device & (kMaxDevices - 1)];                                                          \
         if (!attr) {                                                                                                   \
             PCP_CUDA(cudaFuncSetAttribute(brute_kernel<KK, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
             attr = true;                                                                                               \
@@ -201,7 +202,8 @@ int radius_count_brute_device(pcp_index *ix, const float *d_q, int64_t nq, int64
     const long long n_slots = ix->n > 0 ? v.n_leaf * kLeaf : 0;
     const unsigned grid = (unsigned)((nq + kBruteThreads - 1) / kBruteThreads);
     const size_t smem = 2 * kTileBytes + 16;
-    static bool attr = false;
+    static bool attr_dev[kMaxDevices] = {false};
+    bool &attr = attr_dev[ctx->device & (kMaxDevices - 1)];
     if (!attr) {
         PCP_CUDA(cudaFuncSetAttribute(brute_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;

@@ -719,7 +719,8 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     static const bool no_cloud_sort = getenv("PCP_BUILD_CLOUD_SORT") && atoi(getenv("PCP_BUILD_CLOUD_SORT")) == 0;   // developer A/B
     const bool cloud_sort = wide && !force64 && !no_cloud_sort && b->max_n <= kCsMaxPoints && mbits + kCsIdxBits <= 32;
     if (cloud_sort) {
-        static bool attr = false;
+        static bool attr_dev[kMaxDevices] = {false};   // function attributes are per device
+        bool &attr = attr_dev[ctx->device & (kMaxDevices - 1)];
         if (!attr) {
             PCP_CUDA(cudaFuncSetAttribute(cloud_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(CloudSort::TempStorage)));

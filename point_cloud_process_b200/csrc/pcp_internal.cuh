@@ -54,6 +54,7 @@ struct PinBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+constexpr int kMaxDevices = 64;    // per-device caches of function attributes / occupancy (power of two)
 constexpr int kLeaf = 32;          // points per bucket == warp width
 constexpr int kFan = 32;           // children per hierarchy node == warp width
 constexpr int kMaxLevels = 8;      // 32^7 buckets > 2^31 points

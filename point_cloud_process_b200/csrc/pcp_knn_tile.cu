@@ -642,10 +642,11 @@ int launch_tile(pcp_index *ix, const float *d_q, const unsigned *d_perm, long lo
         const int n_up = v.n_levels > 2 ? v.n_levels - 2 : 0;                                                          \
         const size_t wbytes = tile_warp_bytes(CAP, n_up);                                                              \
         const size_t smem = (size_t)W * wbytes;                                                                        \
-        static int occ_by_levels[kMaxLevels + 1] = {0};   /* resident CTAs per SM, per tree depth */                   \
-        int &ctas_per_sm = occ_by_levels[n_up];                                                                        \
+        static int occ_by_levels[kMaxDevices][kMaxLevels + 1] = {{0}};   /* resident CTAs per SM, per device and tree depth */ \
+        int &ctas_per_sm = occ_by_levels[ctx->device & (kMaxDevices - 1)][n_up];                                       \
         if (!ctas_per_sm) {                                                                                            \
-            static size_t attr_smem = 0;                                                                               \
+            static size_t attr_smem_dev[kMaxDevices] = {0};                                                            \
+            size_t &attr_smem = attr_smem_dev[ctx->device & (kMaxDevices - 1)];                                        \
             if (smem > attr_smem) {                                                                                    \
                 PCP_CUDA(cudaFuncSetAttribute(knn_tile_kernel<KK, SELF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
                 attr_smem = smem;                                                                                      \

@@ -463,3 +463,30 @@ def test_cuda_graph_of_build_and_knn(pcp, kitti):
     step()
     ctx.synchronize()
     assert torch.equal(idx, want[-1][0])
+
+
+def test_two_devices_in_one_process(kitti):
+    """Contexts on two GPUs of one process: kernels that opt into > 48 KB of dynamic shared memory (tiled kNN,
+    brute force, per-cloud sort of the ICP builds) must set their attributes on EVERY device, not once per process."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 visible GPUs")
+    import point_cloud_process_b200 as pcp
+    native = pcp.native
+    from oracle import icp_oracle
+    pts = np.ascontiguousarray(kitti[:40000])
+    tgt, src, _ = icp_oracle.make_pair(77, n=3000, box=(30.0, 30.0, 5.0))
+    so = np.array([0, len(src), 2 * len(src)], np.int64)
+    out = []
+    for dev in (0, 1):
+        ctx = native.Context(dev)
+        ix = native.Index(ctx, pts)
+        a = ix.knn(pts, 8)
+        b = ix.knn_bruteforce(pts[:4096], 8)
+        icp = native.icp_batch(ctx, np.concatenate([src, src]), so, np.concatenate([tgt, tgt]), so,
+                               np.tile(np.eye(4), (2, 1, 1)), 30, 1e-5, 1e-5, 5.0, True, False)
+        assert np.array_equal(a[0][:4096], b[0]) and np.array_equal(a[1][:4096], b[1])
+        out.append((a, icp))
+    assert np.array_equal(out[0][0][0], out[1][0][0]) and np.array_equal(out[0][0][1], out[1][0][1])
+    assert np.array_equal(out[0][1]["iterations"], out[1][1]["iterations"])
+    assert np.allclose(out[0][1]["T_total"], out[1][1]["T_total"], rtol=0, atol=1e-12)
