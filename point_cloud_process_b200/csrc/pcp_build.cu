@@ -565,6 +565,183 @@ __global__ void __launch_bounds__(256) query_key_kernel(const float *__restrict_
     vals[i] = static_cast<unsigned>(i);
 }
 
+// ---- one cloud / one query set of up to 2^18 points: Morton keys and the stable two-pass radix sort in ONE kernel.
+// cub's device sort is four launches here (histogram, scan, two onesweep passes of ~11 us each: 22 CTAs of 5 888 keys
+// with a serial look-back chain) on the critical path of the KITTI step.  This kernel spreads the cloud over up to
+// one CTA per SM (256 threads, <= 8 keys per thread, kept in registers across the passes) and synchronises the grid
+// itself.  Per pass (8-bit digit, LSD):
+//   rank    every warp owns a contiguous run of its CTA's slice, lane-striped; it walks its <= 8 rows in order:
+//           peers = match_any(digit), rank inside the warp = the warp's running count of the digit (shared memory,
+//           private to the warp) + lower peers.  No shared-memory atomics; the running counts end as the warp's
+//           digit histogram.
+//   count   thread d adds the 8 warp histograms -> hist[cta][d] in global memory, and turns the warp histograms
+//           into exclusive warp offsets.                                                     -- grid barrier --
+//   scatter thread d: digit base = exclusive scan over d of the column totals + the column's CTAs before this one;
+//           destination = base + warp offset + rank inside the warp: the order of equal digits is (CTA, warp, row,
+//           lane) = input order, so each pass is stable and the permutation is the one cub produces.
+// Grid barriers: one counter each, G arrivals (the grid is at most one CTA per SM of 256 threads, so it is
+// co-resident beside anything else the library runs, and nothing it runs beside waits for it); counters are zero on
+// entry and the last CTA to leave zeroes them again.  Data written by other CTAs is read with ld.cg (past L1).
+constexpr int kSsThreads = 256, kSsItems = 8, kSsWarps = kSsThreads / 32;
+constexpr long long kSsMaxPoints = 1LL << 18;
+
+__device__ __forceinline__ void ss_grid_barrier(unsigned *counter, unsigned arrivals) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        unsigned seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+            if (seen < arrivals) __nanosleep(64);
+        } while (seen < arrivals);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kSsThreads)
+small_sort_kernel(const float *__restrict__ xyz, long long n, long long stride, const float *__restrict__ bbox, int skip,
+                  int items, unsigned *tmp_key, unsigned *tmp_val, unsigned *__restrict__ out_val, unsigned *hist,
+                  unsigned *sync) {
+    __shared__ unsigned s_cw[kSsWarps][256];   // per warp: running count of a digit, then its histogram, then its offset
+    __shared__ unsigned s_base[256];
+    __shared__ unsigned s_wsum[kSsWarps];
+    const unsigned t = threadIdx.x, lane = t & 31u, warp = t >> 5, G = gridDim.x, cta = blockIdx.x;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    // this warp's run of rows: [first, first + items * 32), row (it, lane) = first + it * 32 + lane
+    const long long first = ((long long)cta * kSsWarps + warp) * items * 32;
+    unsigned key[kSsItems], val[kSsItems];
+#pragma unroll
+    for (int it = 0; it < kSsItems; ++it) {
+        const long long i = first + it * 32 + lane;
+        key[it] = 0xffffffffu;                 // (beyond the run / the cloud: no digit, sorts nowhere)
+        val[it] = 0u;
+        if (it < items && i < n) {
+            const float *p = xyz + i * stride;
+            key[it] = morton30(__ldg(p), __ldg(p + 1), __ldg(p + 2), bbox) >> skip;     // 16 significant bits
+            val[it] = (unsigned)i;
+        }
+    }
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        const int shift = pass * 8;
+        unsigned *h = hist + (size_t)pass * G * 256;
+        for (unsigned d = lane; d < 256; d += 32) s_cw[warp][d] = 0u;
+        __syncwarp();
+        unsigned rank[kSsItems];
+#pragma unroll
+        for (int it = 0; it < kSsItems; ++it) {
+            rank[it] = 0;
+            if (it < items) {                                        // (uniform)
+                const bool live = key[it] != 0xffffffffu;
+                const unsigned dg = live ? (key[it] >> shift) & 255u : 256u + lane;   // dead rows match nobody
+                const unsigned peers = __match_any_sync(kFullMask, dg);
+                unsigned prior = 0;
+                if (live) prior = s_cw[warp][dg];
+                __syncwarp();
+                rank[it] = prior + __popc(peers & lt_mask);
+                if (live && (peers & lt_mask) == 0u) s_cw[warp][dg] = prior + __popc(peers);
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        {   // thread d: the CTA's count of digit d; warp histograms -> exclusive warp offsets
+            unsigned run = 0;
+#pragma unroll
+            for (int w = 0; w < kSsWarps; ++w) {
+                const unsigned c = s_cw[w][t];
+                s_cw[w][t] = run;
+                run += c;
+            }
+            h[(size_t)cta * 256 + t] = run;
+        }
+        ss_grid_barrier(sync + 2 * pass, G);
+        {   // digit bases
+            unsigned total = 0, before = 0;
+            for (unsigned c0 = 0; c0 < G; c0 += 16) {            // 16 independent loads in flight (L2 latency each)
+                unsigned v[16];
+#pragma unroll
+                for (unsigned j = 0; j < 16; ++j) v[j] = c0 + j < G ? __ldcg(h + (size_t)(c0 + j) * 256 + t) : 0u;
+#pragma unroll
+                for (unsigned j = 0; j < 16; ++j) {
+                    total += v[j];
+                    before += c0 + j < cta ? v[j] : 0u;
+                }
+            }
+            unsigned incl = total;
+#pragma unroll
+            for (int d = 1; d < 32; d *= 2) {
+                const unsigned o = __shfl_up_sync(kFullMask, incl, d);
+                if ((int)lane >= d) incl += o;
+            }
+            if (lane == 31u) s_wsum[warp] = incl;
+            __syncthreads();
+            unsigned wbase = 0;
+            for (unsigned w = 0; w < warp; ++w) wbase += s_wsum[w];
+            s_base[t] = wbase + incl - total + before;
+        }
+        __syncthreads();
+        if (pass == 0) {
+#pragma unroll
+            for (int it = 0; it < kSsItems; ++it) {
+                if (it < items && key[it] != 0xffffffffu) {
+                    const unsigned dg = key[it] & 255u;
+                    const unsigned dst = s_base[dg] + s_cw[warp][dg] + rank[it];
+                    tmp_key[dst] = key[it];
+                    tmp_val[dst] = val[it];
+                }
+            }
+            ss_grid_barrier(sync + 1, G);
+#pragma unroll
+            for (int it = 0; it < kSsItems; ++it) {
+                const long long i = first + it * 32 + lane;
+                key[it] = 0xffffffffu;
+                if (it < items && i < n) { key[it] = __ldcg(tmp_key + i); val[it] = __ldcg(tmp_val + i); }
+            }
+        } else {
+#pragma unroll
+            for (int it = 0; it < kSsItems; ++it) {
+                if (it < items && key[it] != 0xffffffffu) {
+                    const unsigned dg = (key[it] >> 8) & 255u;
+                    out_val[s_base[dg] + s_cw[warp][dg] + rank[it]] = val[it];
+                }
+            }
+        }
+        __syncthreads();                       // (s_cw / s_base are rewritten by the next pass)
+    }
+    // the last CTA to leave resets the barrier counters (every CTA has passed all three by then)
+    if (t == 0) {
+        __threadfence();
+        if (atomicAdd(sync + 3, 1u) == G - 1) { sync[0] = 0u; sync[1] = 0u; sync[2] = 0u; sync[3] = 0u; __threadfence(); }
+    }
+}
+
+// Launch helper: false if the set is outside the kernel's range (the caller falls back to cub).
+bool small_sort_applies(pcp_ctx *ctx, long long n, int skip) {
+    static const bool off = getenv("PCP_SMALL_SORT") && atoi(getenv("PCP_SMALL_SORT")) == 0;   // developer A/B
+    return !off && n > 0 && n <= kSsMaxPoints && skip == 14 && (long long)ctx->sm_count * kSsThreads * kSsItems >= n;
+}
+
+int small_sort(pcp_ctx *ctx, const float *d_xyz, long long n, long long stride, const float *d_bbox, int skip, unsigned *tmp_key,
+               unsigned *tmp_val, unsigned *out_val, DevBuf &state, cudaStream_t st) {
+    static const long long per_cta = getenv("PCP_SS_PER_CTA") ? atoll(getenv("PCP_SS_PER_CTA")) : 1024;   // developer sweep
+    const long long g_min = (n + (long long)kSsThreads * kSsItems - 1) / ((long long)kSsThreads * kSsItems);
+    const unsigned G = (unsigned)std::min<long long>(ctx->sm_count, std::max<long long>(g_min, (n + per_cta - 1) / per_cta));
+    const int items = (int)((n + (long long)G * kSsThreads - 1) / ((long long)G * kSsThreads));
+    // state: 4 barrier counters (zero between launches) + 2 x G x 256 histogram words
+    const size_t need = sizeof(unsigned) * (64 + 2 * (size_t)ctx->sm_count * 256);
+    if (state.cap < need) {
+        PCP_TRY(state.ensure(need));
+        PCP_CUDA(cudaMemsetAsync(state.p, 0, state.cap, st));
+    }
+    unsigned *sync = state.as<unsigned>(), *hist = sync + 64;
+    small_sort_kernel<<<G, kSsThreads, 0, st>>>(d_xyz, n, stride, d_bbox, skip, items, tmp_key, tmp_val, out_val, hist, sync);
+    ctx->launches += 1;
+    PCP_CUDA(cudaGetLastError());
+    return PCP_OK;
+}
+
 template <class KeyT>
 int radix_sort_pairs(pcp_ctx *ctx, const KeyT *k_in, KeyT *k_out, const unsigned *v_in, unsigned *v_out, long long n,
                      int begin_bit, int end_bit, cudaStream_t st = nullptr, DevBuf *tmp_buf = nullptr) {
@@ -739,7 +916,11 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
             ctx->launches += 1;
         }
         if (b->ev_bbox_record) PCP_CUDA(cudaEventRecord(b->ev_bbox_record, st));   // query keys only need the boxes, not the sorted cloud
-        for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
+        const bool one_kernel_sort = !wide && small_sort_applies(ctx, b->total_n, 30 - mbits);
+        if (one_kernel_sort)
+            PCP_TRY(small_sort(ctx, d_xyz, b->total_n, stride, b->bbox.as<float>(), 30 - mbits, b->keys_a.as<unsigned>(),
+                               b->vals_a.as<unsigned>(), b->vals_b.as<unsigned>(), ctx->ss_state[0], st));
+        for (int64_t p0 = 0; p0 < P && !one_kernel_sort; p0 += kMaxGridY) {
             const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
             if (wide64)
                 key_kernel<unsigned long long><<<dim3(grid_for(b->max_n, 256), gy), 256, 0, st>>>(
@@ -750,7 +931,8 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
                     b->vals_a.as<unsigned>());
             ctx->launches += 1;
         }
-        if (wide64) {
+        if (one_kernel_sort) {
+        } else if (wide64) {
             PCP_TRY(radix_sort_pairs<unsigned long long>(ctx, b->keys_a.as<unsigned long long>(),
                                                          b->keys_b.as<unsigned long long>(), b->vals_a.as<unsigned>(),
                                                          b->vals_b.as<unsigned>(), b->total_n, 0, mbits + seg_bits));
@@ -804,9 +986,14 @@ int sort_queries_on(pcp_index *ix, const float *d_q, int64_t nq, int64_t stride,
     if (nq == 0) return PCP_OK;
     for (int i = 0; i < 3; ++i) PCP_TRY(keys[i].ensure(sizeof(unsigned) * (size_t)nq));
     unsigned *ka = keys[0].as<unsigned>(), *kb = keys[1].as<unsigned>(), *va = keys[2].as<unsigned>();
-    query_key_kernel<<<grid_for(nq, 256), 256, 0, st>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
-    ctx->launches += 1;
-    PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30, st, &cub_tmp));
+    if (small_sort_applies(ctx, nq, morton_skip_bits(nq))) {
+        PCP_TRY(small_sort(ctx, d_q, nq, stride, make_view(ix).bbox, morton_skip_bits(nq), ka, va, d_perm,
+                           ctx->ss_state[st == ctx->stream ? 0 : 1], st));
+    } else {
+        query_key_kernel<<<grid_for(nq, 256), 256, 0, st>>>(d_q, nq, stride, make_view(ix).bbox, ka, va);
+        ctx->launches += 1;
+        PCP_TRY(radix_sort_pairs<unsigned>(ctx, ka, kb, va, d_perm, nq, morton_skip_bits(nq), 30, st, &cub_tmp));
+    }
     refine_queries_kernel<<<grid_for(nq, kRefine), kRefineT, 0, st>>>(d_q, nq, stride, d_perm);
     ctx->launches += 1;
     PCP_CUDA(cudaGetLastError());

@@ -296,6 +296,7 @@ int pcp_ctx_destroy(pcp_ctx *ctx) {
     DeviceGuard g(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     ctx->cub_tmp.release();
+    for (auto &b : ctx->ss_state) b.release();
     ctx->counters.release();
     ctx->radius_perm.release();
     ctx->voxel_out.release();

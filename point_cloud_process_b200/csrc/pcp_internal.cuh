@@ -141,6 +141,7 @@ struct pcp_ctx {
     size_t small_used = 0;
     bool h2d_by_kernel = false;           // a large upload occupies the copy engine: small structures go by kernel
     pcp::DevBuf cub_tmp;           // CUB temporary storage
+    pcp::DevBuf ss_state[2];       // small_sort_kernel: barrier counters + histograms (main stream / side stream)
     pcp::DevBuf scratch[8];        // per-call device scratch (keys, permutations, staged queries ...)
     pcp::PinBuf pin[4];            // pinned staging for host<->device copies
     pcp::DevBuf counters;          // 8 x u64 work counters (pcp_ctx_enable_counters)
