@@ -299,7 +299,7 @@ __device__ __forceinline__ void refine_store8(unsigned *dst, const unsigned (&v)
 // gate), their pair-layout copy, and the bucket / half-bucket AABBs.
 __global__ void __launch_bounds__(kRefineT) refine_leaf_kernel(const float *__restrict__ xyz, long long stride,
                                                                 const IndexView *__restrict__ views,
-                                                                const unsigned *__restrict__ sorted_rows) {
+                                                                const unsigned *__restrict__ sorted_rows, int fuse_upper) {
     __shared__ __align__(16) RefineSmem sm;
     __shared__ __align__(16) unsigned s_idx[kRefine];
     __shared__ unsigned s_node[6];                               // AABB of the whole block = the level-1 node
@@ -394,6 +394,42 @@ __global__ void __launch_bounds__(kRefineT) refine_leaf_kernel(const float *__re
         const long long at = v.level_off[1] + node;
         const_cast<float4 *>(v.box_lo)[at] = make_float4(ordered_to_float(s_node[0]), ordered_to_float(s_node[1]), ordered_to_float(s_node[2]), 0.f);
         const_cast<float4 *>(v.box_hi)[at] = make_float4(ordered_to_float(s_node[3]), ordered_to_float(s_node[4]), ordered_to_float(s_node[5]), 0.f);
+    }
+    // fuse_upper (small hierarchies: <= 1024 level-1 nodes per cloud): the LAST CTA of a cloud to get here also
+    // computes the few levels above (KITTI: 122 -> 4 -> 1 nodes), instead of a separate launch behind this kernel.
+    // Ticket = word 15 of the cloud's bounding-box record (zero between builds).
+    if (fuse_upper && v.n_levels > 2) {                          // (uniform over the CTA)
+        __shared__ bool s_last;
+        unsigned *ticket = reinterpret_cast<unsigned *>(const_cast<float *>(v.bbox)) + 15;
+        if (t == 0) {
+            __threadfence();
+            s_last = atomicAdd(ticket, 1u) == (unsigned)v.level_cnt[1] - 1u;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            float4 *box_lo = const_cast<float4 *>(v.box_lo), *box_hi = const_cast<float4 *>(v.box_hi);
+            const unsigned lane = t & 31u;
+            for (int level = 2; level < v.n_levels; ++level) {
+                for (long long nd = t >> 5; nd < v.level_cnt[level]; nd += kRefineT / 32) {
+                    const long long c = nd * kFan + lane;
+                    float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+                    if (c < v.level_cnt[level - 1]) {            // (written by other CTAs / the previous round: past L1)
+                        lo = __ldcg(box_lo + v.level_off[level - 1] + c);
+                        hi = __ldcg(box_hi + v.level_off[level - 1] + c);
+                    }
+                    const float lx = warp_min(lo.x), ly = warp_min(lo.y), lz = warp_min(lo.z);
+                    const float hx = warp_max(hi.x), hy = warp_max(hi.y), hz = warp_max(hi.z);
+                    if (lane == 0) {
+                        box_lo[v.level_off[level] + nd] = make_float4(lx, ly, lz, 0.f);
+                        box_hi[v.level_off[level] + nd] = make_float4(hx, hy, hz, 0.f);
+                    }
+                }
+                __threadfence();
+                __syncthreads();
+            }
+            if (t == 0) *ticket = 0u;
+        }
     }
 }
 
@@ -948,11 +984,12 @@ int batch_build_device(BatchIndex *b, const float *d_xyz, int64_t stride, int64_
     }
     for (int64_t p0 = 0; p0 < P; p0 += kMaxGridY) {
         const unsigned gy = (unsigned)std::min<int64_t>(kMaxGridY, P - p0);
+        const bool fuse_upper = b->level_max_cnt[1] <= 1024;     // the last CTA of a cloud finishes its hierarchy
         refine_leaf_kernel<<<dim3((unsigned)((b->max_leaf + kFan - 1) / kFan), gy), kRefineT, 0, st>>>(
-            d_xyz, stride, dv + p0, b->vals_b.as<unsigned>());
+            d_xyz, stride, dv + p0, b->vals_b.as<unsigned>(), fuse_upper ? 1 : 0);
         ctx->launches += 1;
         // level 1 came out of refine_leaf_kernel; wide levels get a launch each, the small ones above share one
-        for (int l = 2; l < b->max_levels; ++l) {
+        for (int l = 2; l < b->max_levels && !fuse_upper; ++l) {
             if (b->level_max_cnt[l] <= kFusedLevelNodes) {
                 upper_boxes_kernel<<<dim3(1, gy), 256, 0, st>>>(dv + p0, l);
                 ctx->launches += 1;

@@ -438,7 +438,7 @@ def test_cuda_graph_of_build_and_knn(pcp, kitti):
     ctx.graph_begin()
     step()
     g = ctx.graph_end()
-    assert g.nodes() >= 10
+    assert g.nodes() >= 5
     frames = [kitti, (kitti[::-1] * np.float32(1.01)).copy(), kitti + np.float32(0.25)]
     for f in frames[1:]:
         d.copy_(torch.from_numpy(f).cuda())
