@@ -490,3 +490,31 @@ def test_two_devices_in_one_process(kitti):
     assert np.array_equal(out[0][0][0], out[1][0][0]) and np.array_equal(out[0][0][1], out[1][0][1])
     assert np.array_equal(out[0][1]["iterations"], out[1][1]["iterations"])
     assert np.allclose(out[0][1]["T_total"], out[1][1]["T_total"], rtol=0, atol=1e-12)
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 1000, 1024, 1025, 4096, 20000, 37888, 37889, 131071, 262144, 262145, 1100000])
+def test_build_paths_by_cloud_size(n):
+    """Every build path by size -- the one-kernel sort (<= 2^18 points; grids of 1 .. 148 CTAs, 1 .. 7 keys per thread),
+    cub's device sort beyond it, the upper hierarchy levels fused into the refinement (<= 1024 level-1 nodes) or
+    launched separately -- gives an index whose searches equal the exhaustive kernel's, for query sets on both the
+    warp-per-query and the tiled path (whose regrouping uses the same sort)."""
+    import point_cloud_process_b200 as pcp
+    rng = np.random.default_rng(n)
+    pts = (rng.random((n, 3)) * np.array([40.0, 30.0, 6.0])).astype(np.float32)
+    if n > 64:
+        pts[n // 3:n // 3 + 40] = pts[7]                          # a mass of identical points
+    ctx = pcp.native.Context(0)
+    ix = pcp.native.Index(ctx, pts)
+    k = 4
+    for nq in (min(n, 500), 9000):
+        q = np.concatenate([pts[rng.integers(0, n, nq // 2 + 1)],
+                            (rng.random((nq // 2 + 1, 3)) * np.array([44.0, 33.0, 7.0]) - 2.0).astype(np.float32)])
+        got = ix.knn(q, k)
+        want = ix.knn_bruteforce(q, k)
+        for g, w, name in zip(got, want, ("idx", "dist", "count")):
+            assert np.array_equal(g, w), f"n={n} nq={len(q)}: {name} differs"
+    if n >= 1000:
+        sel = rng.integers(0, n, 3000)
+        got = ix.knn_self(k)
+        want = ix.knn_bruteforce(pts[sel], k)
+        assert np.array_equal(got[0][sel], want[0]) and np.array_equal(got[1][sel], want[1])
