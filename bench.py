@@ -500,6 +500,37 @@ def measure_icp(torch, pcp, ctx, stream, h_src, h_tgt, first_pair, n_pairs, n_pt
     return res
 
 
+# ---------------------------------------------------------------------------------------------- exhaustive kernel (K5)
+
+def measure_bruteforce(torch, pcp, ctx, stream, pts, k, reps, sm_count, sm_max_mhz):
+    """The exhaustive kNN kernel (pcp_brute.cu) over the whole scan, device resident: every (query, point) pair is
+    evaluated, so the evaluation count is exact (no counters) and the FP32 fraction is the evaluation loop's own."""
+    native = pcp.native
+    n = len(pts)
+    d = torch.from_numpy(pts).cuda()
+    idx = torch.empty((n, k), dtype=torch.int32, device="cuda")
+    dist = torch.empty((n, k), dtype=torch.float32, device="cuda")
+    cnt = torch.empty(n, dtype=torch.int32, device="cuda")
+    ix = native.Index(ctx, d.data_ptr(), n, 3)
+    ms = []
+    for _ in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ix.knn_bruteforce_device(d.data_ptr(), n, 3, k, idx.data_ptr(), dist.data_ptr(), cnt.data_ptr())
+        e1.record(stream)
+        ctx.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    t = statistics.median(ms[1:]) * 1e-3
+    evals = n * ((n + 31) // 32 * 32)
+    peak = sm_count * 128 * sm_max_mhz * 1e6
+    return {"workload": f"kitti_bruteforce k={k}", "queries": n, "ms": t * 1e3, "queries_per_s": n / t,
+            "roofline": {"bound": "fp32", "kernel": "brute_kernel", "achieved": 8 * evals / t / 1e12, "peak": peak / 1e12,
+                         "unit": "TFLOP/s (unfused FP32 ops; 8 per distance evaluation)", "frac": 8 * evals / t / peak,
+                         "distance_evaluations_per_launch": evals, "traffic": None,
+                         "note": "every pair of the 124 668 x 124 672 slots is evaluated (no pruning): the exhaustive "
+                                 "cross-check kernel of SURVEY K5, the packed-FP32 evaluation loop on its own"}}
+
+
 # ---------------------------------------------------------------------------------------------- radius (config 1)
 
 def measure_radius(torch, pcp, ctx, stream, pts, radius, reps, peaks):
@@ -742,6 +773,9 @@ def main():
     radius = None
     if rank == 0 and not args.no_radius and args.workload == "kitti_knn8":
         radius = measure_radius(torch, pcp, ctx, stream, w["pts"], 1.0, 5, peaks)
+    brute = None
+    if rank == 0 and world == 1 and not args.no_radius and args.workload == "kitti_knn8":
+        brute = measure_bruteforce(torch, pcp, ctx, stream, w["pts"], w["k"], 3, sm_count, float(peaks.get("sm_max_mhz", 1965.0)))
     c5 = None
     if world > 1 and not args.no_c5:
         sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -772,7 +806,7 @@ def main():
         line.update({k2: v for k2, v in knn_block.items() if k2 != "per_rank"})
         line.update({"data": "KITTI scan bundled with the reference (tests/golden copy)" if args.workload.startswith("kitti") else "synthetic",
                      "gpu_launches": knn["gpu_launches"], "series": series,
-                     "also": {"icp": icp, "radius": radius}})
+                     "also": {"icp": icp, "radius": radius, "bruteforce": brute}})
     else:
         line = dict(common)
         line.update({"metric": icp["metric"], "value": icp["value"], "unit": icp["unit"], "steps": icp["steps"],
