@@ -24,3 +24,4 @@ for i in range(reps + 1):
     e1.record(stream); ctx.synchronize()
     ms.append(e0.elapsed_time(e1))
 print({"pairs": P, "ms": ms, "pairs_per_s": P / (min(ms[1:]) * 1e-3), "iterations_hist": np.bincount(out["iterations"]).tolist()})
+its = np.asarray(out["iterations"]); print({"pair_iterations": int(its.sum()), "pair_iterations_per_s": float(its.sum() / (min(ms[1:]) * 1e-3)), "mean_iterations": float(its.mean())})
