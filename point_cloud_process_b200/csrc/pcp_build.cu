@@ -761,7 +761,7 @@ bool small_sort_applies(pcp_ctx *ctx, long long n, int skip) {
 
 int small_sort(pcp_ctx *ctx, const float *d_xyz, long long n, long long stride, const float *d_bbox, int skip, unsigned *tmp_key,
                unsigned *tmp_val, unsigned *out_val, DevBuf &state, cudaStream_t st) {
-    static const long long per_cta = getenv("PCP_SS_PER_CTA") ? atoll(getenv("PCP_SS_PER_CTA")) : 1024;   // developer sweep
+    static const long long per_cta = getenv("PCP_SS_PER_CTA") ? atoll(getenv("PCP_SS_PER_CTA")) : 2048;   // developer sweep (KITTI: 24.4 us at 1024, 23.1 us at 2048)
     const long long g_min = (n + (long long)kSsThreads * kSsItems - 1) / ((long long)kSsThreads * kSsItems);
     const unsigned G = (unsigned)std::min<long long>(ctx->sm_count, std::max<long long>(g_min, (n + per_cta - 1) / per_cta));
     const int items = (int)((n + (long long)G * kSsThreads - 1) / ((long long)G * kSsThreads));
