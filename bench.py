@@ -301,6 +301,7 @@ def measure_knn(torch, pcp, ctx, stream, w, args, dist, rank, world, local_rank,
         seen = [None] * world
         dist.all_gather_object(seen, {"reasons": clocks["reasons"], "ms_per_step": total_ms_local / K,
                                       "median_step_ms": statistics.median(step_ms), "max_step_ms": max(step_ms),
+                                      "sm_mhz": clocks.get("sm_mhz"), "clock_samples": clocks.get("samples"),
                                       "wall_ms_per_step": 1e3 * t_wall / K})
         clocks["reasons"] = sorted(set(r for s in seen for r in s["reasons"]))
         clocks["note"] = "sm_mhz: rank 0 (500 Hz); reasons: union over ranks (other ranks polled at 20 Hz)"
