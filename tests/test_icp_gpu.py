@@ -264,3 +264,24 @@ def test_icp_batch_pinned_host_pipeline_same_results(pcp, monkeypatch):
     # whole batch: float64 sums in another order)
     for key in ("T_last", "T_total", "diff_log"):
         assert np.allclose(np.asarray(ref[key]), np.asarray(got[key]), rtol=0, atol=1e-9, equal_nan=True), key
+
+
+def test_icp_rows_with_extra_columns(pcp):
+    """Oxford-layout clouds (x, y, z, nx, ny, nz per row, icp_template.py:11-17): only the first three columns are
+    read; same result as the packed clouds."""
+    from oracle import icp_oracle
+    rng = np.random.default_rng(3)
+    srcs, tgts, srcs6, tgts6 = [], [], [], []
+    for i, n in enumerate((5000, 20000, 333)):
+        tgt, src, _ = icp_oracle.make_pair(900 + i, n=n, box=(40.0, 40.0, 6.0))
+        srcs.append(src), tgts.append(tgt)
+        srcs6.append(np.concatenate([src, rng.normal(size=(n, 3)).astype(np.float32)], 1))
+        tgts6.append(np.concatenate([tgt, rng.normal(size=(n, 3)).astype(np.float32)], 1))
+    off = np.concatenate([[0], np.cumsum([len(s) for s in srcs])]).astype(np.int64)
+    T0 = np.tile(np.eye(4), (len(srcs), 1, 1))
+    ctx = pcp.native.Context(0)                  # (the native layer passes the row stride on; api.py would slice)
+    args = (T0, 30, 1e-6, 1e-6, 5.0, True, False)
+    a = pcp.native.icp_batch(ctx, np.concatenate(srcs), off, np.concatenate(tgts), off, *args)
+    b = pcp.native.icp_batch(ctx, np.concatenate(srcs6), off, np.concatenate(tgts6), off, *args)
+    assert np.array_equal(a["iterations"], b["iterations"]) and np.array_equal(a["status"], b["status"])
+    assert np.array_equal(np.asarray(a["T_total"]), np.asarray(b["T_total"]))

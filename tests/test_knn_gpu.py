@@ -518,3 +518,25 @@ def test_build_paths_by_cloud_size(n):
         got = ix.knn_self(k)
         want = ix.knn_bruteforce(pts[sel], k)
         assert np.array_equal(got[0][sel], want[0]) and np.array_equal(got[1][sel], want[1])
+
+
+@pytest.mark.parametrize("n", [3000, 60000])
+def test_rows_with_extra_columns(n):
+    """(N, 4) KITTI rows (x, y, z, intensity) and (Q, 6) query rows: only x, y, z are read (benchmark.py:16-27 keeps
+    the first three columns; the C ABI takes a row stride): same results as the packed (N, 3) arrays, on the
+    warp-per-query and the tiled path, for kNN, self-kNN and radius search."""
+    import point_cloud_process_b200 as pcp
+    rng = np.random.default_rng(n)
+    p3 = (rng.random((n, 3)) * 30).astype(np.float32)
+    q3 = (rng.random((n // 2, 3)) * 30).astype(np.float32)
+    p4 = np.concatenate([p3, rng.random((n, 1)).astype(np.float32) * 1e6], 1)
+    q6 = np.concatenate([q3, rng.normal(size=(len(q3), 3)).astype(np.float32) * 1e3], 1)
+    ctx = pcp.native.Context(0)                  # (the native layer passes the row stride on; api.py would slice)
+    a, b = pcp.native.Index(ctx, p3), pcp.native.Index(ctx, p4)
+    for x, y in zip(a.knn(q3, 8), b.knn(q6, 8)):
+        assert np.array_equal(x, y)
+    for x, y in zip(a.knn_self(5), b.knn_self(5)):
+        assert np.array_equal(x, y)
+    ra, rb = a.radius(q3[:3000], 1.5, True), b.radius(q6[:3000], 1.5, True)
+    for x, y in zip(ra, rb):
+        assert np.array_equal(x, y)
